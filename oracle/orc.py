@@ -1,0 +1,122 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes binding of oracle/_build/liboracle*.so.
+
+Importers allowed: tests/, __graft_entry__.smoke(), bench.py's cpu_baseline /
+--impl reference legs.  The product package (gmcore_b200/) never imports this.
+Parity unpinned by the reference's own tests (it ships none) — see orc_core.hpp.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+
+
+def build():
+    subprocess.check_call(["make", "-C", _ROOT, "oracle"], stdout=subprocess.DEVNULL)
+
+
+def _load(fast):
+    path = os.path.join(_HERE, "_build", "liboracle_fast.so" if fast else "liboracle.so")
+    if not os.path.exists(path):
+        build()
+    lib = C.CDLL(path)
+    P = C.POINTER(C.c_double)
+    lib.orc_create.restype = C.c_void_p
+    lib.orc_create.argtypes = [C.c_void_p, C.c_void_p, P]
+    lib.orc_destroy.argtypes = [C.c_void_p]
+    lib.orc_set_filters.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), P, C.c_int, C.POINTER(C.c_int), P, C.c_int]
+    lib.orc_set_static.argtypes = [C.c_void_p, P]
+    lib.orc_upload_state.argtypes = [C.c_void_p, C.c_int, P, P, P, P]
+    lib.orc_set_tracers.argtypes = [C.c_void_p, P]
+    lib.orc_get_tracers.argtypes = [C.c_void_p, P]
+    lib.orc_prepare_run.argtypes = [C.c_void_p]
+    lib.orc_run_steps.argtypes = [C.c_void_p, C.c_int, P]
+    lib.orc_diagnose.argtypes = [C.c_void_p, C.c_int, P]
+    for f in ("orc_old_index", "orc_new_index", "orc_time_step"):
+        getattr(lib, f).argtypes = [C.c_void_p]
+    lib.orc_get_field.restype = C.c_longlong
+    lib.orc_get_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p, P]
+    lib.orc_field_shape.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.POINTER(C.c_int)]
+    lib.orc_last_error.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+    return lib
+
+
+def _dp(a):
+    if a is None:
+        return C.POINTER(C.c_double)()
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class Oracle:
+    """CPU restatement driven with the same inputs as the GPU library.
+
+    `host` is a gmcore_b200.host.Host (mesh vectors, filters, config); only plain
+    numpy arrays / ctypes structs are taken from it.
+    """
+
+    def __init__(self, host, fast=False):
+        self.lib = _load(fast)
+        self.host = host
+        self.h = self.lib.orc_create(C.addressof(host.cfg), C.addressof(host.mesh_vectors), _dp(host.vec["full_lat_deg"]))
+        for which, (ngl, wl, ldl, nga, wa, lda) in enumerate(host.filters):
+            self.lib.orc_set_filters(self.h, which, ngl.ctypes.data_as(C.POINTER(C.c_int)), _dp(wl), ldl,
+                                     nga.ctypes.data_as(C.POINTER(C.c_int)), _dp(wa), lda)
+
+    def set_state(self, ic, itime=1):
+        self.lib.orc_set_static(self.h, _dp(ic["gzs"]))
+        self.lib.orc_upload_state(self.h, itime, _dp(ic["u_lon"]), _dp(ic["v_lat"]), _dp(ic["pt_or_gz"]), _dp(ic.get("phs")))
+
+    def set_tracers(self, q):
+        self.lib.orc_set_tracers(self.h, _dp(q))
+
+    def get_tracers(self):
+        n = self.host.cfg.ntracers
+        q = np.zeros((n,) + self.host.shape("cell"))
+        self.lib.orc_get_tracers(self.h, _dp(q))
+        return q
+
+    def prepare_run(self):
+        self._check(self.lib.orc_prepare_run(self.h))
+
+    def run_steps(self, n):
+        diag = np.zeros((n, 8))
+        self._check(self.lib.orc_run_steps(self.h, n, _dp(diag)))
+        return diag
+
+    def diagnose(self, itime=None):
+        out = np.zeros(8)
+        self.lib.orc_diagnose(self.h, self.old_index if itime is None else itime, _dp(out))
+        return out
+
+    @property
+    def old_index(self):
+        return self.lib.orc_old_index(self.h)
+
+    @property
+    def new_index(self):
+        return self.lib.orc_new_index(self.h)
+
+    def field(self, name, itime=None):
+        itime = self.old_index if itime is None else itime
+        shp = (C.c_int * 6)()
+        if self.lib.orc_field_shape(self.h, itime, name.encode(), shp) != 0:
+            raise KeyError(name)
+        a = np.zeros((shp[2], shp[1], shp[0]))
+        self.lib.orc_get_field(self.h, itime, name.encode(), _dp(a))
+        return a
+
+    def _check(self, rc):
+        if rc != 0:
+            buf = C.create_string_buffer(512)
+            self.lib.orc_last_error(self.h, buf, 512)
+            raise RuntimeError("oracle: " + buf.value.decode())
+
+    def __del__(self):
+        try:
+            self.lib.orc_destroy(self.h)
+        except Exception:
+            pass

@@ -1,0 +1,474 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_core.hpp).
+// Pass dispatcher, state update, time schemes, damping, tracer step, diagnostics:
+//   src/dynamics/operators_mod.F90:1008-1118   (calc_grad_ptf)
+//   src/dynamics/gmcore_mod.F90:97-136,213-341,343-591
+//   src/dynamics/time_schemes_mod.F90:102-288
+//   src/dynamics/damp/div_damp_mod.F90:27-139, lon_damp_mod.F90:43-68,158-241
+//   src/dynamics/adv/adv_mod.F90:152-312,420-455
+#pragma once
+#include <algorithm>
+#include "orc_ops.hpp"
+
+namespace orc {
+
+struct Model {
+  Block b;
+  std::vector<double> c_lon, c_lat;            // div_damp coefficients (j,k)
+  std::vector<double> wgt_full_lat;            // lon_damp latitude profile
+  int old_idx = 1, new_idx = 2, time_step = 0;
+  double alert_last = 0, alert_period = 0; bool alert_ring = false;   // 'moist' batch alert
+
+  double& clon(int j, int k) { return c_lon[(size_t)(k - 1) * b.mesh.nlat + (j - 1)]; }
+  double& clat(int j, int k) { return c_lat[(size_t)(k - 1) * b.mesh.nhalf + (j - 1)]; }
+
+  // ---- operators_mod.F90:1008-1118 ------------------------------------------
+  void calc_grad_ptf(State& s, Tend& t, double dt) {
+    const Mesh& mesh = b.mesh;
+    ffsl_calc_tracer_hflx_cell(b, b.adv_batch_mass, s.pt, s.ptf_lon, s.ptf_lat, dt, true);
+    fill_halo(mesh, s.ptf_lon, true, true, false, false, false);
+    fill_halo(mesh, s.ptf_lat, false, false, false, true, false);
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        t.dptfdlon(i, j, k) = (s.ptf_lon(i, j, k) - s.ptf_lon(i - 1, j, k)) * mesh.le_lon(j) / mesh.area_cell(j);
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        t.dptfdlat(i, j, k) = (s.ptf_lat(i, j, k) * mesh.le_lat(j) - s.ptf_lat(i, j - 1, k) * mesh.le_lat(j - 1)) / mesh.area_cell(j);
+    pole_flux_div(mesh, s.ptf_lat, t.dptfdlat);
+    A3& pt = s.pt;
+    for (int k = mesh.full_lev_ibeg - 1; k >= mesh.full_lev_ibeg - 2; --k)
+      for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
+        pt(i, j, k) = 2 * pt(i, j, k + 1) - pt(i, j, k + 2);
+    for (int k = mesh.full_lev_iend + 1; k <= mesh.full_lev_iend + 2; ++k)
+      for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
+        pt(i, j, k) = 2 * pt(i, j, k - 1) - pt(i, j, k - 2);
+    ffsl_calc_tracer_vflx_cell(b, b.adv_batch_mass, pt, s.ptf_lev);
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        t.dptfdlev(i, j, k) = s.ptf_lev(i, j, k + 1) - s.ptf_lev(i, j, k);
+  }
+
+  // ---- operators_mod.F90:96-134 ---------------------------------------------
+  void operators_prepare(State& s, double dt, int pass) {
+    const bool baro = b.cfg.baroclinic;
+    if (pass == 0) {           // all_pass (also operators_prepare_1 order differs only in calc_div position)
+      if (baro) calc_ph(b, s);
+      calc_m(b, s);
+      if (baro) calc_t(b, s);
+      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s);
+      if (baro) calc_gz_lev(b, s);
+    } else if (pass == 1) {    // forward_pass
+      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s);
+    } else {                   // backward_pass
+      if (baro) { calc_ph(b, s); calc_t(b, s); calc_gz_lev(b, s); }
+      calc_m(b, s);
+    }
+  }
+  // operators_prepare_1 (operators_mod.F90:73-94): calc_div after interp_pv.
+  void operators_prepare_1(State& s, double dt) {
+    const bool baro = b.cfg.baroclinic;
+    if (baro) calc_ph(b, s);
+    calc_m(b, s);
+    if (baro) calc_t(b, s);
+    calc_mf(b, s, dt); calc_ke(b, s); calc_pv(b, s); interp_pv(b, s); calc_div(b, s);
+    if (baro) calc_gz_lev(b, s);
+  }
+
+  // ---- gmcore_mod.F90:343-575 (forward_pass / backward_pass branches) ---------
+  void space_operators(const State& old_state, State& star, State& nw, Tend& tend1, const Tend& tend2, double dt, int pass) {
+    (void)old_state;
+    const Mesh& mesh = b.mesh;
+    const int jb = mesh.full_lat_ibeg_no_pole, je = mesh.full_lat_iend_no_pole;
+    tend1.reset_flags();
+    if (pass == 1) {
+      operators_prepare(star, dt, pass);
+      if (b.cfg.baroclinic) {
+        calc_grad_mf(b, star, tend1);
+        calc_dphsdt(b, tend1);
+        calc_we_lev(b, star, tend1, dt);
+        calc_wedudlev_wedvdlev(b, star, tend1);
+        calc_grad_ptf(star, tend1, dt);
+        calc_coriolis(b, star, tend1);
+        calc_grad_ke(b, star, tend1);
+        for (int k = 1; k <= mesh.nlev; ++k) {
+          for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.du(i, j, k) = tend1.qhv(i, j, k) - tend1.dkedlon(i, j, k) - tend1.wedudlev(i, j, k);
+          for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.dv(i, j, k) = -tend1.qhu(i, j, k) - tend1.dkedlat(i, j, k) - tend1.wedvdlev(i, j, k);
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.dpt(i, j, k) = -tend1.dptfdlon(i, j, k) - tend1.dptfdlat(i, j, k) - tend1.dptfdlev(i, j, k);
+        }
+        tend1.update_phs = true; tend1.update_pt = true;
+      } else {
+        calc_grad_mf(b, star, tend1);
+        calc_coriolis(b, star, tend1);
+        calc_grad_ke(b, star, tend1);
+        for (int k = 1; k <= mesh.nlev; ++k) {
+          for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.du(i, j, k) = tend1.qhv(i, j, k) - tend1.dkedlon(i, j, k);
+          for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.dv(i, j, k) = -tend1.qhu(i, j, k) - tend1.dkedlat(i, j, k);
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            tend1.dgz(i, j, k) = -(tend1.dmfdlon(i, j, k) + tend1.dmfdlat(i, j, k)) * b.cfg.g;
+        }
+        tend1.update_gz = true;
+      }
+    } else {
+      operators_prepare(nw, dt, pass);
+      pgf_run(b, nw, tend1);
+      for (int k = 1; k <= mesh.nlev; ++k) {
+        for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+          tend1.du(i, j, k) = tend2.du(i, j, k) - tend1.pgf_lon(i, j, k);
+        for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+          tend1.dv(i, j, k) = tend2.dv(i, j, k) - tend1.pgf_lat(i, j, k);
+      }
+      tend1.update_u = true; tend1.update_v = true;
+    }
+  }
+
+  // ---- time_schemes_mod.F90:120-242 -------------------------------------------
+  void update_state(Tend& tend, const State& old_state, State& ns, double dt) {
+    const Mesh& mesh = b.mesh;
+    if (b.cfg.baroclinic) {
+      if (tend.update_phs) {
+        for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+          ns.phs(i, j) = old_state.phs(i, j) + dt * tend.dphs(i, j);
+        fill_halo(mesh, ns.phs, true, true, true, false, false);
+        filter_full_lat(mesh, b.big_filter, ns.phs, &ns.phs_f, 1, 1);
+        fill_halo(mesh, ns.phs, true);
+        calc_ph(b, ns);
+        calc_m(b, ns);
+      }
+      if (tend.update_pt) {
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            ns.pt(i, j, k) = old_state.pt(i, j, k) * old_state.m(i, j, k) + dt * tend.dpt(i, j, k);
+        fill_halo(mesh, ns.pt, true, true, true, false, false);
+        filter_full_lat(mesh, b.small_filter1, ns.pt, nullptr, 1, mesh.nlev);
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            ns.pt(i, j, k) = ns.pt(i, j, k) / ns.m(i, j, k);
+        fill_halo(mesh, ns.pt, true);
+      }
+    } else {
+      if (tend.update_gz) {
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            ns.gz(i, j, k) = old_state.gz(i, j, k) + dt * tend.dgz(i, j, k);
+        fill_halo(mesh, ns.gz, true, true, true, false, false);
+        filter_full_lat(mesh, b.big_filter, ns.gz, &ns.gz_f, 1, mesh.nlev);
+        fill_halo(mesh, ns.gz_f, true);
+        filter_full_lat(mesh, b.small_filter1, ns.gz, nullptr, 1, mesh.nlev);
+        fill_halo(mesh, ns.gz, true);
+      }
+    }
+    if (tend.update_u && tend.update_v) {
+      for (int k = 1; k <= mesh.nlev; ++k)
+        for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+          ns.u_lon(i, j, k) = old_state.u_lon(i, j, k) + dt * tend.du(i, j, k);
+      for (int k = 1; k <= mesh.nlev; ++k)
+        for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+          ns.v_lat(i, j, k) = old_state.v_lat(i, j, k) + dt * tend.dv(i, j, k);
+      if (b.cfg.baroclinic) {
+        fill_halo(mesh, ns.u_lon, true, true, true, false, false);
+        filter_full_lat(mesh, b.small_filter2, ns.u_lon, nullptr, 1, mesh.nlev);
+        fill_halo(mesh, ns.u_lon, true);
+        fill_halo(mesh, ns.v_lat, false, true, true, false, false);
+        filter_half_lat(mesh, b.small_filter2, ns.v_lat, nullptr, 1, mesh.nlev);
+        fill_halo(mesh, ns.v_lat, false);
+      }
+      fill_halo(mesh, ns.u_lon, true);
+      fill_halo(mesh, ns.v_lat, false);
+      const double wgt = 0.6;
+      {
+        int j = mesh.half_lat_ibeg; A3& v = ns.v_lat;
+        for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
+          v(i, j, k) = (1 - wgt) * v(i, j, k) + wgt * v(i, j + 1, k);
+        j = mesh.half_lat_iend;
+        for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
+          v(i, j, k) = (1 - wgt) * v(i, j, k) + wgt * v(i, j - 1, k);
+      }
+      fill_halo(mesh, ns.v_lat, false, false, false, true, true);
+      filter_full_lat(mesh, b.big_filter, ns.u_lon, &ns.u_f, 1, mesh.nlev);
+      filter_half_lat(mesh, b.big_filter, ns.v_lat, &ns.v_f, 1, mesh.nlev);
+      fill_halo(mesh, ns.u_f, true);
+      fill_halo(mesh, ns.v_f, false);
+    }
+  }
+
+  // ---- time_schemes_mod.F90:102-118,244-288 -----------------------------------
+  void step(const State& old_state, State& star, State& nw, Tend& tend1, Tend& tend2, double dt) {
+    space_operators(old_state, star, nw, tend1, tend2, dt, 1);
+    update_state(tend1, old_state, nw, dt);
+    space_operators(old_state, star, nw, tend2, tend1, dt, 2);
+    update_state(tend2, old_state, nw, dt);
+  }
+  void time_integrator(int old, int nw, double dt) {
+    State* st = b.state; Tend* td = b.tend;
+    switch (b.cfg.time_scheme) {
+      case GMC_EULER:
+        step(st[old], st[old], st[nw], td[old], td[nw], dt); break;
+      case GMC_PC2:
+        step(st[old], st[old], st[nw], td[old], td[nw], dt / 2.0);
+        step(st[old], st[nw], st[3], td[old], td[nw], dt / 2.0);
+        step(st[old], st[3], st[nw], td[old], td[nw], dt); break;
+      default:  // wrfrk3
+        step(st[old], st[old], st[nw], td[old], td[nw], dt / 3.0);
+        step(st[old], st[nw], st[3], td[old], td[nw], dt / 2.0);
+        step(st[old], st[3], st[nw], td[old], td[nw], dt); break;
+    }
+  }
+
+  // ---- div_damp_mod.F90:27-87 ---------------------------------------------------
+  void div_damp_init() {
+    const Mesh& mesh = b.mesh; const gmc_config& c = b.cfg;
+    if (!c.use_div_damp) return;
+    c_lon.assign((size_t)mesh.nlat * mesh.nlev, 0.0); c_lat.assign((size_t)mesh.nhalf * mesh.nlev, 0.0);
+    for (int k = 1; k <= mesh.nlev; ++k) {
+      double fac = 1.0;
+      if (c.div_damp_order == 2 && c.baroclinic) {
+        // vert_coord_calc_ph(k, p0) with hyam/hybm = level means (hybrid_coord_mod.F90:120-125,146-152)
+        double hyam = 0.5 * (mesh.hyai(k) + mesh.hyai(k + 1)), hybm = 0.5 * (mesh.hybi(k) + mesh.hybi(k + 1));
+        double ph = hyam * (c.hybrid_p0 - c.ptop) + hybm * (c.p0 - c.ptop) + c.ptop;
+        fac = std::fmax(1.0, 8 * (1 + std::tanh(std::log(c.ptop / ph))));
+      }
+      for (int j = 2; j <= mesh.nlat - 1; ++j)
+        clon(j, k) = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * mesh.le_lon(j) * mesh.de_lon(j)
+                                           : c.div_damp_coef4 * (mesh.le_lon(j) * mesh.le_lon(j)) * (mesh.de_lon(j) * mesh.de_lon(j));
+      for (int j = 1; j <= mesh.nhalf; ++j)
+        clat(j, k) = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * mesh.le_lat(j) * mesh.de_lat(j)
+                                           : c.div_damp_coef4 * (mesh.le_lat(j) * mesh.le_lat(j)) * (mesh.de_lat(j) * mesh.de_lat(j));
+    }
+  }
+  // ---- div_damp_mod.F90:89-139 --------------------------------------------------
+  void div_damp_run(State& s) {
+    const Mesh& mesh = b.mesh;
+    calc_div(b, s);
+    A3 &u = s.u_lon, &v = s.v_lat; const A3& d = b.cfg.div_damp_order == 2 ? s.div : s.div2;
+    const double sgn = b.cfg.div_damp_order == 2 ? 1.0 : -1.0;
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+        double inc = clon(j, k) * (d(i + 1, j, k) - d(i, j, k)) / mesh.de_lon(j);
+        u(i, j, k) = sgn > 0 ? u(i, j, k) + inc : u(i, j, k) - inc;
+      }
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+        double inc = clat(j, k) * (d(i, j + 1, k) - d(i, j, k)) / mesh.de_lat(j);
+        v(i, j, k) = sgn > 0 ? v(i, j, k) + inc : v(i, j, k) - inc;
+      }
+    fill_halo(mesh, u, true); fill_halo(mesh, v, false);
+  }
+
+  // ---- lon_damp_mod.F90:43-68 -----------------------------------------------------
+  void lon_damp_init(const double* full_lat_deg /* 1-hy : nlat+hy */) {
+    const Mesh& mesh = b.mesh;
+    wgt_full_lat.assign(mesh.nlat + 1, 0.0);
+    auto deg = [&](int j) { return full_lat_deg[j - mesh.full_lat_lb]; };
+    const double lon_damp_lat0 = 80;
+    double lat0 = -deg(2);
+    for (int j = 2; j <= mesh.nlat - 1; ++j) {
+      double lat = std::fabs(deg(j));
+      double w = std::exp((lat0 - lat) * (lat0 - lat) * std::log(1.0e-3) / ((lat0 - lon_damp_lat0) * (lat0 - lon_damp_lat0)));
+      wgt_full_lat[j] = (w < 1.0e-6) ? 0.0 : w;
+    }
+  }
+  // ---- lon_damp_mod.F90:158-177,200-241 (order 2 branch) ----------------------------
+  void lon_damp_on_cell(A3& f) {
+    const Mesh& mesh = b.mesh;
+    std::vector<double> g(mesh.nlon + 2);
+    const double c = 0.25;  // 0.5**2
+    for (int k = 1; k <= mesh.nlev; ++k)
+      for (int j = 2; j <= mesh.nlat - 1; ++j) {
+        double wgt = wgt_full_lat[j];
+        if (wgt == 0) continue;
+        for (int i = 1; i <= mesh.nlon; ++i)
+          g[i] = wgt * (f(i, j, k) + c * (f(i - 1, j, k) - 2.0 * f(i, j, k) + f(i + 1, j, k))) + (1 - wgt) * f(i, j, k);
+        for (int i = 1; i <= mesh.nlon; ++i) f(i, j, k) = g[i];
+      }
+    fill_halo(mesh, f, true);
+  }
+
+  // ---- adv_mod.F90:420-455 ----------------------------------------------------------
+  void adv_accum_wind(int itime) {
+    if (!b.has_tracers) return;
+    State& s = b.state[itime];
+    accum_uv_cell(b, b.adv_batch, s.u_f, s.v_f, 0.0, false);
+    accum_mf_cell(b.adv_batch, s.mfx_lon, s.mfy_lat);
+    if (b.mesh.nlev > 1) accum_we_lev(b, b.adv_batch, s.we_lev, s.m_lev, 0.0, false);
+  }
+
+  // time_mod.F90:270-291 for the single tracer batch alert; clock = time_step * dt_dyn
+  bool time_is_alerted() {
+    double curr = time_step * b.cfg.dt_dyn;
+    if (alert_last + alert_period <= curr) { alert_ring = true; return true; }
+    return false;
+  }
+
+  // ---- adv_mod.F90:152-312 ----------------------------------------------------------
+  void adv_run(int itime) {
+    const Mesh& mesh = b.mesh;
+    adv_accum_wind(itime);
+    if (!b.has_tracers) return;
+    AdvBatch& B = b.adv_batch; State& st = b.state[itime];
+    const double dt_adv = b.cfg.dt_adv;
+    bool alerted = time_is_alerted();
+    if (alerted && time_step > 0) {
+      for (int l = 0; l < B.ntracers; ++l) {
+        A3& qo = B.q[B.old - 1][l]; A3& qn = B.q[B.nw - 1][l];
+        A3 &qmf_lon = B.qmf_lon, &qmf_lat = B.qmf_lat, &qmf_lev = B.qmf_lev; const A3& old_m = B.old_m; const A3& m = st.m;
+        ffsl_calc_tracer_hflx_cell(b, B, qo, qmf_lon, qmf_lat, 0.0, false);
+        fill_halo(mesh, qmf_lon, true, true, false, false, false);
+        fill_halo(mesh, qmf_lat, false, false, false, true, false);
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            qn(i, j, k) = old_m(i, j, k) * qo(i, j, k) - ((qmf_lon(i, j, k) - qmf_lon(i - 1, j, k)) * mesh.le_lon(j) +
+                          (qmf_lat(i, j, k) * mesh.le_lat(j) - qmf_lat(i, j - 1, k) * mesh.le_lat(j - 1))) / mesh.area_cell(j) * dt_adv;
+        std::vector<double> work(mesh.nlon);
+        {
+          int j = 1;
+          for (int k = 1; k <= mesh.nlev; ++k) {
+            for (int i = 1; i <= mesh.nlon; ++i) work[i - 1] = qmf_lat(i, j, k);
+            double pole = zonal_sum(work) * mesh.le_lat(j) / mesh.nlon / mesh.area_cell(j) * dt_adv;
+            for (int i = 1; i <= mesh.nlon; ++i) qn(i, j, k) = old_m(i, j, k) * qo(i, j, k) - pole;
+          }
+        }
+        {
+          int j = mesh.nlat;
+          for (int k = 1; k <= mesh.nlev; ++k) {
+            for (int i = 1; i <= mesh.nlon; ++i) work[i - 1] = qmf_lat(i, j - 1, k);
+            double pole = zonal_sum(work) * mesh.le_lat(j - 1) / mesh.nlon / mesh.area_cell(j) * dt_adv;
+            for (int i = 1; i <= mesh.nlon; ++i) qn(i, j, k) = old_m(i, j, k) * qo(i, j, k) + pole;
+          }
+        }
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            qn(i, j, k) = qn(i, j, k) / m(i, j, k);
+        // negative filling along x (sequential, order dependent)
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            if (qn(i, j, k) < 0) {
+              double qm0 = qn(i, j, k) * m(i, j, k), qm1 = qn(i - 1, j, k) * m(i - 1, j, k), qm2 = qn(i + 1, j, k) * m(i + 1, j, k);
+              double qm0_half = 0.5 * qm0;
+              if (qm1 >= qm0_half && qm2 >= qm0_half) {
+                qn(i - 1, j, k) = (qm1 - qm0_half) / m(i - 1, j, k);
+                qn(i + 1, j, k) = (qm2 - qm0_half) / m(i + 1, j, k);
+              } else if (qm1 > qm0) qn(i - 1, j, k) = (qm1 - qm0) / m(i - 1, j, k);
+              else if (qm2 > qm0) qn(i + 1, j, k) = (qm2 - qm0) / m(i + 1, j, k);
+              else b.fail("Negative tracer!");
+              qn(i, j, k) = 0;
+            }
+        for (int k = mesh.full_lev_lb; k <= 0; ++k)
+          for (int j = qn.jlb; j < qn.jlb + qn.nj; ++j) for (int i = qn.ilb; i < qn.ilb + qn.ni; ++i) qn(i, j, k) = qn(i, j, 1);
+        for (int k = mesh.nlev + 1; k <= mesh.full_lev_ub; ++k)
+          for (int j = qn.jlb; j < qn.jlb + qn.nj; ++j) for (int i = qn.ilb; i < qn.ilb + qn.ni; ++i) qn(i, j, k) = qn(i, j, mesh.nlev);
+        ffsl_calc_tracer_vflx_cell(b, B, qn, qmf_lev);
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            qn(i, j, k) = qn(i, j, k) - ((qmf_lev(i, j, k + 1) - qmf_lev(i, j, k)) * dt_adv) / m(i, j, k);
+        for (int k = 1; k <= mesh.nlev; ++k)
+          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+            if (qn(i, j, k) < 0) {
+              double qm0 = qn(i, j, k) * m(i, j, k);
+              double qm1 = k > 1 ? qn(i, j, k - 1) * m(i, j, k - 1) : 0.0;
+              double qm2 = k < mesh.nlev ? qn(i, j, k + 1) * m(i, j, k + 1) : 0.0;
+              double qm0_half = 0.5 * qm0;
+              if (qm1 >= qm0_half && qm2 >= qm0_half) {
+                if (qm1 > 0) qn(i, j, k - 1) = (qm1 - qm0_half) / m(i, j, k - 1);
+                if (qm2 > 0) qn(i, j, k + 1) = (qm2 - qm0_half) / m(i, j, k + 1);
+              } else if (qm1 > qm0) { if (qm1 > 0) qn(i, j, k - 1) = (qm1 - qm0) / m(i, j, k - 1); }
+              else if (qm2 > qm0) { if (qm2 > 0) qn(i, j, k + 1) = (qm2 - qm0) / m(i, j, k + 1); }
+              else b.fail("Negative tracer!");
+              qn(i, j, k) = 0;
+            }
+        fill_halo(mesh, qn, true, true, true, false, false);
+        for (int it = 0; it < 3; ++it) lon_damp_on_cell(qn);
+        fill_halo(mesh, qn, true);
+      }
+      std::swap(B.old, B.nw);
+    }
+    copy_arr(B.old_m, st.m);
+  }
+
+  // ---- gmcore_mod.F90:213-341 ---------------------------------------------------------
+  void diagnose(int itime, double out[8]) {
+    const Mesh& mesh = b.mesh; State& s = b.state[itime]; const double g = b.cfg.g, cpd = b.cfg.cpd;
+    double tm = 0, te_ke = 0, te_ie = 0, te_pe = 0, tav = 0, tpe = 0, tpt = 0;
+    for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+      tm = tm + s.m(i, j, k) * mesh.area_cell(j);
+    for (int k = 1; k <= mesh.nlev; ++k) {
+      for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        te_ke = te_ke + s.mfx_lon(i, j, k) * 0.5 * s.u_lon(i, j, k) * mesh.area_lon(j) * 2;
+      for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        te_ke = te_ke + s.mfy_lat(i, j, k) * 0.5 * s.v_lat(i, j, k) * mesh.area_lat(j) * 2;
+    }
+    if (b.cfg.baroclinic) {
+      for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        te_ie = te_ie + s.m(i, j, k) * cpd * s.t(i, j, k) * mesh.area_cell(j);
+      for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        te_pe = te_pe + b.st.gzs(i, j) * s.phs(i, j) * mesh.area_cell(j);
+    } else {
+      for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        te_pe = te_pe + (s.m(i, j, 1) * s.m(i, j, 1) * g * 0.5 + s.m(i, j, 1) * b.st.gzs(i, j)) * mesh.area_cell(j);
+    }
+    for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+      tav = tav + s.pv(i, j, k) * mesh.area_vtx(j);
+    for (int k = 1; k <= mesh.nlev; ++k) {
+      for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        tpe = tpe + s.m_lon(i, j, k) * (s.pv_lon(i, j, k) * s.pv_lon(i, j, k)) * 0.5 * mesh.area_lon(j);
+      for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        tpe = tpe + s.m_lat(i, j, k) * (s.pv_lat(i, j, k) * s.pv_lat(i, j, k)) * 0.5 * mesh.area_lat(j);
+    }
+    if (b.cfg.baroclinic)
+      for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        tpt = tpt + s.m(i, j, k) * s.pt(i, j, k) * mesh.area_cell(j);
+    double te = te_ke + te_ie + te_pe;
+    s.tm = tm; s.te = te; s.tav = tav; s.tpe = tpe; s.te_ke = te_ke; s.te_ie = te_ie; s.te_pe = te_pe; s.tpt = tpt;
+    out[0] = tm; out[1] = te; out[2] = tav; out[3] = tpe; out[4] = te_ke; out[5] = te_ie; out[6] = te_pe; out[7] = tpt;
+  }
+
+  // ---- gmcore_mod.F90:101-136 (pre-loop of gmcore_run) -----------------------------------
+  void prepare_run(int old) {
+    const Mesh& mesh = b.mesh; State& s = b.state[old];
+    if (b.cfg.baroclinic) {
+      // prepare_static (dzsdlon/dzsdlat) is unused on this path; gz_lev bottom = gzs (T14)
+      for (int it = 1; it <= 3; ++it) {
+        A3& gl = b.state[it].gz_lev;
+        for (int j = gl.jlb; j < gl.jlb + gl.nj; ++j) for (int i = gl.ilb; i < gl.ilb + gl.ni; ++i)
+          gl(i, j, mesh.half_lev_iend) = b.st.gzs(i, j);
+      }
+    }
+    filter_full_lat(mesh, b.big_filter, s.u_lon, &s.u_f, 1, mesh.nlev);
+    fill_halo(mesh, s.u_f, true);
+    filter_half_lat(mesh, b.big_filter, s.v_lat, &s.v_f, 1, mesh.nlev);
+    fill_halo(mesh, s.v_f, false);
+    if (b.cfg.baroclinic) {
+      filter_full_lat(mesh, b.big_filter, s.phs, &s.phs_f, 1, 1);
+      fill_halo(mesh, s.phs_f, true);
+    } else {
+      filter_full_lat(mesh, b.big_filter, s.gz, &s.gz_f, 1, mesh.nlev);
+      fill_halo(mesh, s.gz_f, true);
+    }
+    if (b.has_tracers) copy_arr(b.adv_batch.old_m, s.m);
+    copy_arr(b.adv_batch_mass.old_m, s.m);
+    adv_accum_wind(old);
+    operators_prepare_1(s, b.cfg.dt_dyn);
+  }
+
+  // ---- gmcore_mod.F90:577-591 --------------------------------------------------------------
+  void time_integrate(int old, int nw, double dt) {
+    time_integrator(old, nw, dt);
+    if (b.cfg.test_forcing == GMC_FORCING_HELD_SUAREZ) held_suarez_forcing(b.state[nw], dt);
+    if (b.cfg.use_div_damp) div_damp_run(b.state[nw]);
+    adv_run(nw);
+  }
+  // time_advance (time_mod.F90:128-159)
+  void time_advance() {
+    if (alert_ring) { alert_last = time_step * b.cfg.dt_dyn; alert_ring = false; }
+    std::swap(old_idx, new_idx);
+    time_step += 1;
+  }
+
+  // held_suarez_test_mod.F90:65-113
+  void held_suarez_forcing(State& s, double dt);
+};
+
+}  // namespace orc
