@@ -1,0 +1,77 @@
+// Common device-side definitions for the GMCORE dynamics kernels (sm_100a).
+//
+// Data layout in HBM: every field is a dense FP64 array
+// (lev, lat_row, lon) with longitude contiguous and NO longitude halo — the
+// periodic wrap is an index map inside the kernels (fill_halo W/E in
+// src/utils/parallel_mod.F90:489-499 becomes `wrapi`).  Latitude rows carry HL
+// materialised halo rows on each side (pole mirror or neighbour band rows,
+// parallel_mod.F90:501-563).  Rows are 128-byte aligned when nlon % 16 == 0.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdint>
+
+#define GMC_HL 2   // device latitude halo rows (== reference lat_halo_width)
+
+struct Geo {
+  int nlon, nlat, nlev;   // global sizes
+  int nhalf;              // nlat - 1
+  int jlo;                // global full-lat index of device row 0 (= lat_ibeg - HL)
+  int NY;                 // device rows per level (owned + 2*HL)
+  int jb, je;             // owned full-lat rows (global, inclusive)
+  int hjb, hje;           // owned half-lat rows (global, inclusive)
+  int has_south, has_north;
+  long long plane;        // NY * nlon
+};
+
+__host__ __device__ __forceinline__ long long gidx(const Geo& g, int i, int j, int k) {
+  return ((long long)k * g.NY + (j - g.jlo)) * g.nlon + i;
+}
+__device__ __forceinline__ int wrapi(int i, int nlon) {
+  return i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
+}
+
+// Per-latitude coefficient vectors (mesh_type, src/dynamics/mesh_mod.F90:84-110),
+// stored with the reference's lower bound 1-hy = -1, so entry j lives at [j+1].
+struct DMesh {
+  const double *full_lat, *half_lat, *full_cos_lat, *half_cos_lat, *full_sin_lat, *half_sin_lat;
+  const double *area_cell, *area_lon, *area_lon_west, *area_lon_east, *area_lon_north, *area_lon_south;
+  const double *area_lat, *area_lat_west, *area_lat_east, *area_lat_north, *area_lat_south, *area_vtx;
+  const double *area_subcell;   // (2, j)
+  const double *de_lon, *le_lon, *de_lat, *le_lat, *full_f, *half_f;
+  const double *full_tangent_wgt, *half_tangent_wgt;   // (2, j)
+  const double *half_lon;       // lower bound 1-hx
+  const double *hyai, *hybi, *full_lev, *half_lev, *full_dlev, *half_dlev;  // 1-based / -1-based as in the header
+  int hx;
+};
+#define MJ(v, j) (v[(j) + 1])                  // vector entry at latitude index j
+#define MJ2(v, c, j) (v[((j) + 1) * 2 + ((c) - 1)])   // (c, j) of a (2,:) array, c = 1|2
+
+struct DFilter {
+  const int* ngrid_lon; const double* wgt_lon; int ld_lon;
+  const int* ngrid_lat; const double* wgt_lat; int ld_lat;
+  int max_hn;
+};
+
+#define CUDA_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { \
+  snprintf(h->err, sizeof(h->err), "%s:%d %s: %s", __FILE__, __LINE__, #x, cudaGetErrorString(e_)); return 1; } } while (0)
+
+__device__ __forceinline__ double sign1(double x) { return copysign(1.0, x); }
+
+// Block-wide sum in a fixed (deterministic) order: warp shuffles then warp 0.
+__device__ __forceinline__ double block_sum(double v, double* sm /* >= 32 doubles */) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) sm[w] = v;
+  __syncthreads();
+  double r = 0;
+  if (w == 0) {
+    r = lane < nw ? sm[lane] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_down_sync(0xffffffffu, r, o);
+    if (lane == 0) sm[0] = r;
+  }
+  __syncthreads();
+  r = sm[0];
+  return r;
+}

@@ -1,0 +1,226 @@
+// libgmcore_b200.so — C ABI of include/gmcore_gpu.h: the GMCORE dynamics hot path
+// (time_integrate and the pre-loop of gmcore_run) as sm_100a CUDA kernels.
+// There is no CPU fallback: every entry point fails if no CUDA device is usable.
+#include "handle.cuh"
+#include "kernels_dyn.cuh"
+#include "kernels_update.cuh"
+#include "kernels_hydro.cuh"
+#include "steps.cuh"
+
+extern "C" {
+
+int gmc_last_error(gmc_handle* h, char* buf, int len) {
+  if (!h) { snprintf(buf, len, "null handle"); return 1; }
+  snprintf(buf, len, "%s", h->err);
+  return h->err[0] ? 1 : 0;
+}
+
+static char g_create_err[512];
+const char* gmc_create_error() { return g_create_err; }
+
+int gmc_create(const gmc_config* cfg, gmc_handle** out) {
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    snprintf(g_create_err, sizeof(g_create_err), "no CUDA device (%s); the GMCORE GPU core has no CPU fallback",
+             cudaGetErrorString(e));
+    return 2;
+  }
+  gmc_handle* h = new gmc_handle();
+  h->cfg = *cfg;
+  if (cudaSetDevice(cfg->device) != cudaSuccess) { snprintf(g_create_err, sizeof(g_create_err), "cudaSetDevice(%d) failed", cfg->device); delete h; return 2; }
+  if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
+  if (cfg->coriolis_scheme != 1) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d not built (only 1)", cfg->coriolis_scheme); delete h; return 3; }
+  if (cfg->use_div_damp && cfg->div_damp_order != 2) { snprintf(g_create_err, sizeof(g_create_err), "div_damp_order=%d not built (only 2)", cfg->div_damp_order); delete h; return 3; }
+  if (cfg->use_smag_damp) { snprintf(g_create_err, sizeof(g_create_err), "use_smag_damp not built"); delete h; return 3; }
+  if (cfg->nranks != 1) { snprintf(g_create_err, sizeof(g_create_err), "nranks>1: use gmc_create_band"); delete h; return 3; }
+  Geo& g = h->g;
+  g.nlon = cfg->nlon; g.nlat = cfg->nlat; g.nlev = cfg->nlev; g.nhalf = cfg->nlat - 1;
+  g.jb = cfg->lat_ibeg; g.je = cfg->lat_iend;
+  g.has_south = g.jb == 1; g.has_north = g.je == g.nlat;
+  g.hjb = g.jb; g.hje = g.has_north ? g.je - 1 : g.je;
+  g.jlo = g.jb - GMC_HL; g.NY = (g.je - g.jb + 1) + 2 * GMC_HL;
+  g.plane = (long long)g.NY * g.nlon;
+  cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  const size_t n3 = (size_t)g.plane * g.nlev, n3h = (size_t)g.plane * (g.nlev + 1), n2 = (size_t)g.plane;
+  const bool baro = cfg->baroclinic != 0;
+  int rc = 0;
+  for (int s = 1; s <= 3 && !rc; ++s) {
+    DState& S = h->st[s];
+    auto A = [&](const char* name, double** p, size_t n, int kind) { if (!rc) { rc = dev_alloc(h, p, n); S.names[name] = {*p, kind}; } };
+    A("u_lon", &S.u, n3, 0); A("v_lat", &S.v, n3, 1); A("u_f", &S.u_f, n3, 0); A("v_f", &S.v_f, n3, 1);
+    A("m", &S.m, n3, 0); A("mfx_lon", &S.mfx_lon, n3, 0); A("mfy_lat", &S.mfy_lat, n3, 1);
+    A("u_lat", &S.u_lat, n3, 1); A("v_lon", &S.v_lon, n3, 0); A("ke", &S.ke, n3, 0); A("pv", &S.pv, n3, 1);
+    A("pv_lon", &S.pv_lon, n3, 0); A("pv_lat", &S.pv_lat, n3, 1); A("div", &S.div, n3, 0);
+    if (!baro) { A("gz", &S.gz, n3, 0); A("gz_f", &S.gz_f, n3, 0); }
+    else {
+      A("pt", &S.pt, n3, 0); A("phs", &S.phs, n2, 3); A("phs_f", &S.phs_f, n2, 3);
+      A("ph_lev", &S.ph_lev, n3h, 2); A("ph_exn_lev", &S.ph_exn_lev, n3h, 2); A("t", &S.t, n3, 0);
+      A("gz_lev", &S.gz_lev, n3h, 2); A("we_lev", &S.we_lev, n3h, 2); A("m_lev", &S.m_lev, n3h, 2);
+    }
+  }
+  if (!rc) rc = dev_alloc(h, &h->du, n3);
+  if (!rc) rc = dev_alloc(h, &h->dv, n3);
+  if (!rc) rc = dev_alloc(h, &h->gzs, n2);
+  if (!rc) rc = dev_alloc(h, &h->pole_dmf, (size_t)2 * g.nlev);
+  if (!rc) rc = dev_alloc(h, &h->pole_work, (size_t)16 * g.nlev);
+  if (!rc) rc = dev_alloc(h, &h->diag_partial, (size_t)7 * (g.je - g.jb + 1) * g.nlev);
+  if (!rc) rc = dev_alloc(h, &h->diag_out, 8);
+  if (!rc && baro) rc = hydro_alloc(h);
+  h->stage_bytes = (size_t)(g.nlon + 2 * cfg->hx) * ((g.je - g.jb + 1) + 2 * cfg->hy) * (g.nlev + 4) * sizeof(double);
+  if (!rc) { double* p; rc = dev_alloc(h, &p, h->stage_bytes / sizeof(double)); h->stage_img = p; }
+  if (rc) { snprintf(g_create_err, sizeof(g_create_err), "%s", h->err); gmc_destroy(h); return 4; }
+  h->nstep = (int)(cfg->dt_adv / cfg->dt_dyn);
+  h->alert_period = cfg->dt_adv; h->alert_last = -cfg->dt_adv;
+  *out = h;
+  return 0;
+}
+
+void gmc_destroy(gmc_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->cfg.device);
+  cudaDeviceSynchronize();
+  for (void* p : h->allocs) cudaFree(p);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+int gmc_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
+  const gmc_config& c = h->cfg;
+  const size_t nf = c.nlat + 2 * c.hy, nh = c.nlat - 1 + 2 * c.hy, nl = c.nlon + 2 * c.hx;
+  if (c.hy != 2) { snprintf(h->err, sizeof(h->err), "lat_halo_width must be 2"); return 1; }
+  DMesh& M = h->M;
+  int rc = 0;
+#define UPF(x) if (!rc) rc = dev_upload(h, &M.x, mv->x, nf)
+#define UPH(x) if (!rc) rc = dev_upload(h, &M.x, mv->x, nh)
+  UPF(full_lat); UPH(half_lat); UPF(full_cos_lat); UPH(half_cos_lat); UPF(full_sin_lat); UPH(half_sin_lat);
+  UPF(area_cell); UPF(area_lon); UPF(area_lon_west); UPF(area_lon_east); UPF(area_lon_north); UPF(area_lon_south);
+  UPH(area_lat); UPH(area_lat_west); UPH(area_lat_east); UPH(area_lat_north); UPH(area_lat_south); UPH(area_vtx);
+  UPF(de_lon); UPF(le_lon); UPH(de_lat); UPH(le_lat); UPF(full_f); UPH(half_f);
+  if (!rc) rc = dev_upload(h, &M.area_subcell, mv->area_subcell, 2 * nf);
+  if (!rc) rc = dev_upload(h, &M.full_tangent_wgt, mv->full_tangent_wgt, 2 * nf);
+  if (!rc) rc = dev_upload(h, &M.half_tangent_wgt, mv->half_tangent_wgt, 2 * nh);
+  if (!rc) rc = dev_upload(h, &M.half_lon, mv->half_lon, nl);
+  if (c.baroclinic) {
+    if (!mv->hyai) { snprintf(h->err, sizeof(h->err), "hybrid coefficients missing"); return 1; }
+    if (!rc) rc = dev_upload(h, &M.hyai, mv->hyai, (size_t)c.nlev + 1);
+    if (!rc) rc = dev_upload(h, &M.hybi, mv->hybi, (size_t)c.nlev + 1);
+    if (!rc) rc = dev_upload(h, &M.half_lev, mv->half_lev, (size_t)c.nlev + 1);
+    if (!rc) rc = dev_upload(h, &M.half_dlev, mv->half_dlev, (size_t)c.nlev + 1);
+    if (!rc) rc = dev_upload(h, &M.full_lev, mv->full_lev, (size_t)c.nlev + 4);
+    if (!rc) rc = dev_upload(h, &M.full_dlev, mv->full_dlev, (size_t)c.nlev + 4);
+    if (!rc) rc = hydro_set_mesh(h, mv);
+  }
+#undef UPF
+#undef UPH
+  M.hx = c.hx;
+  h->mesh_set = !rc;
+  return rc;
+}
+
+int gmc_set_filters(gmc_handle* h, int which, const int* ngrid_lon, const double* wgt_lon, int ld_lon,
+                    const int* ngrid_lat, const double* wgt_lat, int ld_lat) {
+  if (which < 0 || which > 2) { snprintf(h->err, sizeof(h->err), "bad filter id %d", which); return 1; }
+  const gmc_config& c = h->cfg;
+  const size_t nf = c.nlat + 2 * c.hy, nh = c.nlat - 1 + 2 * c.hy;
+  DFilter& F = h->filt[which];
+  int rc = dev_upload(h, &F.ngrid_lon, ngrid_lon, nf);
+  if (!rc) rc = dev_upload(h, &F.ngrid_lat, ngrid_lat, nh);
+  if (!rc) rc = dev_upload(h, &F.wgt_lon, wgt_lon, nf * ld_lon);
+  if (!rc) rc = dev_upload(h, &F.wgt_lat, wgt_lat, nh * ld_lat);
+  F.ld_lon = ld_lon; F.ld_lat = ld_lat;
+  int mx = 0;
+  for (size_t j = 0; j < nf; ++j) mx = ngrid_lon[j] > mx ? ngrid_lon[j] : mx;
+  for (size_t j = 0; j < nh; ++j) mx = ngrid_lat[j] > mx ? ngrid_lat[j] : mx;
+  F.max_hn = mx > 1 ? (mx - 1) / 2 : 0;
+  if (F.max_hn > h->max_hn) h->max_hn = F.max_hn;
+  if (F.max_hn >= c.nlon) { snprintf(h->err, sizeof(h->err), "filter wider than the zonal circle"); return 1; }
+  h->filters_set[which] = !rc;
+  return rc;
+}
+
+// kind: 0 full-lat full-lev, 1 half-lat full-lev, 2 full-lat half-lev, 3 2-D full-lat
+static int xfer(gmc_handle* h, double* dev, double* host, int kind, int dir) {
+  const gmc_config& c = h->cfg; const Geo& g = h->g;
+  PackArgs a;
+  a.dev = dev; a.img = h->stage_img; a.hx = c.hx; a.hy = c.hy; a.nx = c.nlon + 2 * c.hx;
+  const int nrows_full = g.je - g.jb + 1, nrows_half = g.hje - g.hjb + 1;
+  a.nrows = kind == 1 ? nrows_half : nrows_full;
+  a.ny = a.nrows + 2 * c.hy;
+  a.jfirst = g.jb;
+  a.klev0 = (kind == 0 || kind == 1) ? 2 : 0;
+  a.nk = kind == 3 ? 1 : (kind == 2 ? c.nlev + 1 : c.nlev);
+  const int nz_img = kind == 3 ? 1 : (kind == 2 ? c.nlev + 1 : c.nlev + 4);
+  const size_t bytes = (size_t)a.nx * a.ny * nz_img * sizeof(double);
+  dim3 grid((g.nlon + 127) / 128, a.nrows, a.nk);
+  if (dir == 0) {
+    CUDA_CHECK(cudaMemcpyAsync(h->stage_img, host, bytes, cudaMemcpyHostToDevice, h->stream));
+    LAUNCH(h, k_pack, grid, 128, 0, g, a, 0);
+  } else {
+    CUDA_CHECK(cudaMemsetAsync(h->stage_img, 0, bytes, h->stream));
+    LAUNCH(h, k_pack, grid, 128, 0, g, a, 1);
+    CUDA_CHECK(cudaMemcpyAsync(host, h->stage_img, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+  }
+  CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int gmc_set_static(gmc_handle* h, const double* gzs) { return xfer(h, h->gzs, const_cast<double*>(gzs), 3, 0); }
+
+int gmc_upload_state(gmc_handle* h, int itime, const double* u, const double* v, const double* s, const double* phs) {
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  DState& S = h->st[itime];
+  if (xfer(h, S.u, const_cast<double*>(u), 0, 0)) return 1;
+  if (xfer(h, S.v, const_cast<double*>(v), 1, 0)) return 1;
+  if (h->cfg.baroclinic) {
+    if (!phs) { snprintf(h->err, sizeof(h->err), "phs is required for the hydrostatic core"); return 1; }
+    if (xfer(h, S.pt, const_cast<double*>(s), 0, 0)) return 1;
+    if (xfer(h, S.phs, const_cast<double*>(phs), 3, 0)) return 1;
+  } else {
+    if (xfer(h, S.gz, const_cast<double*>(s), 0, 0)) return 1;
+  }
+  return 0;
+}
+
+int gmc_download_state(gmc_handle* h, int itime, double* u, double* v, double* s, double* phs) {
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  DState& S = h->st[itime];
+  if (u && xfer(h, S.u, u, 0, 1)) return 1;
+  if (v && xfer(h, S.v, v, 1, 1)) return 1;
+  if (h->cfg.baroclinic) {
+    if (s && xfer(h, S.pt, s, 0, 1)) return 1;
+    if (phs && xfer(h, S.phs, phs, 3, 1)) return 1;
+  } else {
+    if (s && xfer(h, S.gz, s, 0, 1)) return 1;
+  }
+  return 0;
+}
+
+int gmc_get_field(gmc_handle* h, int itime, const char* name, double* buf) {
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  std::string n(name);
+  double* p = nullptr; int kind = 0;
+  auto it = h->st[itime].names.find(n);
+  if (it != h->st[itime].names.end()) { p = it->second.first; kind = it->second.second; }
+  else if (hydro_work_field(h, n, &p, &kind)) {}
+  else if (n == "du") { p = h->du; kind = 0; }
+  else if (n == "dv") { p = h->dv; kind = 1; }
+  else if (n == "gzs") { p = h->gzs; kind = 3; }
+  if (!p) { snprintf(h->err, sizeof(h->err), "unknown field %s", name); return 1; }
+  return xfer(h, p, buf, kind, 1);
+}
+
+int gmc_synchronize(gmc_handle* h) {
+  CUDA_CHECK(cudaStreamSynchronize(h->stream));
+  CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+int gmc_launch_count(gmc_handle* h, long long* launches) { *launches = h->launches; return 0; }
+void* gmc_stream(gmc_handle* h) { return (void*)h->stream; }
+int gmc_struct_sizes(int* cfg, int* mv) { *cfg = (int)sizeof(gmc_config); *mv = (int)sizeof(gmc_mesh_vectors); return 0; }
+
+}  // extern "C"
+
+#include "api_run.cuh"

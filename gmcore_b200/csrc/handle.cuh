@@ -1,0 +1,73 @@
+// Host-side handle of the GPU dynamics core: device memory pool, per-state field
+// sets (mirroring state_type, src/dynamics/state_mod.F90:17-101), launch helpers.
+#pragma once
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+#include "../../include/gmcore_gpu.h"
+#include "common.cuh"
+
+struct DState {
+  // prognostic + filtered copies
+  double *u = 0, *v = 0, *gz = 0, *u_f = 0, *v_f = 0, *gz_f = 0, *pt = 0, *phs = 0, *phs_f = 0;
+  // derived, kept per time level because stale copies are consumed
+  double *m = 0, *mfx_lon = 0, *mfy_lat = 0, *u_lat = 0, *v_lon = 0, *ke = 0, *pv = 0, *pv_lon = 0, *pv_lat = 0, *div = 0;
+  // hydrostatic core
+  double *ph_lev = 0, *ph_exn_lev = 0, *t = 0, *gz_lev = 0, *we_lev = 0, *m_lev = 0;
+  std::map<std::string, std::pair<double*, int>> names;   // name -> (ptr, kind) kind: 0 full-lat 3D, 1 half-lat 3D, 2 full-lat half-lev, 3 2-D
+};
+
+struct gmc_handle {
+  gmc_config cfg;
+  Geo g;
+  DMesh M;
+  DFilter filt[3];
+  cudaStream_t stream = 0;
+  char err[512] = {0};
+  long long launches = 0;
+  std::vector<void*> allocs;
+  DState st[4];
+  double *du = 0, *dv = 0;            // forward-pass tendencies (tend_type%du/dv)
+  double *gzs = 0;                    // static%gzs (2-D)
+  double *pole_dmf = 0;               // [2][nlev]
+  double *diag_partial = 0, *diag_out = 0;
+  double *stage_img = 0; size_t stage_bytes = 0;
+  // hydrostatic work arrays (allocated only when baroclinic)
+  double *wedudlev = 0, *wedvdlev = 0, *dphs = 0;
+  double *cflx = 0, *cfly = 0, *cflz = 0, *divx = 0, *divy = 0;   // adv_batch_mass
+  double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
+  double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)
+  double *pole_work = 0;
+  // tracer batch
+  double *q[2] = {0, 0}, *old_m = 0, *bu = 0, *bv = 0, *bmfx = 0, *bmfy = 0, *bwe = 0, *bm_lev = 0;
+  double *bcflx = 0, *bcfly = 0, *bcflz = 0, *bdivx = 0, *bdivy = 0, *lon_damp_wgt = 0;
+  int q_old = 0, q_new = 1, uv_step = 0, mf_step = 0, we_step = 0, nstep = 1;
+  double alert_last = 0, alert_period = 0; bool alert_ring = false;
+  bool mesh_set = false, filters_set[3] = {false, false, false};
+  int max_hn = 0;
+};
+
+#define LAUNCH(h, kern, grid, block, smem, ...) do { \
+  kern<<<grid, block, smem, (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
+
+template <typename T>
+static int dev_alloc(gmc_handle* h, T** p, size_t n) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, n * sizeof(T));
+  if (e != cudaSuccess) { snprintf(h->err, sizeof(h->err), "cudaMalloc(%zu B): %s", n * sizeof(T), cudaGetErrorString(e)); return 1; }
+  e = cudaMemset(q, 0, n * sizeof(T));
+  if (e != cudaSuccess) { snprintf(h->err, sizeof(h->err), "cudaMemset: %s", cudaGetErrorString(e)); return 1; }
+  h->allocs.push_back(q);
+  *p = (T*)q;
+  return 0;
+}
+template <typename T>
+static int dev_upload(gmc_handle* h, const T** dst, const T* src, size_t n) {
+  T* p = nullptr;
+  if (dev_alloc(h, &p, n)) return 1;
+  cudaError_t e = cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { snprintf(h->err, sizeof(h->err), "cudaMemcpy H2D: %s", cudaGetErrorString(e)); return 1; }
+  *dst = p;
+  return 0;
+}

@@ -1,0 +1,184 @@
+// State-update kernels: zonal polar filters, pressure-gradient force + u,v update,
+// global diagnostics, host<->device layout conversion.
+#pragma once
+#include "kernels_dyn.cuh"
+
+// ---- zonal Gaussian filter (src/dynamics/filter_mod.F90:25-163) -------------------
+// One block per (latitude row, level).  The row is staged once in shared memory with
+// its periodic wrap, then up to two filters are applied to it (update_state applies
+// big_filter and a small filter back to back to the same raw row,
+// time_schemes_mod.F90:186-190,216-236).  Taps are accumulated left to right exactly
+// as sum(wgt(:n) * x(i-hn:i+hn)) so results are bit-identical to the CPU order.
+enum { POST_NONE = 0, POST_SWM_M = 1, POST_DIV_M = 2 };
+struct FilterArgs {
+  const double* in;
+  int half_lat;                 // rows are half-lat rows (filter_on_lat_edge) or full-lat
+  int nlev;
+  DFilter f1; double* out1;     // out1 = f1(in)          (may be NULL)
+  DFilter f2; double* out2;     // out2 = post(f2(in))    (may be NULL, may alias in)
+  int use_f1, use_f2;           // 0: plain copy for that output
+  int post; const double* gzs; double grav; const double* mdiv; double* out_m;
+};
+__global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
+  extern __shared__ double srow[];
+  const int j = (a.half_lat ? g.hjb : g.jb) + blockIdx.x, k = blockIdx.y;
+  if (a.half_lat ? (j > g.hje) : (j > g.je)) return;
+  const int n1 = a.use_f1 ? (a.half_lat ? a.f1.ngrid_lat[j + 1] : a.f1.ngrid_lon[j + 1]) : 0;
+  const int n2 = a.use_f2 ? (a.half_lat ? a.f2.ngrid_lat[j + 1] : a.f2.ngrid_lon[j + 1]) : 0;
+  const int hn1 = n1 > 1 ? (n1 - 1) / 2 : 0, hn2 = n2 > 1 ? (n2 - 1) / 2 : 0;
+  const int hn = hn1 > hn2 ? hn1 : hn2;
+  const double* __restrict__ row = a.in + gidx(g, 0, j, k);
+  const int nlon = g.nlon;
+  for (int x = threadIdx.x; x < nlon + 2 * hn; x += blockDim.x) {
+    int i = x - hn; i = i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
+    srow[x] = row[i];
+  }
+  __syncthreads();
+  const double* __restrict__ w1 = a.half_lat ? a.f1.wgt_lat + (size_t)(j + 1) * a.f1.ld_lat : a.f1.wgt_lon + (size_t)(j + 1) * a.f1.ld_lon;
+  const double* __restrict__ w2 = a.half_lat ? a.f2.wgt_lat + (size_t)(j + 1) * a.f2.ld_lat : a.f2.wgt_lon + (size_t)(j + 1) * a.f2.ld_lon;
+  const long long base = gidx(g, 0, j, k);
+  for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
+    if (a.out1) {
+      double s;
+      if (n1 > 1) { s = 0; const double* x = srow + (i + hn - hn1); for (int t = 0; t < n1; ++t) s += __ldg(w1 + t) * x[t]; }
+      else s = srow[i + hn];
+      a.out1[base + i] = s;
+    }
+    if (a.out2 || a.out_m) {
+      double s;
+      if (n2 > 1) { s = 0; const double* x = srow + (i + hn - hn2); for (int t = 0; t < n2; ++t) s += __ldg(w2 + t) * x[t]; }
+      else s = srow[i + hn];
+      if (a.post == POST_DIV_M) s = s / __ldg(a.mdiv + base + i);
+      if (a.out2) a.out2[base + i] = s;
+      if (a.post == POST_SWM_M) a.out_m[base + i] = (s - __ldg(a.gzs + gidx(g, i, j, 0))) / a.grav;
+    }
+  }
+}
+
+// ---- backward pass: PGF + du,dv + u,v update (gmcore_mod.F90:529-571,
+// pgf_swm_mod.F90:18-46, pgf_lin97_mod.F90:57-102, time_schemes_mod.F90:198-233) ------
+struct UvArgs {
+  const double *gz_f;                 // shallow water
+  const double *ph_exn_lev, *gz_lev;  // hydrostatic (half-level arrays)
+  const double *du_fwd, *dv_fwd, *u_old, *v_old;
+  double *u_new, *v_new;
+  double dt; int swm; int blend;      // blend: apply the pole-adjacent v blend here (no small_filter2 in between)
+};
+__device__ __forceinline__ double pgf_lat_at(const Geo& g, const DMesh& M, const UvArgs& a, int i, int j, int k) {
+  if (a.swm) return (ldW(a.gz_f, g, i, j + 1, k) - ldW(a.gz_f, g, i, j, k)) / MJ(M.de_lat, j);
+  const double dph1 = ldW(a.ph_exn_lev, g, i, j + 1, k + 1) - ldW(a.ph_exn_lev, g, i, j, k);
+  const double dph2 = ldW(a.ph_exn_lev, g, i, j, k + 1) - ldW(a.ph_exn_lev, g, i, j + 1, k);
+  const double dgz1 = ldW(a.gz_lev, g, i, j, k + 1) - ldW(a.gz_lev, g, i, j + 1, k);
+  const double dgz2 = ldW(a.gz_lev, g, i, j, k) - ldW(a.gz_lev, g, i, j + 1, k + 1);
+  return -(dph1 * dgz1 + dph2 * dgz2) / MJ(M.de_lat, j) / (dph1 + dph2);
+}
+__device__ __forceinline__ double v_raw_at(const Geo& g, const DMesh& M, const UvArgs& a, int i, int j, int k) {
+  const long long c = gidx(g, i, j, k);
+  const double dv = __ldg(a.dv_fwd + c) - pgf_lat_at(g, M, a, i, j, k);
+  return __ldg(a.v_old + c) + a.dt * dv;
+}
+__global__ void __launch_bounds__(128) k_uv_update(Geo g, DMesh M, UvArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  if (j > 1 && j < g.nlat) {
+    double pgf;
+    if (a.swm) pgf = (ldW(a.gz_f, g, i + 1, j, k) - __ldg(a.gz_f + c)) / MJ(M.de_lon, j);
+    else {
+      const double dph1 = ldW(a.ph_exn_lev, g, i + 1, j, k + 1) - ldW(a.ph_exn_lev, g, i, j, k);
+      const double dph2 = ldW(a.ph_exn_lev, g, i, j, k + 1) - ldW(a.ph_exn_lev, g, i + 1, j, k);
+      const double dgz1 = ldW(a.gz_lev, g, i, j, k + 1) - ldW(a.gz_lev, g, i + 1, j, k);
+      const double dgz2 = ldW(a.gz_lev, g, i, j, k) - ldW(a.gz_lev, g, i + 1, j, k + 1);
+      pgf = -(dph1 * dgz1 + dph2 * dgz2) / MJ(M.de_lon, j) / (dph1 + dph2);
+    }
+    const double du = __ldg(a.du_fwd + c) - pgf;
+    a.u_new[c] = __ldg(a.u_old + c) + a.dt * du;
+  }
+  if (j <= g.nhalf) {
+    double v = v_raw_at(g, M, a, i, j, k);
+    if (a.blend) {
+      const double wgt = 0.6;
+      if (j == 1) v = (1 - wgt) * v + wgt * v_raw_at(g, M, a, i, j + 1, k);
+      else if (j == g.nhalf) v = (1 - wgt) * v + wgt * v_raw_at(g, M, a, i, j - 1, k);
+    }
+    a.v_new[c] = v;
+  }
+}
+// Pole-adjacent v blend as a separate pass (hydrostatic core: it follows small_filter2;
+// time_schemes_mod.F90:225-233).  Rows 1 and nhalf only; north uses the final j-1 row.
+__global__ void k_v_pole_blend(Geo g, double* v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y, north = blockIdx.z;
+  if (i >= g.nlon) return;
+  if ((north && !g.has_north) || (!north && !g.has_south)) return;
+  const double wgt = 0.6;
+  const int j = north ? g.nhalf : 1, jn = north ? j - 1 : j + 1;
+  v[gidx(g, i, j, k)] = (1 - wgt) * v[gidx(g, i, j, k)] + wgt * v[gidx(g, i, jn, k)];
+}
+
+// ---- diagnose (gmcore_mod.F90:213-341) ----------------------------------------------
+// Stage 1: one block per (row, level) -> 7 partial sums; stage 2: one block folds
+// them in a fixed order (deterministic run to run).
+struct DiagArgs {
+  const double *m, *mfx_lon, *mfy_lat, *u_lon, *v_lat, *pv, *pv_lon, *pv_lat, *t, *pt, *phs, *gzs;
+  double* partial;   // [7][nrows*nlev]
+  double grav, cpd; int baroclinic;
+};
+__global__ void __launch_bounds__(256) k_diag_partial(Geo g, DMesh M, DiagArgs a) {
+  __shared__ double sm[32];
+  const int j = g.jb + blockIdx.x, k = blockIdx.y;
+  const int nrows = g.je - g.jb + 1;
+  double tm = 0, ke = 0, ie = 0, pe = 0, av = 0, tpe = 0, tpt = 0;
+  const bool nopole = j > 1 && j < g.nlat, half = j <= g.nhalf;
+  for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) {
+    const long long c = gidx(g, i, j, k);
+    const double m = __ldg(a.m + c);
+    tm += m * MJ(M.area_cell, j);
+    if (nopole) {
+      ke += __ldg(a.mfx_lon + c) * 0.5 * __ldg(a.u_lon + c) * MJ(M.area_lon, j) * 2;
+      const double pl = __ldg(a.pv_lon + c);
+      tpe += m_lon_at(a.m, g, i, j, k) * (pl * pl) * 0.5 * MJ(M.area_lon, j);
+    }
+    if (half) {
+      ke += __ldg(a.mfy_lat + c) * 0.5 * __ldg(a.v_lat + c) * MJ(M.area_lat, j) * 2;
+      av += __ldg(a.pv + c) * MJ(M.area_vtx, j);
+      const double pl = __ldg(a.pv_lat + c);
+      tpe += m_lat_at(a.m, g, i, j, k) * (pl * pl) * 0.5 * MJ(M.area_lat, j);
+    }
+    if (a.baroclinic) {
+      ie += m * a.cpd * __ldg(a.t + c) * MJ(M.area_cell, j);
+      tpt += m * __ldg(a.pt + c) * MJ(M.area_cell, j);
+      if (k == 0) pe += __ldg(a.gzs + gidx(g, i, j, 0)) * __ldg(a.phs + gidx(g, i, j, 0)) * MJ(M.area_cell, j);
+    } else {
+      pe += (m * m * a.grav * 0.5 + m * __ldg(a.gzs + gidx(g, i, j, 0))) * MJ(M.area_cell, j);
+    }
+  }
+  const int slot = blockIdx.y * nrows + blockIdx.x, ns = nrows * g.nlev;
+  double v[7] = {tm, ke, ie, pe, av, tpe, tpt};
+  for (int q = 0; q < 7; ++q) {
+    const double s = block_sum(v[q], sm);
+    if (threadIdx.x == 0) a.partial[(size_t)q * ns + slot] = s;
+  }
+}
+__global__ void __launch_bounds__(1024) k_diag_final(const double* partial, int ns, double* out /*[7]*/) {
+  __shared__ double sm[32];
+  for (int q = 0; q < 7; ++q) {
+    double s = 0;
+    for (int x = threadIdx.x; x < ns; x += blockDim.x) s += partial[(size_t)q * ns + x];
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) out[q] = s;
+  }
+}
+
+// ---- host (halo'd Fortran storage) <-> device (compact) layout conversion --------------
+// dir 0: staged host image -> device field; dir 1: device field -> staged image.
+struct PackArgs { double* dev; double* img; int hx, hy, nx, ny, klev0, nk, nrows, jfirst; };
+__global__ void k_pack(Geo g, PackArgs a, int dir) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const int j = a.jfirst + r;   // global row
+  const long long d = gidx(g, i, j, k);
+  const long long s = (long long)(i + a.hx) + (long long)a.nx * ((long long)(j - g.jb + a.hy) + (long long)a.ny * (k + a.klev0));
+  if (dir == 0) a.dev[d] = a.img[s]; else a.img[s] = a.dev[d];
+}

@@ -1,0 +1,30 @@
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    # host + oracle libraries are CPU code; build them if the in-tree copies are missing
+    need = [os.path.join(ROOT, "gmcore_b200/lib/libgmcore_host.so"), os.path.join(ROOT, "oracle/_build/liboracle.so")]
+    if not all(os.path.exists(p) for p in need):
+        subprocess.check_call(["make", "-C", ROOT, "host", "oracle"], stdout=subprocess.DEVNULL)
+
+
+def has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.fixture(scope="session")
+def gpu_required():
+    if not has_gpu():
+        pytest.skip("no CUDA device")
