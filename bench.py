@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py — simulated days per wall-clock day of the GMCORE dynamics hot path on B200.
+
+Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` prints ONE
+JSON line (rank 0).  A "step" is one model time step (time_integrate + time_advance +
+diagnose, gmcore_mod.F90:138-144) of the named workload on synthetic (analytic) input.
+
+  value     device-resident throughput (state already in HBM), CUDA events on the
+            library's stream, max over ranks
+  e2e       the same job through the C ABI from HOST buffers: gmc_upload_state from
+            pinned memory + gmc_prepare_run + K x (gmc_time_integrate + gmc_diagnose,
+            a 64-byte D2H read per step) + gmc_download_state, wall clock around it
+  roofline  dominant kernel: algorithmic bytes per launch / mean launch duration
+            (per-launch CUDA events inside the library, gmc_profile) vs the measured
+            HBM copy bandwidth in MEASURED_PEAKS.json
+  cpu_baseline  the CPU restatement (oracle/, "port") timed on the host cores on a
+            bounded sample of the same workload
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # Williamson 5 at 0.5 deg, shallow water
+    "swm_mz_720x360": dict(nlon=720, nlat=360, nlev=1, dt=75.0, case="mountain_zonal_flow", bytes_per_cell=936),
+    # Jablonowski-Williamson baroclinic wave, hydrostatic, 1 FFSL tracer (qv)
+    "bw_360x180x32": dict(nlon=360, nlat=180, nlev=32, dt=150.0, case="baroclinic_wave", bytes_per_cell=2320),
+    "bw_1440x720x32": dict(nlon=1440, nlat=720, nlev=32, dt=30.0, case="baroclinic_wave", bytes_per_cell=2320),
+}
+DEFAULT_WORKLOAD = "swm_mz_720x360"
+
+# Algorithmic 3-D r8 array passes per launch of each kernel (SURVEY.md §8d / DESIGN.md):
+# reads + writes of full 3-D fields; 2-D fields and coefficient vectors ignored.
+KERNEL_PASSES = {
+    "k_fwd1": 3 + 7, "k_pv_edge": 5 + 2, "k_tend": 5 + 3, "k_uv_update": 5 + 2, "k_filter_rows": None,
+    "k_diag_partial": 8,
+}
+L2_BYTES = 126e6
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(n_gpus):
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def max_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def pinned_like(a):
+    import torch
+    t = torch.empty(a.shape, dtype=torch.float64, pin_memory=True)
+    n = t.numpy(); n[...] = a
+    return n, t
+
+
+def cpu_baseline(wl, name, budget_s=20.0):
+    """Time the CPU restatement (oracle, -O3 -march=native build) on a bounded sample."""
+    from gmcore_b200.host import Host
+    from oracle.orc import Oracle
+    host = Host(wl["nlon"], wl["nlat"], wl["nlev"], wl["dt"], wl["case"])
+    ic = host.initial_condition()
+    orc = Oracle(host, fast=True)
+    orc.set_state(ic)
+    if host.cfg.ntracers:
+        orc.set_tracers(np.zeros((host.cfg.ntracers,) + host.shape("cell")))
+    orc.prepare_run()
+    t0 = time.perf_counter(); orc.run_steps(1); t1 = time.perf_counter() - t0
+    n = int(max(1, min(200, budget_s / max(t1, 1e-6))))
+    t0 = time.perf_counter(); orc.run_steps(n); el = time.perf_counter() - t0
+    sdpd = n * wl["dt"] / el
+    cores = int(os.environ.get("OMP_NUM_THREADS", "0")) or 1
+    return {"value": sdpd, "unit": "simulated days/day", "cores": orc_threads(), "kind": "port",
+            "sample": f"{n} steps of {name} after 1 warm-up step ({el:.1f} s wall)", "s_per_step": el / n}
+
+
+def orc_threads():
+    try:
+        import ctypes
+        lib = ctypes.CDLL(os.path.join(ROOT, "oracle/_build/liboracle_fast.so"))
+        return int(lib.orc_num_threads())
+    except Exception:
+        return 1
+
+
+def run_reference(args, name, wl, rank, world):
+    if rank != 0:
+        return
+    t0 = time.perf_counter()
+    cb = cpu_baseline(wl, name, budget_s=max(5.0, 6.0 * (args.steps + args.warmup)))
+    line = {"impl": "reference", "metric": "simulated days per wall-clock day", "value": cb["value"], "unit": "simulated days/day",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["s_per_step"] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")}},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": "simulated days/day", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "wall_s": time.perf_counter() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default=os.environ.get("GMCORE_WORKLOAD", DEFAULT_WORKLOAD))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    name = args.workload; wl = WORKLOADS[name]
+    K, W = args.steps, max(3, args.warmup)
+
+    if args.impl == "reference":
+        rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+        run_reference(args, name, wl, rank, world)
+        return
+
+    rank, world, local = dist_setup(args.gpus)
+    import torch
+    from gmcore_b200.host import Host
+    from gmcore_b200.model import GmcoreGPU
+
+    host = Host(wl["nlon"], wl["nlat"], wl["nlev"], wl["dt"], wl["case"])
+    ic = host.initial_condition()
+    gpu = GmcoreGPU(host, device=local)
+    gpu.set_state(ic)
+    q0 = None
+    if host.cfg.ntracers:
+        q0 = np.zeros((host.cfg.ntracers,) + host.shape("cell"))
+        gpu.set_tracers(q0)
+    gpu.prepare_run()
+    gpu.run_steps(W, diag=True)
+    gpu.synchronize()
+
+    n3 = wl["nlon"] * wl["nlat"] * wl["nlev"]
+    working_set = 40 * n3 * 8
+    flush = working_set < 2 * L2_BYTES
+    flush_buf = torch.empty(int(2 * L2_BYTES) // 8, dtype=torch.float64, device=f"cuda:{local}") if flush else None
+
+    # ---- device-resident timed region: exactly K steps --------------------------------
+    clocks = ClockSampler(local); clocks.start()
+    barrier(world); torch.cuda.synchronize()
+    l0 = gpu.launches
+    if flush:
+        ms = 0.0
+        for _ in range(K):
+            flush_buf.fill_(1.0); torch.cuda.synchronize()
+            gpu.timer_start(); gpu.run_steps(1, diag=True); ms += gpu.timer_stop_ms()
+    else:
+        gpu.timer_start(); gpu.run_steps(K, diag=True); ms = gpu.timer_stop_ms()
+    torch.cuda.synchronize(); barrier(world)
+    launches = gpu.launches - l0
+    clk = clocks.stop()
+    ms = max_over_ranks(ms, world)
+    value = world * K * wl["dt"] / (ms / 1e3)     # replicas: every rank integrates the same K steps
+
+    # ---- per-kernel CUDA-event pass (same K steps, profiling on) -------------------------
+    gpu.profile(True); gpu.run_steps(K, diag=True); rep = gpu.profile_report(); gpu.profile(False)
+    tot = sum(v[1] for v in rep.values())
+    top = max(rep.items(), key=lambda kv: kv[1][1])
+    peak, peak_src = measured_peak_gbs()
+    passes = KERNEL_PASSES.get(top[0])
+    mean_ms = top[1][1] / top[1][0]
+    achieved = (passes * 8 * n3 / (mean_ms * 1e-3) / 1e9) if passes else None
+    step_gbs = wl["bytes_per_cell"] * n3 / (ms / K * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": top[0], "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "kernel_share_of_step": top[1][1] / tot, "kernel_mean_ms": mean_ms,
+                "whole_step_algorithmic_gbs": step_gbs, "whole_step_frac": step_gbs / peak,
+                "kernels_ms_per_step": {k: v[1] / K for k, v in sorted(rep.items(), key=lambda kv: -kv[1][1])}}
+
+    # ---- end to end through the C ABI from pinned host buffers ------------------------------
+    pin = {k: pinned_like(v) for k, v in ic.items() if v is not None}
+    gpu2 = GmcoreGPU(host, device=local)
+    icp = {k: pin[k][0] if k in pin else None for k in ic}
+    h2d = sum(pin[k][0].nbytes for k in pin)
+    out = {"u_lon": pinned_like(ic["u_lon"]), "v_lat": pinned_like(ic["v_lat"]), "s": pinned_like(ic["pt_or_gz"])}
+    barrier(world); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    gpu2.set_state(icp)
+    if q0 is not None:
+        gpu2.set_tracers(q0); h2d += q0.nbytes
+    gpu2.prepare_run()
+    for _ in range(K):
+        gpu2.time_integrate()
+        gpu2.diagnose()
+    st = gpu2.download_state()
+    gpu2.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    d2h = sum(v.nbytes for v in st.values() if v is not None)
+    e2e = {"value": world * K * wl["dt"] / e2e_s, "unit": "simulated days/day",
+           "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K + 64,
+           "region": "upload_state(pinned)+prepare_run+K*(time_integrate+diagnose D2H)+download_state"}
+    gpu2.close()
+
+    if rank == 0:
+        cb = None
+        if not args.no_cpu_baseline:
+            cb = cpu_baseline(wl, name)
+            cb.pop("s_per_step")
+        line = {"metric": "simulated days per wall-clock day", "value": value, "unit": "simulated days/day", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+                "scaling": "weak" if world > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")},
+                           "time_scheme": "wrfrk3", "hx": host.hx, "parallelism": f"replicas x{world}" if world > 1 else "1 GPU",
+                           "l2": "flushed between timed steps (256 MB write)" if flush else "working set >> L2 (no flush)"},
+                "gpu_launches": launches, "clocks": clk, "e2e": e2e, "roofline": roofline, "cpu_baseline": cb}
+        print(json.dumps(line), flush=True)
+    gpu.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

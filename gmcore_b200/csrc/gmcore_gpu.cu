@@ -1,6 +1,7 @@
 // libgmcore_b200.so — C ABI of include/gmcore_gpu.h: the GMCORE dynamics hot path
 // (time_integrate and the pre-loop of gmcore_run) as sm_100a CUDA kernels.
 // There is no CPU fallback: every entry point fails if no CUDA device is usable.
+#include <algorithm>
 #include "handle.cuh"
 #include "kernels_dyn.cuh"
 #include "kernels_update.cuh"
@@ -218,6 +219,42 @@ int gmc_synchronize(gmc_handle* h) {
   return 0;
 }
 int gmc_launch_count(gmc_handle* h, long long* launches) { *launches = h->launches; return 0; }
+// Timing helpers (CUDA events on the handle's stream; torch.cuda.Event only sees
+// torch's current stream).  slot 0 = start, 1 = stop.
+int gmc_timer_record(gmc_handle* h, int slot) {
+  if (!h->tev[slot]) CUDA_CHECK(cudaEventCreate(&h->tev[slot]));
+  CUDA_CHECK(cudaEventRecord(h->tev[slot], h->stream));
+  return 0;
+}
+int gmc_timer_elapsed_ms(gmc_handle* h, double* ms) {
+  CUDA_CHECK(cudaEventSynchronize(h->tev[1]));
+  float f = 0; CUDA_CHECK(cudaEventElapsedTime(&f, h->tev[0], h->tev[1]));
+  *ms = f; return 0;
+}
+int gmc_profile(gmc_handle* h, int on) {
+  h->prof.on = on != 0;
+  if (on) { h->prof.entries.clear(); h->prof.used = 0; }
+  return 0;
+}
+// Text report "name count total_ms\n" per kernel, sorted by total time.
+int gmc_profile_report(gmc_handle* h, char* buf, int len) {
+  CUDA_CHECK(cudaStreamSynchronize(h->stream));
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto& e : h->prof.entries) {
+    float ms = 0; cudaEventElapsedTime(&ms, e.e0, e.e1);
+    auto& a = agg[e.name]; a.first++; a.second += ms;
+  }
+  std::vector<std::pair<double, std::string>> order;
+  for (auto& kv : agg) order.push_back({-kv.second.second, kv.first});
+  std::sort(order.begin(), order.end());
+  int off = 0;
+  for (auto& o : order) {
+    auto& a = agg[o.second];
+    off += snprintf(buf + off, off < len ? len - off : 0, "%s %lld %.6f\n", o.second.c_str(), a.first, a.second);
+    if (off >= len) break;
+  }
+  return 0;
+}
 void* gmc_stream(gmc_handle* h) { return (void*)h->stream; }
 int gmc_struct_sizes(int* cfg, int* mv) { *cfg = (int)sizeof(gmc_config); *mv = (int)sizeof(gmc_mesh_vectors); return 0; }
 

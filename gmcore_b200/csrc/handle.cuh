@@ -18,6 +18,25 @@ struct DState {
   std::map<std::string, std::pair<double*, int>> names;   // name -> (ptr, kind) kind: 0 full-lat 3D, 1 half-lat 3D, 2 full-lat half-lev, 3 2-D
 };
 
+// Every kernel goes through LAUNCH: it counts launches and, in profiling mode
+// (gmc_profile), brackets the launch with CUDA events on the launching stream.
+struct ProfEntry { const char* name; cudaEvent_t e0, e1; };
+struct Profiler {
+  bool on = false;
+  std::vector<ProfEntry> entries;
+  std::vector<cudaEvent_t> pool; size_t used = 0;
+  cudaEvent_t get() {
+    if (used == pool.size()) { cudaEvent_t e; cudaEventCreate(&e); pool.push_back(e); }
+    return pool[used++];
+  }
+};
+#define LAUNCH(h, kern, grid, block, smem, ...) do { \
+  ProfEntry pe_{#kern, 0, 0}; \
+  if ((h)->prof.on) { pe_.e0 = (h)->prof.get(); cudaEventRecord(pe_.e0, (h)->stream); } \
+  kern<<<grid, block, smem, (h)->stream>>>(__VA_ARGS__); (h)->launches++; \
+  if ((h)->prof.on) { pe_.e1 = (h)->prof.get(); cudaEventRecord(pe_.e1, (h)->stream); (h)->prof.entries.push_back(pe_); } \
+} while (0)
+
 struct gmc_handle {
   gmc_config cfg;
   Geo g;
@@ -26,6 +45,8 @@ struct gmc_handle {
   cudaStream_t stream = 0;
   char err[512] = {0};
   long long launches = 0;
+  Profiler prof;
+  cudaEvent_t tev[2] = {0, 0};
   std::vector<void*> allocs;
   DState st[4];
   double *du = 0, *dv = 0;            // forward-pass tendencies (tend_type%du/dv)
@@ -48,8 +69,6 @@ struct gmc_handle {
   int max_hn = 0;
 };
 
-#define LAUNCH(h, kern, grid, block, smem, ...) do { \
-  kern<<<grid, block, smem, (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
 
 template <typename T>
 static int dev_alloc(gmc_handle* h, T** p, size_t n) {

@@ -50,6 +50,10 @@ def load_library():
     lib.gmc_launch_count.argtypes = [V, C.POINTER(C.c_longlong)]
     lib.gmc_last_error.argtypes = [V, C.c_char_p, C.c_int]
     lib.gmc_struct_sizes.argtypes = [I, I]
+    lib.gmc_timer_record.argtypes = [V, C.c_int]
+    lib.gmc_timer_elapsed_ms.argtypes = [V, P]
+    lib.gmc_profile.argtypes = [V, C.c_int]
+    lib.gmc_profile_report.argtypes = [V, C.c_char_p, C.c_int]
     lib.gmc_stream.restype = C.c_void_p
     lib.gmc_stream.argtypes = [V]
     _LIB = lib
@@ -131,6 +135,28 @@ class GmcoreGPU:
         n = C.c_longlong()
         self.lib.gmc_launch_count(self.h, C.byref(n))
         return n.value
+
+    def timer_start(self):
+        self._chk(self.lib.gmc_timer_record(self.h, 0))
+
+    def timer_stop_ms(self):
+        self._chk(self.lib.gmc_timer_record(self.h, 1))
+        ms = C.c_double()
+        self._chk(self.lib.gmc_timer_elapsed_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def profile(self, on):
+        self._chk(self.lib.gmc_profile(self.h, int(on)))
+
+    def profile_report(self):
+        """{kernel: (launches, total_ms)} for the launches since profile(True)."""
+        buf = C.create_string_buffer(1 << 16)
+        self._chk(self.lib.gmc_profile_report(self.h, buf, len(buf)))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            n, c, ms = line.split()
+            out[n] = (int(c), float(ms))
+        return out
 
     @property
     def stream(self):

@@ -4,6 +4,9 @@
 #include "orc_model.hpp"
 #include "orc_forcing.hpp"
 #include <map>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 using namespace orc;
 
@@ -137,6 +140,13 @@ int orc_field_shape(void* h, int itime, const char* name, int* shape /*ni,nj,nk,
   return 0;
 }
 // Run one named operator on state(itime) for operator-level parity tests.
+int orc_num_threads() {
+#if defined(_OPENMP) && defined(ORC_OPENMP_LOOPS)
+  return omp_get_max_threads();
+#else
+  return 1;   // the restatement's loops are scalar (no OpenMP pragmas yet)
+#endif
+}
 int orc_last_error(void* h, char* buf, int len) {
   Model* m = (Model*)h;
   std::snprintf(buf, len, "%s", m->b.error.c_str());
