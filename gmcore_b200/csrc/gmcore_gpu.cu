@@ -6,6 +6,7 @@
 #include "kernels_dyn.cuh"
 #include "kernels_update.cuh"
 #include "kernels_hydro.cuh"
+extern "C" { static int xfer(gmc_handle* h, double* dev, double* host, int kind, int dir); }
 #include "steps.cuh"
 
 extern "C" {
@@ -57,7 +58,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
     if (!baro) { A("gz", &S.gz, n3, 0); A("gz_f", &S.gz_f, n3, 0); }
     else {
       A("pt", &S.pt, n3, 0); A("phs", &S.phs, n2, 3); A("phs_f", &S.phs_f, n2, 3);
-      A("ph_lev", &S.ph_lev, n3h, 2); A("ph_exn_lev", &S.ph_exn_lev, n3h, 2); A("t", &S.t, n3, 0);
+      A("ph_exn_lev", &S.ph_exn_lev, n3h, 2); A("t", &S.t, n3, 0);
       A("gz_lev", &S.gz_lev, n3h, 2); A("we_lev", &S.we_lev, n3h, 2); A("m_lev", &S.m_lev, n3h, 2);
     }
   }

@@ -55,7 +55,7 @@ struct gmc_handle {
   double *diag_partial = 0, *diag_out = 0;
   double *stage_img = 0; size_t stage_bytes = 0;
   // hydrostatic work arrays (allocated only when baroclinic)
-  double *wedudlev = 0, *wedvdlev = 0, *dphs = 0;
+  double *dphs = 0; int* dflags = 0;   // dflags: device word of the reference's log_error guards
   double *cflx = 0, *cfly = 0, *cflz = 0, *divx = 0, *divy = 0;   // adv_batch_mass
   double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
   double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)

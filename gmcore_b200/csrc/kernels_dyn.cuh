@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(128) k_pv_edge(Geo g, PvEdgeArgs a) {
 // (time_schemes_mod.F90:179-185).
 struct TendArgs {
   const double *mfx_lon, *mfy_lat, *pv_lon, *pv_lat, *ke, *u_lat_unused;
-  const double *wedudlev, *wedvdlev;      // NULL for shallow water
+  const double *we_lev, *u_f, *v_f, *m;   // hydrostatic: vertical advection of u, v formed inline; NULL for shallow water
   double *du, *dv;
   // shallow water only
   const double *gz_old, *pole_dmf; double *gz_new; double dt, grav;
@@ -216,7 +216,26 @@ __global__ void __launch_bounds__(128) k_tend(Geo g, DMesh M, TendArgs a) {
     const double ke0 = __ldg(a.ke + c);
     const double dkedlon = (ldW(a.ke, g, i + 1, j, k) - ke0) / MJ(M.de_lon, j);
     double du = qhv - dkedlon;
-    if (a.wedudlev) du = du - __ldg(a.wedudlev + c);
+    if (a.we_lev) {
+      // calc_wedudlev_wedvdlev (:1145-1180) with we_lev_lon from interp_mod.F90:361-369
+      const int kb = 0, ke = g.nlev - 1;
+      const double aw = MJ(M.area_lon_west, j), ae = MJ(M.area_lon_east, j), al = MJ(M.area_lon, j);
+      const double mlon = m_lon_at(a.m, g, i, j, k);
+      const double u0 = __ldg(a.u_f + c);
+      double w;
+      if (k > kb && k < ke) {
+        const double wl1 = (aw * ldW(a.we_lev, g, i, j, k + 1) + ae * ldW(a.we_lev, g, i + 1, j, k + 1)) / al;
+        const double wl0 = (aw * ldW(a.we_lev, g, i, j, k) + ae * ldW(a.we_lev, g, i + 1, j, k)) / al;
+        w = (wl1 * (ldW(a.u_f, g, i, j, k + 1) - u0) + wl0 * (u0 - ldW(a.u_f, g, i, j, k - 1))) / mlon / 2.0;
+      } else if (k == kb) {
+        const double wl1 = (aw * ldW(a.we_lev, g, i, j, k + 1) + ae * ldW(a.we_lev, g, i + 1, j, k + 1)) / al;
+        w = (wl1 * (ldW(a.u_f, g, i, j, k + 1) - u0)) / mlon / 2.0;
+      } else {
+        const double wl0 = (aw * ldW(a.we_lev, g, i, j, k) + ae * ldW(a.we_lev, g, i + 1, j, k)) / al;
+        w = (wl0 * (u0 - ldW(a.u_f, g, i, j, k - 1))) / mlon / 2.0;
+      }
+      du = du - w;
+    }
     a.du[c] = du;
     if (a.swm) {
       const double dmfdlon = (__ldg(a.mfx_lon + c) - ldW(a.mfx_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
@@ -240,7 +259,26 @@ __global__ void __launch_bounds__(128) k_tend(Geo g, DMesh M, TendArgs a) {
                         MJ2(M.half_tangent_wgt, 2, j) * (mx_c * (pt + pl_c) + mx_d * (pt + pl_d))) * 0.5;
     const double dkedlat = (ldW(a.ke, g, i, j + 1, k) - __ldg(a.ke + c)) / MJ(M.de_lat, j);
     double dv = -qhu - dkedlat;
-    if (a.wedvdlev) dv = dv - __ldg(a.wedvdlev + c);
+    if (a.we_lev) {
+      // :1181-1214 with we_lev_lat from interp_mod.F90:426-434
+      const int kb = 0, ke = g.nlev - 1;
+      const double an = MJ(M.area_lat_north, j), as = MJ(M.area_lat_south, j), al = MJ(M.area_lat, j);
+      const double mlat = m_lat_at(a.m, g, i, j, k);
+      const double v0 = __ldg(a.v_f + c);
+      double w;
+      if (k > kb && k < ke) {
+        const double wl1 = (an * ldW(a.we_lev, g, i, j + 1, k + 1) + as * ldW(a.we_lev, g, i, j, k + 1)) / al;
+        const double wl0 = (an * ldW(a.we_lev, g, i, j + 1, k) + as * ldW(a.we_lev, g, i, j, k)) / al;
+        w = (wl1 * (ldW(a.v_f, g, i, j, k + 1) - v0) + wl0 * (v0 - ldW(a.v_f, g, i, j, k - 1))) / mlat / 2.0;
+      } else if (k == kb) {
+        const double wl1 = (an * ldW(a.we_lev, g, i, j + 1, k + 1) + as * ldW(a.we_lev, g, i, j, k + 1)) / al;
+        w = (wl1 * (ldW(a.v_f, g, i, j, k + 1) - v0)) / mlat / 2.0;
+      } else {
+        const double wl0 = (an * ldW(a.we_lev, g, i, j + 1, k) + as * ldW(a.we_lev, g, i, j, k)) / al;
+        w = (wl0 * (v0 - ldW(a.v_f, g, i, j, k - 1))) / mlat / 2.0;
+      }
+      dv = dv - w;
+    }
     a.dv[c] = dv;
   }
 }

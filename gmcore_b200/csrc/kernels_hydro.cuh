@@ -1,12 +1,571 @@
-// Hydrostatic-core kernels (placeholder while the shallow-water path is validated).
+// Hydrostatic-core kernels: RK4 departure-point CFL, vertical mass flux, FFSL/PPM
+// advection (horizontal inner/outer + vertical), hydrostatic integration, damping,
+// Held-Suarez forcing, tracer batch.  References (GMCORE source tree):
+//   src/dynamics/adv/adv_batch_mod.F90:218-403,493-632
+//   src/dynamics/adv/ffsl_mod.F90:318-432,778-941,1147-1194
+//   src/dynamics/operators_mod.F90:136-232,433-543,1008-1216
+//   src/dynamics/damp/div_damp_mod.F90:27-139, lon_damp_mod.F90:43-68,158-241
+//   src/dynamics/adv/adv_mod.F90:152-312,420-455
 #pragma once
 #include "handle.cuh"
-static int hydro_alloc(gmc_handle* h) { snprintf(h->err, sizeof(h->err), "hydrostatic core not built yet"); return 1; }
-static int hydro_set_mesh(gmc_handle*, const gmc_mesh_vectors*) { return 0; }
-static bool hydro_work_field(gmc_handle*, const std::string&, double**, int*) { return false; }
-static void hydro_step(gmc_handle*, DState&, DState&, DState&, double) {}
-static void hydro_post_step(gmc_handle*, int, double, int) {}
-static void hydro_prepare_run(gmc_handle*, int) {}
-static int hydro_check_flags(gmc_handle*) { return 0; }
-static int hydro_set_tracers(gmc_handle* h, const double*) { snprintf(h->err, sizeof(h->err), "no tracers"); return 1; }
-static int hydro_get_tracers(gmc_handle* h, double*) { snprintf(h->err, sizeof(h->err), "no tracers"); return 1; }
+#include "kernels_dyn.cuh"
+
+// Vertical-coordinate constants (hybrid_coord_mod.F90:146-171), by value.
+struct VC { double ptop, p0h, p0, kappa, Rd; };
+
+__device__ __forceinline__ double ph_lev_at(const DMesh& M, const VC& vc, int k1 /*1-based half level*/, double phs) {
+  return M.hyai[k1 - 1] * (vc.p0h - vc.ptop) + M.hybi[k1 - 1] * (phs - vc.ptop) + vc.ptop;
+}
+
+__device__ __forceinline__ double fsign(double a, double b) { return copysign(fabs(a), b); }
+__device__ __forceinline__ double min3(double a, double b, double c) { return fmin(fmin(a, b), c); }
+__device__ __forceinline__ double max3(double a, double b, double c) { return fmax(fmax(a, b), c); }
+
+// ffsl_mod.F90:1183-1194 (limiter_type = 'mono')
+__device__ __forceinline__ double slope_mono(double fm1, double f, double fp1) {
+  const double df = (fp1 - fm1) * 0.5;
+  const double df_min = 2 * (f - min3(fm1, f, fp1));
+  const double df_max = 2 * (max3(fm1, f, fp1) - f);
+  return fsign(min3(fabs(df), df_min, df_max), df);
+}
+// ffsl_mod.F90:1147-1173
+__device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
+  const double dfl = slope_mono(fm2, fm1, f);
+  df = slope_mono(fm1, f, fp1);
+  const double dfr = slope_mono(f, fp1, fp2);
+  fl = 0.5 * (fm1 + f) + (dfl - df) / 6.0;
+  double fr = 0.5 * (fp1 + f) + (df - dfr) / 6.0;
+  fl = f - fsign(fmin(fabs(df), fabs(fl - f)), df);
+  fr = f + fsign(fmin(fabs(df), fabs(fr - f)), df);
+  f6 = 6 * f - 3 * (fl + fr);
+  df = fr - fl;
+}
+// The PPM flux integral shared by the three directions (ffsl_mod.F90:831-851).
+__device__ __forceinline__ double ppm_integral(double sm, double ml, double dm, double m6, double s1, double s2) {
+  const double ds1 = s2 - s1, ds2 = s2 * s2 - s1 * s1, ds3 = s2 * s2 * s2 - s1 * s1 * s1;
+  return sm + ml * ds1 + 0.5 * dm * ds2 + m6 * (ds2 / 2.0 - ds3 / 3.0);
+}
+
+// ---- RK4 departure-point CFL + divx/divy (adv_batch_mod.F90:253-373) ---------------
+struct CflArgs {
+  const double *u, *v;                 // batch%u, batch%v
+  double *cflx, *cfly, *divx, *divy;
+  double dt, radius; int* flags;
+};
+__global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  const int i1 = i + 1;                       // Fortran index
+  const double* __restrict__ hl = M.half_lon + (M.hx - 1);   // hl[l] = half_lon(l), l Fortran index
+  if (j > 1 && j < g.nlat) {
+    const double dx = MJ(M.de_lon, j), cl = MJ(M.full_cos_lat, j);
+    const double x0 = a.radius * hl[i1] * cl;
+    const double u1 = __ldg(a.u + c);
+    double x = x0 + a.dt / 2 * u1;
+    double us[3];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int l = (int)floor(i1 + (x - x0) / dx);
+      const double ua = ldW(a.u, g, wrapi(l - 1, g.nlon), j, k), ub = ldW(a.u, g, wrapi(l, g.nlon), j, k);
+      us[s] = ((a.radius * hl[l + 1] * cl - x) * ua + (x - a.radius * hl[l] * cl) * ub) / dx;
+      x = x0 + (s == 1 ? a.dt : a.dt / 2) * us[s];
+    }
+    const double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) / 6 * a.dt / dx;
+    a.cflx[c] = cf;
+    if (fabs(cf) > M.hx) atomicOr(a.flags, 1);
+    const double um = ldW(a.u, g, i - 1, j, k);
+    a.divx[c] = (u1 - um) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
+    a.divy[c] = (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+  }
+  if (j <= g.nhalf) {
+    const double dy = MJ(M.de_lat, j);
+    const double y0 = a.radius * MJ(M.half_lat, j);
+    const double v1 = __ldg(a.v + c);
+    double y = y0 + a.dt / 2 * v1;
+    double vs[3];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int l = (int)floor(j + (y - y0) / dy);
+      if (l < 1 || l > g.nhalf - 1) vs[s] = v1;
+      else vs[s] = ((a.radius * MJ(M.half_lat, l + 1) - y) * ldW(a.v, g, i, l, k) + (y - a.radius * MJ(M.half_lat, l)) * ldW(a.v, g, i, l + 1, k)) / dy;
+      y = y0 + (s == 1 ? a.dt : a.dt / 2) * vs[s];
+    }
+    const double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) / 6 * a.dt / dy;
+    a.cfly[c] = cf;
+    if (fabs(cf) > 1) atomicOr(a.flags, 2);
+  }
+}
+
+// ---- zonal sums on the pole-adjacent half rows (zonal_sum, parallel_mod.F90:741-764) ---
+// out[north*nlev + k] = (+-) sum_i f(i, jh, k) * le_lat(jh) / nlon / area_cell(pole) * scale
+// sign: south +f, north -f when signed != 0 (flux divergences); north +f otherwise.
+// If row_out != NULL the value is also broadcast along the pole row of row_out.
+struct PoleSumArgs { const double* f; double* out; double* row_out; int signed_north; };
+__global__ void __launch_bounds__(256) k_pole_sum(Geo g, DMesh M, PoleSumArgs a) {
+  __shared__ double sm[32];
+  const int k = blockIdx.x, north = blockIdx.y;
+  if ((north && !g.has_north) || (!north && !g.has_south)) return;
+  const int j = north ? g.nlat : 1, jh = north ? g.nhalf : 1;
+  double s = 0;
+  for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) {
+    const double f = __ldg(a.f + gidx(g, i, jh, k));
+    s += (north && a.signed_north) ? -f : f;
+  }
+  s = block_sum(s, sm);
+  const double pole = s * MJ(M.le_lat, jh) / g.nlon / MJ(M.area_cell, j);
+  if (a.out && threadIdx.x == 0) a.out[north * g.nlev + k] = pole;
+  if (a.row_out) for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) a.row_out[gidx(g, i, j, k)] = pole;
+}
+
+// ---- column kernel: calc_grad_mf + calc_dphsdt + calc_we_lev + accum_we_lev ------------
+// (operators_mod.F90:939-1006,1120-1143,192-232; adv_batch_mod.F90:526-627).
+// One thread per (i, j) column; level loops keep the reference's summation order.
+// m_lev is a pure function of phs_f (operators_mod.F90:498-521) and is formed on the fly.
+struct WeArgs {
+  const double *mfx_lon, *mfy_lat, *pole_dmf, *m_lev;
+  double *we_lev;       // (nlev+1 levels) of the star state
+  double *dphs;         // 2-D
+  double *cflz;         // (nlev+1 levels)
+  double dt; int* flags;
+};
+__device__ __forceinline__ double m_lev_at(const DMesh& M, const VC& vc, int nlev, int k1, double phs) {
+  // k1 = 1..nlev+1
+  if (k1 == 1) return 0.5 * (ph_lev_at(M, vc, 1, phs) + ph_lev_at(M, vc, 2, phs)) - ph_lev_at(M, vc, 1, phs);
+  if (k1 == nlev + 1) return ph_lev_at(M, vc, nlev + 1, phs) - 0.5 * (ph_lev_at(M, vc, nlev, phs) + ph_lev_at(M, vc, nlev + 1, phs));
+  return 0.5 * (ph_lev_at(M, vc, k1, phs) + ph_lev_at(M, vc, k1 + 1, phs)) - 0.5 * (ph_lev_at(M, vc, k1 - 1, phs) + ph_lev_at(M, vc, k1, phs));
+}
+
+// RK4 in eta for one half level (adv_batch_mod.F90:529-627).  we/ml are this column's
+// we and m_lev with stride `st` between levels (index 0 = half level 1).
+__device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const double* we, const double* ml, long long st,
+                                         double dt, double* out, int* flags) {
+  const double* hl = M.half_lev - 1;     // hl[l] = half_lev(l)
+  const double* hd = M.half_dlev - 1;
+  const double* fd = M.full_dlev + 1;    // fd[l] = full_dlev(l), stored from -1
+  auto W = [&](int l) { return we[(l - 1) * st]; };
+  auto ML = [&](int l) { return ml[(l - 1) * st]; };
+  auto search = [&](double w, double z) {
+    int l;
+    if (w > 0) { for (l = k1; l <= nlev; ++l) if (hl[l] <= z && z <= hl[l + 1]) break; if (l == nlev + 1) { atomicOr(flags, 4); l = nlev; } }
+    else { for (l = k1 - 1; l >= 1; --l) if (hl[l] <= z && z <= hl[l + 1]) break; if (l == 0) { atomicOr(flags, 4); l = 1; } }
+    return l;
+  };
+  auto interp = [&](int l, double z) {
+    return ((hl[l + 1] - z) * W(l) / ML(l) * hd[l] + (z - hl[l]) * W(l + 1) / ML(l + 1) * hd[l + 1]) / fd[l];
+  };
+  const double z0 = hl[k1];
+  const double w1 = W(k1) / ML(k1) * hd[k1];
+  double z = z0 + dt / 2 * w1;
+  int l = search(w1, z);
+  const double w2 = interp(l, z);
+  z = z0 + dt / 2 * w2; l = search(w2, z);
+  const double w3 = interp(l, z);
+  z = z0 + dt * w3; l = search(w3, z);
+  const double w4 = interp(l, z);
+  double deta = (w1 + 2 * w2 + 2 * w3 + w4) / 6 * dt;
+  int ks, ke, s;
+  if (deta < 0) { ks = k1 - 1; ke = 1; s = -1; } else { ks = k1; ke = nlev; s = 1; }
+  deta = fabs(deta);
+  for (l = ks; s > 0 ? l <= ke : l >= ke; l += s) {
+    deta = deta - fd[l];
+    if (deta < 0) { *out = s * ((1 + deta / fd[l]) + abs(l - ks)); return true; }
+  }
+  return false;
+}
+
+__global__ void __launch_bounds__(128) k_we_col(Geo g, DMesh M, WeArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const bool pole = (j == 1 || j == g.nlat);
+  const long long st = g.plane;
+  const long long c0 = gidx(g, i, j, 0);
+  double* we = a.we_lev + c0;
+  double dphs = 0, mf = 0;
+  we[0] = 0.0;
+  for (int k = 0; k < g.nlev; ++k) {
+    double dlon, dlat;
+    if (pole) { dlon = 0.0; dlat = __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k); }
+    else {
+      dlon = (__ldg(a.mfx_lon + c0 + k * st) - ldW(a.mfx_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
+      dlat = (__ldg(a.mfy_lat + c0 + k * st) * MJ(M.le_lat, j) - ldW(a.mfy_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+    }
+    dphs = dphs - dlon - dlat;
+    mf = mf + dlon + dlat;
+    we[(k + 1) * st] = mf;          // prefix over levels 1..k+1, finalised below
+  }
+  a.dphs[gidx(g, i, j, 0)] = dphs;
+  for (int k1 = 2; k1 <= g.nlev; ++k1) we[(k1 - 1) * st] = -(M.hybi[k1 - 1] * dphs) - we[(k1 - 1) * st];
+  we[g.nlev * st] = 0.0;
+  const double* ml = a.m_lev + c0;
+  for (int k1 = 2; k1 <= g.nlev; ++k1) {
+    double cz;
+    if (cflz_one(M, g.nlev, k1, we, ml, st, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+  }
+}
+
+// cflz for a tracer batch from its accumulated we / m_lev (adv_batch_mod.F90:526-627)
+struct CflzArgs { const double *we, *m_lev; double* cflz; double dt; int* flags; };
+__global__ void __launch_bounds__(128) k_cflz(Geo g, DMesh M, CflzArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const long long c0 = gidx(g, i, j, 0);
+  for (int k1 = 2; k1 <= g.nlev; ++k1) {
+    double cz;
+    if (cflz_one(M, g.nlev, k1, a.we + c0, a.m_lev + c0, g.plane, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * g.plane] = cz;
+  }
+}
+
+// ---- FFSL horizontal PPM flux (hflx_ppm_cell, ffsl_mod.F90:778-881) ----------------
+// The PPM coefficients of the upwind cell are formed on the fly from the 5-point
+// stencil instead of being stored in six work arrays and halo-filled (:813-826).
+struct HflxArgs {
+  const double *u, *v;          // advecting wind (inner) or mass flux (outer)
+  const double *mx, *my;        // field swept in x / in y
+  const double *cflx, *cfly;
+  double *mfx, *mfy;
+};
+__global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  if (j > 1 && j < g.nlat) {
+    const double cx = __ldg(a.cflx + c);
+    double flux = 0;
+    if (cx != 0) {
+      const int ci = (int)cx;
+      const double cf = cx - ci;
+      int iu; double s1, s2, sm = 0;
+      if (cx > 0) { iu = i - ci; s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += ldW(a.mx, g, wrapi(l, g.nlon), j, k); }
+      else { iu = i - ci + 1; s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += ldW(a.mx, g, wrapi(l, g.nlon), j, k); }
+      iu = wrapi(iu, g.nlon);
+      double ml, dm, m6;
+      ppm(ldW(a.mx, g, iu - 2, j, k), ldW(a.mx, g, iu - 1, j, k), ldW(a.mx, g, iu, j, k), ldW(a.mx, g, iu + 1, j, k),
+          ldW(a.mx, g, iu + 2, j, k), ml, dm, m6);
+      const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);
+      flux = (cx > 0 ? __ldg(a.u + c) : -__ldg(a.u + c)) * integ / cx;
+    }
+    a.mfx[c] = flux;
+  }
+  if (j <= g.nhalf) {
+    const double cy = __ldg(a.cfly + c);
+    double flux = 0;
+    if (cy != 0) {
+      int ju; double s1, s2;
+      if (cy > 0) { ju = j; s1 = 1 - cy; s2 = 1; } else { ju = j + 1; s1 = 0; s2 = -cy; }
+      double ml, dm, m6;
+      ppm(ldF(a.my, g, i, ju - 2, k), ldF(a.my, g, i, ju - 1, k), ldF(a.my, g, i, ju, k), ldF(a.my, g, i, ju + 1, k),
+          ldF(a.my, g, i, ju + 2, k), ml, dm, m6);
+      const double integ = ppm_integral(0.0, ml, dm, m6, s1, s2);
+      flux = (cy > 0 ? __ldg(a.v + c) : -__ldg(a.v + c)) * integ / cy;
+    }
+    a.mfy[c] = flux;
+  }
+}
+
+// Intermediate fields of the inner advective step (ffsl_mod.F90:354-406)
+struct FfslQArgs { const double *q, *qmfx, *qmfy, *divx, *divy, *pole; double *qx, *qy; double dt; };
+__global__ void __launch_bounds__(128) k_ffsl_q(Geo g, DMesh M, FfslQArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  const double q = __ldg(a.q + c);
+  if (j > 1 && j < g.nlat) {
+    a.qx[c] = q - 0.5 * ((__ldg(a.qmfx + c) - ldW(a.qmfx, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j) - __ldg(a.divx + c) * q) * a.dt;
+    a.qy[c] = q - 0.5 * ((__ldg(a.qmfy + c) * MJ(M.le_lat, j) - ldW(a.qmfy, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j) - __ldg(a.divy + c) * q) * a.dt;
+  } else {
+    const double pole = __ldg(a.pole + (j == 1 ? 0 : g.nlev) + k);
+    const double t = 0.5 * (pole - __ldg(a.divy + c) * q) * a.dt;
+    a.qx[c] = q;
+    a.qy[c] = j == 1 ? q - t : q + t;
+  }
+}
+
+// ---- FFSL vertical PPM flux (vflx_ppm_cell, ffsl_mod.F90:883-941) --------------------
+// Column accessor with the two ghost-level rules: GH_LINEAR = linear extrapolation
+// (pt, operators_mod.F90:1085-1090), GH_COPY = copies of the end levels (tracers,
+// adv_mod.F90:260-265).  l is the 1-based full level, valid for -1..nlev+2.
+enum { GH_LINEAR = 0, GH_COPY = 1 };
+struct ColQ {
+  const double* p; long long st; int nlev, mode;
+  __device__ __forceinline__ double in(int l) const { return p[(long long)(l - 1) * st]; }   // plain load: p may be shared memory
+  __device__ double operator()(int l) const {
+    if (l >= 1 && l <= nlev) return in(l);
+    if (mode == GH_COPY) return l < 1 ? in(1) : in(nlev);
+    if (l == 0) return 2 * in(1) - in(2);
+    if (l == -1) return 2 * (2 * in(1) - in(2)) - in(1);
+    if (l == nlev + 1) return 2 * in(nlev) - in(nlev - 1);
+    return 2 * (2 * in(nlev) - in(nlev - 1)) - in(nlev);
+  }
+};
+// flux through half level k1 (2..nlev)
+__device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, double w) {
+  if (cz == 0) return 0.0;
+  const int ci = (int)cz;
+  const double cf = cz - ci;
+  int ku; double s1, s2, sm = 0;
+  if (cz > 0) { ku = k1 - ci - 1; s1 = 1 - cf; s2 = 1; for (int l = k1 - ci; l <= k1 - 1; ++l) sm += q(l); }
+  else { ku = k1 - ci; s1 = 0; s2 = -cf; for (int l = k1; l <= k1 - ci - 1; ++l) sm += q(l); }
+  double ml = 0, dm = 0, m6 = 0;
+  if (ku >= 1 && ku <= q.nlev) ppm(q(ku - 2), q(ku - 1), q(ku), q(ku + 1), q(ku + 2), ml, dm, m6);
+  const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);
+  return (cz > 0 ? w : -w) * integ / cz;
+}
+
+// calc_grad_ptf tail (operators_mod.F90:1040-1112) + dpt (gmcore_mod.F90:490-495) + the
+// raw pt*m update of update_state (time_schemes_mod.F90:150-156), one thread per column.
+struct PtColArgs {
+  const double *pt, *ptf_lon, *ptf_lat, *pole_ptf, *we_lev, *cflz;   // star state / mass batch
+  const double *pt_old, *m_old;
+  double *ptm_new;      // new%pt (raw pt*m, filtered and divided by m afterwards)
+  double *dpt;          // optional (parity tests), may be NULL
+  double dt;
+};
+__global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const bool pole = (j == 1 || j == g.nlat);
+  const long long st = g.plane, c0 = gidx(g, i, j, 0);
+  ColQ q{a.pt + c0, st, g.nlev, GH_LINEAR};
+  double f_up = 0.0;   // ptf_lev(k), k = 1 -> 0
+  for (int k = 0; k < g.nlev; ++k) {
+    const long long c = c0 + k * st;
+    double dlon, dlat;
+    if (pole) { dlon = 0.0; dlat = __ldg(a.pole_ptf + (j == 1 ? 0 : g.nlev) + k); }
+    else {
+      dlon = (__ldg(a.ptf_lon + c) - ldW(a.ptf_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
+      dlat = (__ldg(a.ptf_lat + c) * MJ(M.le_lat, j) - ldW(a.ptf_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+    }
+    const int k1 = k + 2;   // lower half level of full level k+1
+    const double f_dn = k1 <= g.nlev ? vflx_one(q, k1, __ldg(a.cflz + c0 + (k1 - 1) * st), __ldg(a.we_lev + c0 + (k1 - 1) * st)) : 0.0;
+    const double dlev = f_dn - f_up;
+    f_up = f_dn;
+    const double dpt = -dlon - dlat - dlev;
+    if (a.dpt) a.dpt[c] = dpt;
+    a.ptm_new[c] = __ldg(a.pt_old + c) * __ldg(a.m_old + c) + a.dt * dpt;
+  }
+}
+
+// ---- calc_ph + calc_m (operators_mod.F90:136-168,471-543) from the filtered phs ------
+// ph_lev / ph are never stored: they are affine in phs_f and re-formed where needed.
+struct PhArgs { const double* phs_f; double *ph_exn_lev, *m, *m_lev; VC vc; int* flags; };
+__global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;     // k = 0..nlev (half level k+1)
+  if (i >= g.nlon) return;
+  const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
+  const long long c = gidx(g, i, j, k);
+  const double pl = ph_lev_at(M, a.vc, k + 1, phs);
+  a.ph_exn_lev[c] = pow(pl, a.vc.kappa);
+  a.m_lev[c] = m_lev_at(M, a.vc, g.nlev, k + 1, phs);
+  if (k < g.nlev) {
+    const double m = ph_lev_at(M, a.vc, k + 2, phs) - pl;
+    a.m[c] = m;
+    if (m <= 0) atomicOr(a.flags, 8);
+  }
+}
+
+// ---- calc_t + calc_gz_lev (operators_mod.F90:170-190,433-469) ------------------------
+// One thread per column.  The hydrostatic integral keeps the reference's summation
+// order (for each k: l = k..nlev ascending); the per-level terms are computed once and
+// parked in shared memory, so the O(nlev^2) part is additions only.
+struct GzArgs { const double *pt, *phs_f, *gzs; double *t, *gz_lev; VC vc; };
+__global__ void __launch_bounds__(64) k_gz_col(Geo g, DMesh M, GzArgs a) {
+  extern __shared__ double term[];     // [nlev][blockDim.x]
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const long long st = g.plane, c0 = gidx(g, i, j, 0);
+  const double phs = __ldg(a.phs_f + c0);
+  double pl0 = ph_lev_at(M, a.vc, 1, phs);
+  for (int k = 0; k < g.nlev; ++k) {
+    const double pl1 = ph_lev_at(M, a.vc, k + 2, phs);
+    const double ph = 0.5 * (pl0 + pl1);
+    const double t = __ldg(a.pt + c0 + k * st) * pow(ph / a.vc.p0, a.vc.kappa);
+    a.t[c0 + k * st] = t;
+    term[k * blockDim.x + threadIdx.x] = a.vc.Rd * t * log(pl1 / pl0);
+    pl0 = pl1;
+  }
+  const double gzs = __ldg(a.gzs + c0);
+  for (int k = 0; k < g.nlev; ++k) {
+    double dgz = 0.0;
+    for (int l = k; l < g.nlev; ++l) dgz = dgz + term[l * blockDim.x + threadIdx.x];
+    a.gz_lev[c0 + k * st] = gzs + dgz;
+  }
+  a.gz_lev[c0 + g.nlev * st] = gzs;    // T14: bottom interface = surface geopotential
+}
+
+// ---- div_damp_run, order 2 (div_damp_mod.F90:89-139); div is recomputed from the
+// filtered winds by k_div first (calc_div, operators_mod.F90:354-412). ---------------
+struct DivArgs { const double *u, *v; double* div; };
+__global__ void __launch_bounds__(128) k_div(Geo g, DMesh M, DivArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j == 1 || j == g.nlat) return;
+  const long long c = gidx(g, i, j, k);
+  a.div[c] = ((__ldg(a.u + c) * MJ(M.le_lon, j) - ldW(a.u, g, i - 1, j, k) * MJ(M.le_lon, j)) +
+              (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1))) / MJ(M.area_cell, j);
+}
+struct DivDampArgs { const double *div, *c_lon, *c_lat; double *u, *v; };
+__global__ void __launch_bounds__(128) k_div_damp(Geo g, DMesh M, DivDampArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  const double d0 = __ldg(a.div + c);
+  if (j > 1 && j < g.nlat)
+    a.u[c] = a.u[c] + __ldg(a.c_lon + (size_t)k * g.nlat + (j - 1)) * (ldW(a.div, g, i + 1, j, k) - d0) / MJ(M.de_lon, j);
+  if (j <= g.nhalf)
+    a.v[c] = a.v[c] + __ldg(a.c_lat + (size_t)k * g.nhalf + (j - 1)) * (ldW(a.div, g, i, j + 1, k) - d0) / MJ(M.de_lat, j);
+}
+
+// ---- tracer batch (adv_batch_mod.F90:207-252,379-403; adv_mod.F90:152-312) -----------
+// wind / mass-flux accumulation: mode 0 copy, 1 add, 2 add and divide by nstep+1
+struct AccumArgs { double* dst[2]; const double* src[2]; int nlev_[2]; int mode, nstep; };
+__global__ void __launch_bounds__(128) k_accum(Geo g, AccumArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    if (!a.dst[q] || k >= a.nlev_[q]) continue;
+    const double s = __ldg(a.src[q] + c);
+    if (a.mode == 0) a.dst[q][c] = s;
+    else { const double t = a.dst[q][c] + s; a.dst[q][c] = a.mode == 2 ? t / (a.nstep + 1) : t; }
+  }
+}
+
+// horizontal update q* = (old_m q - dt div F) / m, pole rows by zonal means (:183-233)
+struct TrHArgs { const double *qo, *old_m, *m, *qmf_lon, *qmf_lat, *pole; double* qn; double dt; };
+__global__ void __launch_bounds__(128) k_tracer_h(Geo g, DMesh M, TrHArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  const double mq = __ldg(a.old_m + c) * __ldg(a.qo + c);
+  double r;
+  if (j > 1 && j < g.nlat)
+    r = mq - ((__ldg(a.qmf_lon + c) - ldW(a.qmf_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) +
+              (__ldg(a.qmf_lat + c) * MJ(M.le_lat, j) - ldW(a.qmf_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1))) / MJ(M.area_cell, j) * a.dt;
+  else {
+    const double pole = __ldg(a.pole + (j == 1 ? 0 : g.nlev) + k) * a.dt;
+    r = j == 1 ? mq - pole : mq + pole;
+  }
+  a.qn[c] = r / __ldg(a.m + c);
+}
+
+// sequential negative filling along x (:236-258); one block per (row, level), the sweep
+// itself only runs on rows that contain a negative value.  The reference reads/writes
+// the (stale) lon-halo cells at i=1 / i=nlon; here the row is periodic.
+struct NegXArgs { double* q; const double* m; int* flags; };
+__global__ void __launch_bounds__(128) k_negfill_x(Geo g, NegXArgs a) {
+  const int j = g.jb + blockIdx.x, k = blockIdx.y;
+  double* q = a.q + gidx(g, 0, j, k); const double* m = a.m + gidx(g, 0, j, k);
+  int neg = 0;
+  for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) neg |= q[i] < 0;
+  neg = __syncthreads_or(neg);
+  if (!neg || threadIdx.x != 0) return;
+  const int n = g.nlon;
+  for (int i = 0; i < n; ++i) {
+    if (q[i] < 0) {
+      const int im = i == 0 ? n - 1 : i - 1, ip = i == n - 1 ? 0 : i + 1;
+      const double qm0 = q[i] * m[i], qm1 = q[im] * m[im], qm2 = q[ip] * m[ip], h = 0.5 * qm0;
+      if (qm1 >= h && qm2 >= h) { q[im] = (qm1 - h) / m[im]; q[ip] = (qm2 - h) / m[ip]; }
+      else if (qm1 > qm0) q[im] = (qm1 - qm0) / m[im];
+      else if (qm2 > qm0) q[ip] = (qm2 - qm0) / m[ip];
+      else atomicOr(a.flags, 16);
+      q[i] = 0;
+    }
+  }
+}
+
+// vertical flux + update + negative filling in z (:259-297), one thread per column,
+// the column staged in shared memory (the update is in place).
+struct TrVArgs { double* q; const double *m, *we, *cflz; double dt; int* flags; };
+__global__ void __launch_bounds__(64) k_tracer_v(Geo g, TrVArgs a) {
+  extern __shared__ double col[];     // [2*nlev][blockDim.x]: q, then new q
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const long long st = g.plane, c0 = gidx(g, i, j, 0);
+  const int B = blockDim.x, nlev = g.nlev;
+  double* qs = col + threadIdx.x; double* qn = col + (size_t)nlev * B + threadIdx.x;
+  for (int k = 0; k < nlev; ++k) qs[k * B] = a.q[c0 + k * st];
+  ColQ q{qs, (long long)B, nlev, GH_COPY};
+  double f_up = 0;
+  for (int k = 0; k < nlev; ++k) {
+    const int k1 = k + 2;
+    const double f_dn = k1 <= nlev ? vflx_one(q, k1, __ldg(a.cflz + c0 + (k1 - 1) * st), __ldg(a.we + c0 + (k1 - 1) * st)) : 0.0;
+    qn[k * B] = qs[k * B] - ((f_dn - f_up) * a.dt) / __ldg(a.m + c0 + k * st);
+    f_up = f_dn;
+  }
+  for (int k = 0; k < nlev; ++k) {
+    if (qn[k * B] < 0) {
+      const double m0 = __ldg(a.m + c0 + k * st);
+      const double mm = k > 0 ? __ldg(a.m + c0 + (k - 1) * st) : 0.0, mp = k < nlev - 1 ? __ldg(a.m + c0 + (k + 1) * st) : 0.0;
+      const double qm0 = qn[k * B] * m0, qm1 = k > 0 ? qn[(k - 1) * B] * mm : 0.0, qm2 = k < nlev - 1 ? qn[(k + 1) * B] * mp : 0.0;
+      const double h = 0.5 * qm0;
+      if (qm1 >= h && qm2 >= h) { if (qm1 > 0) qn[(k - 1) * B] = (qm1 - h) / mm; if (qm2 > 0) qn[(k + 1) * B] = (qm2 - h) / mp; }
+      else if (qm1 > qm0) { if (qm1 > 0) qn[(k - 1) * B] = (qm1 - qm0) / mm; }
+      else if (qm2 > qm0) { if (qm2 > 0) qn[(k + 1) * B] = (qm2 - qm0) / mp; }
+      else atomicOr(a.flags, 16);
+      qn[k * B] = 0;
+    }
+  }
+  for (int k = 0; k < nlev; ++k) a.q[c0 + k * st] = qn[k * B];
+}
+
+// 3 x lon_damp_on_cell(order 2) (lon_damp_mod.F90:158-177,231-236), one block per row
+struct LonDampArgs { double* q; const double* wgt; /* [nlat+1], entry j */ int npass; };
+__global__ void __launch_bounds__(256) k_lon_damp(Geo g, LonDampArgs a) {
+  extern __shared__ double row[];     // [2][nlon]
+  const int j = g.jb + blockIdx.x, k = blockIdx.y;
+  if (j == 1 || j == g.nlat) return;
+  const double wgt = __ldg(a.wgt + j);
+  if (wgt == 0) return;
+  double* q = a.q + gidx(g, 0, j, k);
+  const int n = g.nlon;
+  double *f = row, *gn = row + n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) f[i] = q[i];
+  __syncthreads();
+  const double c = 0.25;
+  for (int p = 0; p < a.npass; ++p) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const double fm = f[i == 0 ? n - 1 : i - 1], f0 = f[i], fp = f[i == n - 1 ? 0 : i + 1];
+      gn[i] = wgt * (f0 + c * (fm - 2.0 * f0 + fp)) + (1 - wgt) * f0;
+    }
+    __syncthreads();
+    double* t = f; f = gn; gn = t;
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) q[i] = f[i];
+}
+
+// ---- Held-Suarez forcing (held_suarez_test_mod.F90:65-113) ---------------------------
+struct HsArgs { double *u, *v, *pt; const double *t, *phs_f; double dt; VC vc; };
+__global__ void __launch_bounds__(128) k_held_suarez(Geo g, DMesh M, HsArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const long long c = gidx(g, i, j, k);
+  const double sig_b = 0.7, kf = 1.0 / 86400.0, ka = 0.025 / 86400.0, ks = 0.25 / 86400.0;
+  const double fl = M.full_lev[k + 2];      // full_lev(k+1), stored from -1
+  const double prof = fmax(0.0, (fl - sig_b) / (1.0 - sig_b));
+  const double kv = kf * prof;
+  if (j > 1 && j < g.nlat) a.u[c] = a.u[c] - a.dt * kv * a.u[c];
+  if (j <= g.nhalf) a.v[c] = a.v[c] - a.dt * kv * a.v[c];
+  const double cl = MJ(M.full_cos_lat, j), sn = MJ(M.full_sin_lat, j);
+  const double c4 = (cl * cl) * (cl * cl);
+  const double kt = ka + (ks - ka) * prof * c4;
+  const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
+  const double ph = 0.5 * (ph_lev_at(M, a.vc, k + 1, phs) + ph_lev_at(M, a.vc, k + 2, phs));
+  const double p_p0 = ph / a.vc.p0;
+  const double teq = fmax(200.0, (315.0 - 60.0 * (sn * sn) - 10.0 * log(p_p0) * (cl * cl)) * pow(p_p0, a.vc.kappa));
+  a.pt[c] = a.pt[c] - a.dt * kt * a.pt[c] * (1.0 - teq / __ldg(a.t + c));
+}

@@ -36,13 +36,15 @@ static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, 
   LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
 }
 
+#include "hydro.cuh"
+
 // One shallow-water step(old, star, new, dt) (time_schemes_mod.F90:102-118).
 static void swm_step(gmc_handle* h, DState& old_, DState& star, DState& nw, double dt) {
   const Geo& g = h->g;
   run_forward_prepare(h, star);
   TendArgs t{};
   t.mfx_lon = star.mfx_lon; t.mfy_lat = star.mfy_lat; t.pv_lon = star.pv_lon; t.pv_lat = star.pv_lat; t.ke = star.ke;
-  t.wedudlev = nullptr; t.wedvdlev = nullptr; t.du = h->du; t.dv = h->dv;
+  t.we_lev = nullptr; t.du = h->du; t.dv = h->dv;
   t.gz_old = old_.gz; t.pole_dmf = h->pole_dmf; t.gz_new = nw.gz; t.dt = dt; t.grav = h->cfg.g;
   t.coriolis_scheme = h->cfg.coriolis_scheme; t.swm = 1;
   LAUNCH(h, k_tend, grid3(h, g.nlev), 128, 0, g, h->M, t);

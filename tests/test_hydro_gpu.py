@@ -1,0 +1,84 @@
+"""GPU parity: hydrostatic core (CUDA via the C ABI) against the CPU oracle.
+
+Tolerance (BASELINE.json north_star): per-step relative L2 <= 1e-12 on every
+prognostic field (u, v, pt, phs) and on the FFSL tracer; conserved integrals agree
+to 1e-13 relative.
+"""
+import numpy as np
+import pytest
+
+from util import PROGNOSTIC_HYDRO, assert_diag_close, make_pair, rel_l2, smooth_tracer
+
+pytestmark = pytest.mark.gpu
+
+TOL_STEP = 1e-12
+DERIVED = [("u_f", "lon"), ("v_f", "lat"), ("phs_f", "2d"), ("m", "cell"), ("mfx_lon", "lon"), ("mfy_lat", "lat"),
+           ("u_lat", "lat"), ("v_lon", "lon"), ("ke", "cell"), ("pv", "vtx"), ("pv_lon", "lon"), ("pv_lat", "lat"),
+           ("div", "cell"), ("t", "cell"), ("gz_lev", "cell+lev"), ("ph_exn_lev", "cell+lev"), ("we_lev", "cell+lev"),
+           ("m_lev", "cell+lev")]
+WORK = [("cflx", "lon"), ("cfly", "lat"), ("cflz", "cell+lev"), ("divx", "cell"), ("divy", "cell"), ("qx", "cell"),
+        ("qy", "cell"), ("ptf_lon", "lon"), ("ptf_lat", "lat"), ("du", "lon"), ("dv", "lat"), ("dpt", "cell")]
+
+
+def field_errors(host, orc, gpu, fields):
+    out = {}
+    for name, loc in fields:
+        a = gpu.field(name); b = orc.field(name)
+        if loc == "2d":
+            a = a.reshape(a.shape[-2:]); b = b.reshape(b.shape[-2:])
+        a = host.interior(a, loc); b = host.interior(b, loc)
+        if name in ("we_lev", "cflz"):      # top/bottom interfaces are identically 0
+            a, b = a[1:-1], b[1:-1]
+        out[name] = rel_l2(a, b)
+    return out
+
+
+def check(host, orc, gpu, fields, tol, what):
+    errs = field_errors(host, orc, gpu, fields)
+    bad = {k: v for k, v in errs.items() if not v <= tol}
+    assert not bad, f"{what}: rel L2 above {tol}: {bad}"
+
+
+def start(nlon, nlat, nlev, dt, case, **kw):
+    host, ic, orc, gpu = make_pair(nlon, nlat, nlev, dt, case, **kw)
+    if host.cfg.ntracers:
+        q = smooth_tracer(host, host.cfg.ntracers)
+        orc.set_tracers(q); gpu.set_tracers(q)
+    orc.prepare_run(); gpu.prepare_run()
+    return host, ic, orc, gpu
+
+
+@pytest.mark.parametrize("case,nlon,nlat,nlev,dt,scheme", [
+    ("baroclinic_wave", 64, 33, 8, 600.0, "wrfrk3"),
+    ("baroclinic_wave", 64, 33, 8, 600.0, "pc2"),
+    ("baroclinic_wave", 120, 60, 32, 300.0, "wrfrk3"),
+    ("held_suarez", 64, 32, 8, 600.0, "wrfrk3"),
+])
+def test_hydro_per_step_parity(gpu_required, case, nlon, nlat, nlev, dt, scheme):
+    host, ic, orc, gpu = start(nlon, nlat, nlev, dt, case, time_scheme=scheme)
+    check(host, orc, gpu, [f for f in DERIVED if f[0] not in ("we_lev",)], 1e-12, "prepare_run")
+    assert_diag_close(gpu.diagnose(), orc.diagnose())
+    for step in range(4):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL_STEP, f"step {step}")
+        check(host, orc, gpu, DERIVED, 1e-10, f"step {step} derived")
+        qg, qo = gpu.get_tracers(), orc.get_tracers()
+        for l in range(host.cfg.ntracers):
+            assert rel_l2(host.interior(qg[l], "cell"), host.interior(qo[l], "cell")) <= TOL_STEP, f"step {step} tracer {l}"
+        assert_diag_close(dg, do)
+
+
+def test_hydro_conservation_drift(gpu_required):
+    """JW baroclinic wave, 1 simulated day at coarse resolution: tm drift ~ round-off and equal to the oracle's."""
+    host, ic, orc, gpu = start(64, 33, 8, 600.0, "baroclinic_wave")
+    d0 = gpu.diagnose()
+    n = 144
+    dg = gpu.run_steps(n); do = orc.run_steps(n)
+    tm_g = dg[:, 0] / d0[0] - 1; tm_o = do[:, 0] / d0[0] - 1
+    assert np.abs(tm_g).max() < 1e-13
+    assert np.abs(tm_g - tm_o).max() < 1e-13
+    te_g = dg[:, 1] / d0[1] - 1; te_o = do[:, 1] / d0[1] - 1
+    assert np.abs(te_g - te_o).max() < 1e-12
+    for name, loc in PROGNOSTIC_HYDRO:
+        e = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name), loc))
+        assert e < 1e-9, (name, e)

@@ -38,3 +38,15 @@ def assert_diag_close(dg, do, rtol=1e-13, tav_atol=1e-6):
     idx = [3, 4, 5, 6, 7]
     np.testing.assert_allclose(dg[:, idx], do[:, idx], rtol=10 * rtol, atol=1e-30)
     assert np.abs(dg[:, 2] - do[:, 2]).max() < tav_atol
+
+
+def smooth_tracer(host, n):
+    """Positive, smooth tracer fields in the halo'd host layout (interior written)."""
+    q = np.zeros((n,) + host.shape("cell"))
+    lon = host.vec["full_lon"][host.hx:host.hx + host.nlon]
+    lat = host.vec["full_lat"][host.hy:host.hy + host.nlat]
+    for l in range(n):
+        f = 1.0 + 0.5 * np.cos(lat)[:, None] ** 2 * np.sin((l + 2) * lon)[None, :] + 0.3 * np.sin(lat)[:, None]
+        for k in range(host.nlev):
+            host.interior(q[l], "cell")[k] = f * (1.0 + 0.1 * k / host.nlev)
+    return q
