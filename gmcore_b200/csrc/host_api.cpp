@@ -83,12 +83,13 @@ int gmh_set_ic(const gmh_host* h, int test_case, double* u, double* v, double* p
                unsigned long long seed) {
   const Mesh& m = h->mesh;
   Lay L{m.hx, m.hy, m.nlon, m.nlat, m.nlev};
-  (void)seed;
   switch (test_case) {
     case GMH_IC_ROSSBY_HAURWITZ: ic_rossby_haurwitz(h->c, m, L, u, v, pt_or_gz, gzs); return 0;
     case GMH_IC_MOUNTAIN_ZONAL_FLOW: ic_mountain_zonal_flow(h->c, m, L, u, v, pt_or_gz, gzs); return 0;
     case GMH_IC_BAROCLINIC_WAVE:
       ic_baroclinic_wave(h->c, m, h->vc, L, h->ptop, 1.0e5, u, v, pt_or_gz, phs, gzs); return 0;
+    case GMH_IC_HELD_SUAREZ:
+      ic_held_suarez(h->c, m, h->vc, L, h->ptop, 1.0e5, u, v, pt_or_gz, phs, gzs, seed, true); return 0;
     default: return -1;
   }
 }

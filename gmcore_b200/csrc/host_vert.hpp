@@ -119,4 +119,71 @@ inline void ic_baroclinic_wave(const Consts& c, const Mesh& m, const VertCoord& 
   }
 }
 
+// SplitMix64 -> U[0,1): fixed-seed stand-in for random_number (the reference seeds from
+// the OS, held_suarez_test_mod.F90:37, so it is not reproducible run to run).
+struct SplitMix64 {
+  unsigned long long s;
+  explicit SplitMix64(unsigned long long seed) : s(seed) {}
+  double next() {
+    unsigned long long z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+    return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+  }
+};
+
+// src/tests/rossby_haurwitz_wave_3d_test_mod.F90:26-136 followed by the perturbation of
+// src/tests/held_suarez_test_mod.F90:28-63 (perturb = false gives the plain 3-D RH wave).
+inline void ic_held_suarez(const Consts& c, const Mesh& m, const VertCoord& vc, const Lay& L, double ptop, double hyb_p0,
+                           double* u, double* v, double* pt, double* phs, double* gzs, unsigned long long seed, bool perturb) {
+  const int n = 4, nlev = m.nlev;
+  const double u0 = 50.0, t0 = 288.0, gamma = 0.0065, pref = 955.0e2;
+  const double a = c.radius, M = u0 / (n * c.radius), g = c.g, omega = c.omega;
+  for (size_t q = 0; q < L.n2_full(); ++q) gzs[q] = 0.0;
+  for (int k = 1; k <= nlev; ++k) {
+    for (int j = 1; j <= m.nlat; ++j) {
+      const double cl = m.full_cos_lat(j), sl = m.full_sin_lat(j);
+      for (int i = 1; i <= m.nlon; ++i) {
+        const double lon = m.half_lon(i);
+        u[L.f(i, j, k)] = a * M * cl + a * M * ipow(cl, n - 1) * std::cos(n * lon) * (n * (sl * sl) - cl * cl);
+      }
+    }
+    for (int j = 1; j <= m.num_half_lat; ++j) {
+      const double cl = m.half_cos_lat(j), sl = m.half_sin_lat(j);
+      for (int i = 1; i <= m.nlon; ++i) v[L.h(i, j, k)] = -a * M * n * ipow(cl, n - 1) * sl * std::sin(n * m.full_lon(i));
+    }
+  }
+  for (int j = 1; j <= m.nlat; ++j) {
+    const double cl = m.full_cos_lat(j);
+    for (int i = 1; i <= m.nlon; ++i) {
+      const double lon = m.full_lon(i);
+      const double a_lat = M * (2 * omega + M) / 2 * (cl * cl) + (M * M) / 4.0 * ipow(cl, 2 * n) * ((n + 1) * (cl * cl) + (2 * n * n - n - 2)) -
+                           n * n * (M * M) / 2 * ipow(cl, 2 * (n - 1));
+      const double b_lat = 2 * (omega + M) * M / (n + 1) / (n + 2) * ipow(cl, n) * ((n * n + 2 * n + 2) - (n + 1) * (n + 1) * (cl * cl));
+      const double c_lat = (M * M) / 4.0 * ipow(cl, 2 * n) * ((n + 1) * (cl * cl) - (n + 2));
+      const double phi_p = (a * a) * (a_lat + b_lat * std::cos(n * lon) + c_lat * std::cos(2 * n * lon));
+      phs[L.f2(i, j)] = pref * std::pow(1 + gamma / g / t0 * phi_p, g / gamma / c.Rd);
+    }
+  }
+  auto ph_lev = [&](int k, double ps) { return vc.hyai[k - 1] * (hyb_p0 - ptop) + vc.hybi[k - 1] * (ps - ptop) + ptop; };
+  // t and pt from the UNPERTURBED phs (the reference perturbs phs first but keeps t, ph)
+  for (int k = 1; k <= nlev; ++k)
+    for (int j = 1; j <= m.nlat; ++j) for (int i = 1; i <= m.nlon; ++i) {
+      const double ps = phs[L.f2(i, j)];
+      const double ph = 0.5 * (ph_lev(k, ps) + ph_lev(k + 1, ps));
+      const double t = t0 * std::pow(ph / pref, gamma * c.Rd / g);
+      pt[L.f(i, j, k)] = t * std::pow(c.p0 / ph, c.Rd_o_cpd);
+    }
+  if (!perturb) return;
+  SplitMix64 rng(seed);
+  for (int j = 1; j <= m.nlat; ++j) for (int i = 1; i <= m.nlon; ++i) {
+    const double cl = m.full_cos_lat(j);
+    phs[L.f2(i, j)] = phs[L.f2(i, j)] - (0.5 + rng.next()) * (cl * cl);
+  }
+  for (int k = 1; k <= nlev; ++k)
+    for (int j = 1; j <= m.nlat; ++j) for (int i = 1; i <= m.nlon; ++i) {
+      const double cl = m.full_cos_lat(j);
+      pt[L.f(i, j, k)] = pt[L.f(i, j, k)] - (0.5 + rng.next()) * (cl * cl);
+    }
+}
+
 }  // namespace gmh

@@ -391,7 +391,10 @@ struct Model {
   // ---- gmcore_mod.F90:213-341 ---------------------------------------------------------
   void diagnose(int itime, double out[8]) {
     const Mesh& mesh = b.mesh; State& s = b.state[itime]; const double g = b.cfg.g, cpd = b.cfg.cpd;
-    double tm = 0, te_ke = 0, te_ie = 0, te_pe = 0, tav = 0, tpe = 0, tpt = 0;
+    // Accumulators are long double: the reference's global sums (per-rank partial sums + MPI_Allreduce,
+    // any association under -Ofast) carry O(sqrt(N) eps) noise that would otherwise mask the 1e-13
+    // drift criterion; each term is still formed in double exactly as in the Fortran.
+    long double tm = 0, te_ke = 0, te_ie = 0, te_pe = 0, tav = 0, tpe = 0, tpt = 0;
     for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       tm = tm + s.m(i, j, k) * mesh.area_cell(j);
     for (int k = 1; k <= mesh.nlev; ++k) {
@@ -420,7 +423,7 @@ struct Model {
     if (b.cfg.baroclinic)
       for (int k = 1; k <= mesh.nlev; ++k) for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         tpt = tpt + s.m(i, j, k) * s.pt(i, j, k) * mesh.area_cell(j);
-    double te = te_ke + te_ie + te_pe;
+    long double te = te_ke + te_ie + te_pe;
     s.tm = tm; s.te = te; s.tav = tav; s.tpe = tpe; s.te_ke = te_ke; s.te_ie = te_ie; s.te_pe = te_pe; s.tpt = tpt;
     out[0] = tm; out[1] = te; out[2] = tav; out[3] = tpe; out[4] = te_ke; out[5] = te_ie; out[6] = te_pe; out[7] = tpt;
   }

@@ -20,22 +20,39 @@ WORK = [("cflx", "lon"), ("cfly", "lat"), ("cflz", "cell+lev"), ("divx", "cell")
         ("qy", "cell"), ("ptf_lon", "lon"), ("ptf_lat", "lat"), ("du", "lon"), ("dv", "lat"), ("dpt", "cell")]
 
 
+def pair(host, orc, gpu, name, loc):
+    a = gpu.field(name); b = orc.field(name)
+    if loc == "2d":
+        a = a.reshape(a.shape[-2:]); b = b.reshape(b.shape[-2:])
+    return host.interior(a, loc), host.interior(b, loc)
+
+
+WIND = ("u_lon", "v_lat", "u_f", "v_f")
+
+
 def field_errors(host, orc, gpu, fields):
+    """rel L2 per field.  The two wind components are normalised by the L2 norm of the
+    horizontal wind vector (|u|^2 + |v|^2)^(1/2): the Jablonowski-Williamson state starts
+    from v == 0, so a component-wise relative norm of v is ill-defined there."""
     out = {}
+    wind = None
     for name, loc in fields:
-        a = gpu.field(name); b = orc.field(name)
-        if loc == "2d":
-            a = a.reshape(a.shape[-2:]); b = b.reshape(b.shape[-2:])
-        a = host.interior(a, loc); b = host.interior(b, loc)
+        a, b = pair(host, orc, gpu, name, loc)
         if name in ("we_lev", "cflz"):      # top/bottom interfaces are identically 0
             a, b = a[1:-1], b[1:-1]
-        out[name] = rel_l2(a, b)
+        if name in WIND:
+            if wind is None:
+                wind = float(np.hypot(np.linalg.norm(pair(host, orc, gpu, "u_lon", "lon")[1]),
+                                      np.linalg.norm(pair(host, orc, gpu, "v_lat", "lat")[1])))
+            out[name] = float(np.linalg.norm((a - b).ravel())) / wind
+        else:
+            out[name] = rel_l2(a, b)
     return out
 
 
-def check(host, orc, gpu, fields, tol, what):
+def check(host, orc, gpu, fields, tol, what, loose=None):
     errs = field_errors(host, orc, gpu, fields)
-    bad = {k: v for k, v in errs.items() if not v <= tol}
+    bad = {k: v for k, v in errs.items() if not v <= (loose or {}).get(k, tol)}
     assert not bad, f"{what}: rel L2 above {tol}: {bad}"
 
 
@@ -61,7 +78,9 @@ def test_hydro_per_step_parity(gpu_required, case, nlon, nlat, nlev, dt, scheme)
     for step in range(4):
         dg = gpu.run_steps(1); do = orc.run_steps(1)
         check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL_STEP, f"step {step}")
-        check(host, orc, gpu, DERIVED, 1e-10, f"step {step} derived")
+        # pv_lon blends with the upwind value selected by sign(v_lon); while the JW flow still has
+        # v == round-off noise that sign is arbitrary, so pv_lon gets a looser bound.
+        check(host, orc, gpu, DERIVED, 1e-10, f"step {step} derived", loose={"pv_lon": 1e-7} if case == "baroclinic_wave" else None)
         qg, qo = gpu.get_tracers(), orc.get_tracers()
         for l in range(host.cfg.ntracers):
             assert rel_l2(host.interior(qg[l], "cell"), host.interior(qo[l], "cell")) <= TOL_STEP, f"step {step} tracer {l}"
@@ -80,5 +99,5 @@ def test_hydro_conservation_drift(gpu_required):
     te_g = dg[:, 1] / d0[1] - 1; te_o = do[:, 1] / d0[1] - 1
     assert np.abs(te_g - te_o).max() < 1e-12
     for name, loc in PROGNOSTIC_HYDRO:
-        e = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name), loc))
+        e = rel_l2(*pair(host, orc, gpu, name, loc))
         assert e < 1e-9, (name, e)
