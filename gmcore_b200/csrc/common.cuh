@@ -24,8 +24,10 @@ struct Geo {
   long long plane;        // NY * nlon
 };
 
-__host__ __device__ __forceinline__ long long gidx(const Geo& g, int i, int j, int k) {
-  return ((long long)k * g.NY + (j - g.jlo)) * g.nlon + i;
+// 32-bit element index: every field has fewer than 2^31 elements (checked in gmc_create),
+// which keeps the per-load address arithmetic off the 64-bit IMAD path.
+__host__ __device__ __forceinline__ int gidx(const Geo& g, int i, int j, int k) {
+  return (k * g.NY + (j - g.jlo)) * g.nlon + i;
 }
 __device__ __forceinline__ int wrapi(int i, int nlon) {
   return i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);

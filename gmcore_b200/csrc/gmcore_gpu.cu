@@ -44,6 +44,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   g.hjb = g.jb; g.hje = g.has_north ? g.je - 1 : g.je;
   g.jlo = g.jb - GMC_HL; g.NY = (g.je - g.jb + 1) + 2 * GMC_HL;
   g.plane = (long long)g.NY * g.nlon;
+  if (g.plane * (g.nlev + 2) >= (1LL << 31)) { snprintf(g_create_err, sizeof(g_create_err), "band too large for 32-bit field indices"); delete h; return 3; }
   cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   const size_t n3 = (size_t)g.plane * g.nlev, n3h = (size_t)g.plane * (g.nlev + 1), n2 = (size_t)g.plane;
   const bool baro = cfg->baroclinic != 0;
