@@ -26,10 +26,23 @@ static void diag_to_abi(const double* s, double* out) {
   out[4] = s[1]; out[5] = s[2]; out[6] = s[3]; out[7] = s[6];
 }
 
+// time_integrate (gmcore_mod.F90:577-591) for every band driven by this handle
 static int time_integrate_impl(gmc_handle* h, int old_, int nw, double dt, int time_step) {
-  time_integrator(h, old_, nw, dt);
-  if (h->cfg.baroclinic) hydro_post_step(h, nw, dt, time_step);
+  if (time_integrator(h, old_, nw, dt)) return 1;
+  if (!h->cfg.baroclinic) return 0;
+  bool adv = false;
+  for_bands(h, [&](gmc_handle* b) { adv = hydro_post_compute(b, nw, dt, time_step); });
+  const bool hs = h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ;
+  if (adv || hs) {
+    auto post_set = [&](gmc_handle* b) { HaloSet s = adv ? tracer_halo_set(b, 1) : halo_set(); if (hs) halo_add(s, b->st[nw].pt, b->g.nlev); return s; };
+    if (halo_exchange(h, post_set)) return 1;
+  }
+  for_bands(h, [&](gmc_handle* b) { hydro_adv_finish(b, nw, adv); });
   return 0;
+}
+// time_advance bookkeeping of the tracer alert (time_mod.F90:128-159), every band
+static void alert_advance(gmc_handle* h, int time_step) {
+  for_bands(h, [&](gmc_handle* b) { if (b->alert_ring) { b->alert_last = time_step * b->cfg.dt_dyn; b->alert_ring = false; } });
 }
 
 extern "C" {
@@ -37,15 +50,23 @@ extern "C" {
 int gmc_prepare_run(gmc_handle* h, int old_) {
   if (check_ready(h)) return 1;
   if (old_ < 1 || old_ > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", old_); return 1; }
-  const Geo& g = h->g; DState& S = h->st[old_];
-  run_filter(h, S.u, 0, g.nlev, GMC_BIG_FILTER, S.u_f, -1, nullptr);
-  run_filter(h, S.v, 1, g.nlev, GMC_BIG_FILTER, S.v_f, -1, nullptr);
-  if (h->cfg.baroclinic) {
-    hydro_prepare_run(h, old_);
-  } else {
+  if (!h->cfg.baroclinic) {
+    const Geo& g = h->g; DState& S = h->st[old_];
+    run_filter(h, S.u, 0, g.nlev, GMC_BIG_FILTER, S.u_f, -1, nullptr);
+    run_filter(h, S.v, 1, g.nlev, GMC_BIG_FILTER, S.v_f, -1, nullptr);
     // gz_f = big(gz); calc_m: m = (gz - gzs) / g
     run_filter(h, S.gz, 0, g.nlev, GMC_BIG_FILTER, S.gz_f, -1, nullptr, POST_SWM_M, nullptr, S.m);
     run_forward_prepare(h, S);
+  } else {
+    for_bands(h, [&](gmc_handle* b) {
+      DState& S = b->st[old_];
+      run_filter(b, S.u, 0, b->g.nlev, GMC_BIG_FILTER, S.u_f, -1, nullptr);
+      run_filter(b, S.v, 1, b->g.nlev, GMC_BIG_FILTER, S.v_f, -1, nullptr);
+      hydro_prepare_run_1(b, old_);
+    });
+    if (halo_exchange(h, [&](gmc_handle* b) { return prepare_halo_set(b, old_); })) return 1;
+    if (h->cfg.ntracers > 0 && halo_exchange(h, [&](gmc_handle* b) { return tracer_halo_set(b, 0); })) return 1;
+    for_bands(h, [&](gmc_handle* b) { hydro_prepare_run_2(b, old_); });
   }
   CUDA_CHECK(cudaGetLastError());
   return 0;
@@ -53,46 +74,61 @@ int gmc_prepare_run(gmc_handle* h, int old_) {
 
 int gmc_time_integrate(gmc_handle* h, int old_, int nw, double dt, int time_step) {
   if (check_ready(h)) return 1;
-  time_integrate_impl(h, old_, nw, dt, time_step);
+  alert_advance(h, time_step - 1);     // the host's time_advance ran since the previous call
+  if (time_integrate_impl(h, old_, nw, dt, time_step)) return 1;
   CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Global sums over all bands: single-process group -> host sum in band order;
+// one process per GPU -> ncclAllReduce of the partial sums (global_sum, parallel_mod.F90:805-816).
+static int reduce_diag(gmc_handle* h, std::vector<double*>& dbufs, int nsets, double* out_abi) {
+  std::vector<double> acc((size_t)nsets * 8, 0.0), tmp((size_t)nsets * 8);
+  if (h->nccl_comm) {
+    NcclApi& n = nccl_api();
+    if (n.AllReduce(dbufs[0], dbufs[0], (size_t)nsets * 8, GMC_NCCL_DOUBLE, GMC_NCCL_SUM, h->nccl_comm, h->stream)) {
+      snprintf(h->err, sizeof(h->err), "ncclAllReduce failed"); return 1; }
+  }
+  for (double* d : dbufs) {
+    CUDA_CHECK(cudaMemcpyAsync(tmp.data(), d, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    for (size_t q = 0; q < acc.size(); ++q) acc[q] += tmp[q];
+  }
+  for (int s = 0; s < nsets; ++s) diag_to_abi(&acc[(size_t)s * 8], out_abi + (size_t)s * 8);
   return 0;
 }
 
 int gmc_diagnose(gmc_handle* h, int itime, double out[8]) {
   if (check_ready(h)) return 1;
-  launch_diag(h, itime, h->diag_out);
-  double s[8];
-  CUDA_CHECK(cudaMemcpyAsync(s, h->diag_out, 7 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  CUDA_CHECK(cudaStreamSynchronize(h->stream));
-  diag_to_abi(s, out);
-  return 0;
+  std::vector<double*> dbufs;
+  for_bands(h, [&](gmc_handle* b) { launch_diag(b, itime, b->diag_out); dbufs.push_back(b->diag_out); });
+  return reduce_diag(h, dbufs, 1, out);
 }
 
 int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int nsteps, double* diag) {
   if (check_ready(h)) return 1;
-  double* dbuf = nullptr;
-  if (diag) {
-    cudaError_t e = cudaMalloc(&dbuf, (size_t)nsteps * 8 * sizeof(double));
-    if (e != cudaSuccess) { snprintf(h->err, sizeof(h->err), "cudaMalloc diag: %s", cudaGetErrorString(e)); return 1; }
-  }
-  for (int s = 0; s < nsteps; ++s) {
-    time_integrate_impl(h, *old_idx, *new_idx, h->cfg.dt_dyn, *time_step);
-    // time_advance (time_mod.F90:128-159)
-    if (h->alert_ring) { h->alert_last = (*time_step) * h->cfg.dt_dyn; h->alert_ring = false; }
+  std::vector<double*> dbufs;
+  int rc = 0;
+  if (diag) for_bands(h, [&](gmc_handle* b) {
+    double* d = nullptr;
+    if (cudaMalloc(&d, (size_t)nsteps * 8 * sizeof(double)) != cudaSuccess) rc = 1;
+    cudaMemsetAsync(d, 0, (size_t)nsteps * 8 * sizeof(double), b->stream);
+    dbufs.push_back(d);
+  });
+  for (int s = 0; s < nsteps && !rc; ++s) {
+    rc = time_integrate_impl(h, *old_idx, *new_idx, h->cfg.dt_dyn, *time_step);
+    alert_advance(h, *time_step);   // time_advance (time_mod.F90:128-159)
     int t = *old_idx; *old_idx = *new_idx; *new_idx = t;
     *time_step += 1;
-    if (diag) launch_diag(h, *old_idx, dbuf + (size_t)s * 8);
+    if (diag) { int bi = 0; for_bands(h, [&](gmc_handle* b) { launch_diag(b, *old_idx, dbufs[bi++] + (size_t)s * 8); }); }
   }
-  cudaError_t e = cudaGetLastError();
-  if (e == cudaSuccess && diag) {
-    std::vector<double> tmp((size_t)nsteps * 8);
-    e = cudaMemcpyAsync(tmp.data(), dbuf, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    for (int s = 0; s < nsteps; ++s) diag_to_abi(&tmp[(size_t)s * 8], diag + (size_t)s * 8);
-  }
-  if (dbuf) cudaFree(dbuf);
-  if (e != cudaSuccess) { snprintf(h->err, sizeof(h->err), "run_steps: %s", cudaGetErrorString(e)); return 1; }
-  return hydro_check_flags(h);
+  if (!rc && cudaGetLastError() != cudaSuccess) { snprintf(h->err, sizeof(h->err), "run_steps: CUDA launch error"); rc = 1; }
+  if (!rc && diag) rc = reduce_diag(h, dbufs, nsteps, diag);
+  for (double* d : dbufs) cudaFree(d);
+  if (rc) return 1;
+  int bad = 0;
+  for_bands(h, [&](gmc_handle* b) { if (hydro_check_flags(b)) { bad = 1; if (b != h) snprintf(h->err, sizeof(h->err), "%s", b->err); } });
+  return bad;
 }
 
 int gmc_set_tracers(gmc_handle* h, const double* q) { return hydro_set_tracers(h, q); }

@@ -36,13 +36,17 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (cfg->coriolis_scheme != 1) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d not built (only 1)", cfg->coriolis_scheme); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order != 2) { snprintf(g_create_err, sizeof(g_create_err), "div_damp_order=%d not built (only 2)", cfg->div_damp_order); delete h; return 3; }
   if (cfg->use_smag_damp) { snprintf(g_create_err, sizeof(g_create_err), "use_smag_damp not built"); delete h; return 3; }
-  if (cfg->nranks != 1) { snprintf(g_create_err, sizeof(g_create_err), "nranks>1: use gmc_create_band"); delete h; return 3; }
+  if (cfg->nranks > 1 && !cfg->baroclinic) { snprintf(g_create_err, sizeof(g_create_err), "latitude bands (nranks>1) are built for the hydrostatic core only"); delete h; return 3; }
+  if (cfg->nranks > 1 && cfg->lat_iend - cfg->lat_ibeg + 1 < 6) { snprintf(g_create_err, sizeof(g_create_err), "a latitude band needs at least 6 rows"); delete h; return 3; }
+  if ((cfg->rank == 0) != (cfg->lat_ibeg == 1) || (cfg->rank == cfg->nranks - 1) != (cfg->lat_iend == cfg->nlat)) {
+    snprintf(g_create_err, sizeof(g_create_err), "rank %d of %d does not match rows %d..%d", cfg->rank, cfg->nranks, cfg->lat_ibeg, cfg->lat_iend); delete h; return 3; }
   Geo& g = h->g;
   g.nlon = cfg->nlon; g.nlat = cfg->nlat; g.nlev = cfg->nlev; g.nhalf = cfg->nlat - 1;
   g.jb = cfg->lat_ibeg; g.je = cfg->lat_iend;
   g.has_south = g.jb == 1; g.has_north = g.je == g.nlat;
   g.hjb = g.jb; g.hje = g.has_north ? g.je - 1 : g.je;
-  g.jlo = g.jb - GMC_HL; g.NY = (g.je - g.jb + 1) + 2 * GMC_HL;
+  const int HL = cfg->nranks > 1 ? 6 : GMC_HL;   // band mode: 4 exchanged rows + 2 rows of stencil over-reach
+  g.jlo = g.jb - HL; g.NY = (g.je - g.jb + 1) + 2 * HL;
   g.plane = (long long)g.NY * g.nlon;
   if (g.plane * (g.nlev + 2) >= (1LL << 31)) { snprintf(g_create_err, sizeof(g_create_err), "band too large for 32-bit field indices"); delete h; return 3; }
   cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -71,6 +75,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (!rc) rc = dev_alloc(h, &h->diag_partial, (size_t)7 * (g.je - g.jb + 1) * g.nlev);
   if (!rc) rc = dev_alloc(h, &h->diag_out, 8);
   if (!rc && baro) rc = hydro_alloc(h);
+  if (!rc) rc = halo_alloc(h);
   h->stage_bytes = (size_t)(g.nlon + 2 * cfg->hx) * ((g.je - g.jb + 1) + 2 * cfg->hy) * (g.nlev + 4) * sizeof(double);
   if (!rc) { double* p; rc = dev_alloc(h, &p, h->stage_bytes / sizeof(double)); h->stage_img = p; }
   if (rc) { snprintf(g_create_err, sizeof(g_create_err), "%s", h->err); gmc_destroy(h); return 4; }
@@ -85,7 +90,14 @@ void gmc_destroy(gmc_handle* h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
-  if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->nccl_comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->nccl_comm);
+  if (h->group) {   // the group vector is shared: the last member to go frees it
+    auto* grp = h->group;
+    for (auto& m : *grp) if (m == h) m = nullptr;
+    bool any = false; for (auto m : *grp) any = any || m;
+    if (!any) delete grp;
+  }
+  if (h->stream && h->owns_stream) cudaStreamDestroy(h->stream);
   delete h;
 }
 
@@ -213,6 +225,43 @@ int gmc_get_field(gmc_handle* h, int itime, const char* name, double* buf) {
   else if (n == "gzs") { p = h->gzs; kind = 3; }
   if (!p) { snprintf(h->err, sizeof(h->err), "unknown field %s", name); return 1; }
   return xfer(h, p, buf, kind, 1);
+}
+
+// ---- latitude-band set-up (process_mod.F90:93-139 decompose_domains, 1-D in latitude) --------
+// (a) single process, all bands on one device: link the handles (rank order) into a group;
+//     gmc_prepare_run / gmc_time_integrate / gmc_run_steps / gmc_diagnose on hs[0] then drive all bands.
+int gmc_group_link(gmc_handle** hs, int n) {
+  if (n < 1 || !hs[0]) return 1;
+  auto* grp = new std::vector<gmc_handle*>(hs, hs + n);
+  for (int r = 0; r < n; ++r) {
+    gmc_handle* b = hs[r];
+    if (b->cfg.nranks != n || b->cfg.rank != r || b->cfg.device != hs[0]->cfg.device) {
+      snprintf(hs[0]->err, sizeof(hs[0]->err), "gmc_group_link: handle %d is rank %d of %d on device %d", r, b->cfg.rank, b->cfg.nranks, b->cfg.device);
+      delete grp; return 1; }
+  }
+  for (int r = 0; r < n; ++r) {
+    gmc_handle* b = hs[r];
+    if (r > 0) { if (b->owns_stream && b->stream) cudaStreamDestroy(b->stream); b->stream = hs[0]->stream; b->owns_stream = false; }
+    b->group = grp;
+  }
+  return 0;
+}
+// (b) one process per GPU: rank 0 creates the id, the host broadcasts its 128 bytes (MPI_Bcast /
+//     torch.distributed), every rank calls gmc_nccl_init.
+int gmc_nccl_unique_id(char id[128]) {
+  NcclApi& n = nccl_api();
+  if (!n.ok) return 1;
+  gmc_ncclUniqueId u; if (n.GetUniqueId(&u)) return 1;
+  memcpy(id, u.internal, 128); return 0;
+}
+int gmc_nccl_init(gmc_handle* h, const char id[128]) {
+  NcclApi& n = nccl_api();
+  if (!n.ok) { snprintf(h->err, sizeof(h->err), "libnccl.so.2 not found in the process"); return 1; }
+  gmc_ncclUniqueId u; memcpy(u.internal, id, 128);
+  CUDA_CHECK(cudaSetDevice(h->cfg.device));
+  int rc = n.CommInitRank(&h->nccl_comm, h->cfg.nranks, u, h->cfg.rank);
+  if (rc) { snprintf(h->err, sizeof(h->err), "ncclCommInitRank: %s", n.GetErrorString ? n.GetErrorString(rc) : "error"); h->nccl_comm = nullptr; return 1; }
+  return 0;
 }
 
 int gmc_synchronize(gmc_handle* h) {

@@ -65,6 +65,12 @@ struct gmc_handle {
   double *bcflx = 0, *bcfly = 0, *bcflz = 0, *bdivx = 0, *bdivy = 0, *lon_damp_wgt = 0;
   int q_old = 0, q_new = 1, uv_step = 0, mf_step = 0, we_step = 0, nstep = 1;
   double alert_last = 0, alert_period = 0; bool alert_ring = false;
+  // latitude-band mode (cfg.nranks > 1): packed halo exchange with the two neighbours
+  int H = 0;                          // halo rows exchanged per side
+  double *send_s = 0, *send_n = 0, *recv_s = 0, *recv_n = 0; size_t xbuf_elems = 0;
+  std::vector<gmc_handle*>* group = nullptr;   // single-process band group (all bands on this device/stream)
+  bool owns_stream = true;
+  void* nccl_comm = nullptr;          // one-process-per-GPU mode
   bool mesh_set = false, filters_set[3] = {false, false, false};
   int max_hn = 0;
 };

@@ -56,6 +56,7 @@ struct CflArgs {
   const double *u, *v;                 // batch%u, batch%v
   double *cflx, *cfly, *divx, *divy;
   double dt, radius; int* flags;
+  int jx0, jx1, jy0, jy1;              // rows of the x part (cflx, divx, divy) / the y part (cfly); band mode
 };
 __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -64,7 +65,7 @@ __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
   const long long c = gidx(g, i, j, k);
   const int i1 = i + 1;                       // Fortran index
   const double* __restrict__ hl = M.half_lon + (M.hx - 1);   // hl[l] = half_lon(l), l Fortran index
-  if (j > 1 && j < g.nlat) {
+  if (j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1) {
     const double dx = MJ(M.de_lon, j), cl = MJ(M.full_cos_lat, j);
     const double x0 = a.radius * hl[i1] * cl;
     const double u1 = __ldg(a.u + c);
@@ -84,7 +85,7 @@ __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
     a.divx[c] = (u1 - um) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
     a.divy[c] = (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
   }
-  if (j <= g.nhalf) {
+  if (j <= g.nhalf && j >= a.jy0 && j <= a.jy1) {
     const double dy = MJ(M.de_lat, j);
     const double y0 = a.radius * MJ(M.half_lat, j);
     const double v1 = __ldg(a.v + c);
@@ -232,13 +233,14 @@ struct HflxArgs {
   const double *mx, *my;        // field swept in x / in y
   const double *cflx, *cfly;
   double *mfx, *mfy;
+  int jx0, jx1, jy0, jy1;       // rows of the x flux / half rows of the y flux (band mode)
 };
 __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
   if (i >= g.nlon) return;
   const long long c = gidx(g, i, j, k);
-  if (j > 1 && j < g.nlat) {
+  if (j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1) {
     const double cx = __ldg(a.cflx + c);
     double flux = 0;
     if (cx != 0) {
@@ -256,7 +258,7 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
     }
     a.mfx[c] = flux;
   }
-  if (j <= g.nhalf) {
+  if (j <= g.nhalf && j >= a.jy0 && j <= a.jy1) {
     const double cy = __ldg(a.cfly + c);
     double flux = 0;
     if (cy != 0) {
@@ -273,7 +275,7 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
 }
 
 // Intermediate fields of the inner advective step (ffsl_mod.F90:354-406)
-struct FfslQArgs { const double *q, *qmfx, *qmfy, *divx, *divy, *pole; double *qx, *qy; double dt; };
+struct FfslQArgs { const double *q, *qmfx, *qmfy, *divx, *divy, *pole; double *qx, *qy; double dt; int jy0, jy1; /* rows of qy */ };
 __global__ void __launch_bounds__(128) k_ffsl_q(Geo g, DMesh M, FfslQArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(128) k_ffsl_q(Geo g, DMesh M, FfslQArgs a) {
   const double q = __ldg(a.q + c);
   if (j > 1 && j < g.nlat) {
     a.qx[c] = q - 0.5 * ((__ldg(a.qmfx + c) - ldW(a.qmfx, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j) - __ldg(a.divx + c) * q) * a.dt;
-    a.qy[c] = q - 0.5 * ((__ldg(a.qmfy + c) * MJ(M.le_lat, j) - ldW(a.qmfy, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j) - __ldg(a.divy + c) * q) * a.dt;
+    if (j >= a.jy0 && j <= a.jy1) a.qy[c] = q - 0.5 * ((__ldg(a.qmfy + c) * MJ(M.le_lat, j) - ldW(a.qmfy, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j) - __ldg(a.divy + c) * q) * a.dt;
   } else {
     const double pole = __ldg(a.pole + (j == 1 ? 0 : g.nlev) + k);
     const double t = 0.5 * (pole - __ldg(a.divy + c) * q) * a.dt;

@@ -6,6 +6,7 @@
 #include "kernels_dyn.cuh"
 #include "kernels_update.cuh"
 #include "kernels_hydro.cuh"
+#include "halo.cuh"
 
 static inline dim3 grid3(const gmc_handle* h, int nk) {
   return dim3((h->g.nlon + 127) / 128, h->g.je - h->g.jb + 1, nk);
@@ -25,8 +26,8 @@ static void run_forward_prepare(gmc_handle* h, DState& S) {
 }
 
 static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, int f1, double* out1, int f2, double* out2,
-                       int post = POST_NONE, const double* mdiv = nullptr, double* out_m = nullptr) {
-  const Geo& g = h->g;
+                       int post = POST_NONE, const double* mdiv = nullptr, double* out_m = nullptr, const Geo* gp = nullptr) {
+  const Geo& g = gp ? *gp : h->g;
   FilterArgs a;
   a.in = in; a.half_lat = half_lat; a.nlev = nlev;
   a.f1 = h->filt[f1 >= 0 ? f1 : 0]; a.out1 = out1; a.use_f1 = f1 >= 0;
@@ -59,18 +60,22 @@ static void swm_step(gmc_handle* h, DState& old_, DState& star, DState& nw, doub
   run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr);
 }
 
-static void do_step(gmc_handle* h, int old_, int star, int nw, double dt) {
-  if (h->cfg.baroclinic) hydro_step(h, h->st[old_], h->st[star], h->st[nw], dt);
-  else swm_step(h, h->st[old_], h->st[star], h->st[nw], dt);
+// One step(old, star, new, dt) on every band of this process, then the stage exchange.
+static int do_step(gmc_handle* h, int old_, int star, int nw, double dt) {
+  if (!h->cfg.baroclinic) { swm_step(h, h->st[old_], h->st[star], h->st[nw], dt); return 0; }
+  for_bands(h, [&](gmc_handle* b) { hydro_stage(b, b->st[old_], b->st[star], b->st[nw], dt); });
+  if (halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); })) return 1;
+  for_bands(h, [&](gmc_handle* b) { hydro_after_exchange(b, b->st[nw]); });
+  return 0;
 }
 
 // pc2 / wrfrk3 / euler (time_schemes_mod.F90:244-288)
-static void time_integrator(gmc_handle* h, int old_, int nw, double dt) {
+static int time_integrator(gmc_handle* h, int old_, int nw, double dt) {
   switch (h->cfg.time_scheme) {
-    case GMC_EULER: do_step(h, old_, old_, nw, dt); break;
+    case GMC_EULER: return do_step(h, old_, old_, nw, dt);
     case GMC_PC2:
-      do_step(h, old_, old_, nw, dt / 2.0); do_step(h, old_, nw, 3, dt / 2.0); do_step(h, old_, 3, nw, dt); break;
+      return do_step(h, old_, old_, nw, dt / 2.0) || do_step(h, old_, nw, 3, dt / 2.0) || do_step(h, old_, 3, nw, dt);
     default:
-      do_step(h, old_, old_, nw, dt / 3.0); do_step(h, old_, nw, 3, dt / 2.0); do_step(h, old_, 3, nw, dt); break;
+      return do_step(h, old_, old_, nw, dt / 3.0) || do_step(h, old_, nw, 3, dt / 2.0) || do_step(h, old_, 3, nw, dt);
   }
 }

@@ -18,7 +18,8 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error"]
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error",
+               "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init"]
 
 
 def load_library():
@@ -50,6 +51,9 @@ def load_library():
     lib.gmc_launch_count.argtypes = [V, C.POINTER(C.c_longlong)]
     lib.gmc_last_error.argtypes = [V, C.c_char_p, C.c_int]
     lib.gmc_struct_sizes.argtypes = [I, I]
+    lib.gmc_group_link.argtypes = [C.POINTER(V), C.c_int]
+    lib.gmc_nccl_unique_id.argtypes = [C.c_char_p]
+    lib.gmc_nccl_init.argtypes = [V, C.c_char_p]
     lib.gmc_timer_record.argtypes = [V, C.c_int]
     lib.gmc_timer_elapsed_ms.argtypes = [V, P]
     lib.gmc_profile.argtypes = [V, C.c_int]
@@ -187,3 +191,143 @@ class GmcoreGPU:
             self.close()
         except Exception:
             pass
+
+
+# ---- latitude bands (1-D latitude decomposition, process_mod.F90:93-139) -------------------
+def round_robin(n, nparts):
+    """Rows per part as parallel_types_mod.F90:235-262: the remainder goes to the lowest ranks.
+    Returns [(ibeg, iend)] 1-based inclusive."""
+    base, rem = divmod(n, nparts)
+    out, beg = [], 1
+    for r in range(nparts):
+        cnt = base + (1 if r < rem else 0)
+        out.append((beg, beg + cnt - 1)); beg += cnt
+    return out
+
+
+def band_config(host, rank, nranks, device):
+    cfg = abi.GmcConfig.from_buffer_copy(host.cfg)
+    cfg.lat_ibeg, cfg.lat_iend = round_robin(host.nlat, nranks)[rank]
+    cfg.rank, cfg.nranks, cfg.device = rank, nranks, device
+    return cfg
+
+
+def band_slice(host, cfg, a, loc):
+    """Rows lat_ibeg-hy .. lat_iend+hy (half-lat: .. half_iend+hy) of a global halo'd array, contiguous."""
+    hy = host.hy
+    half = loc.split("+")[0] in ("lat", "vtx")
+    jend = cfg.lat_iend - 1 if (half and cfg.lat_iend == host.nlat) else cfg.lat_iend
+    sl = slice(cfg.lat_ibeg - 1, jend + 2 * hy)
+    return np.ascontiguousarray(a[sl] if loc == "2d" else a[:, sl])
+
+
+class GmcoreBand(GmcoreGPU):
+    """One latitude band = one handle (what one MPI rank of GMCORE owns)."""
+
+    def __init__(self, host, rank, nranks, device=0):
+        self.lib = load_library()
+        self.host = host
+        self.cfg = band_config(host, rank, nranks, device)
+        self.h = C.c_void_p()
+        rc = self.lib.gmc_create(C.byref(self.cfg), C.byref(self.h))
+        if rc != 0:
+            raise RuntimeError("gmc_create failed: " + self.lib.gmc_create_error().decode())
+        self._chk(self.lib.gmc_set_mesh(self.h, C.byref(host.mesh_vectors)))
+        for which, (ngl, wl, ldl, nga, wa, lda) in enumerate(host.filters):
+            self._chk(self.lib.gmc_set_filters(self.h, which, abi.iptr(ngl), abi.dptr(wl), ldl, abi.iptr(nga), abi.dptr(wa), lda))
+        self.old, self.new, self.time_step = C.c_int(1), C.c_int(2), C.c_int(0)
+
+    def _b(self, a, loc):
+        return None if a is None else band_slice(self.host, self.cfg, a, loc)
+
+    def set_state(self, ic, itime=1):
+        self._chk(self.lib.gmc_set_static(self.h, abi.dptr(self._b(ic["gzs"], "2d"))))
+        self._chk(self.lib.gmc_upload_state(self.h, itime, abi.dptr(self._b(ic["u_lon"], "lon")), abi.dptr(self._b(ic["v_lat"], "lat")),
+                                            abi.dptr(self._b(ic["pt_or_gz"], "cell")), abi.dptr(self._b(ic.get("phs"), "2d"))))
+
+    def set_tracers(self, q):
+        self._chk(self.lib.gmc_set_tracers(self.h, abi.dptr(np.ascontiguousarray(np.stack([self._b(x, "cell") for x in q])))))
+
+    def band_shape(self, loc):
+        s = list(self.host.shape(loc))
+        half = loc.split("+")[0] in ("lat", "vtx")
+        jend = self.cfg.lat_iend - 1 if (half and self.cfg.lat_iend == self.host.nlat) else self.cfg.lat_iend
+        s[-2] = jend - self.cfg.lat_ibeg + 1 + 2 * self.host.hy
+        return tuple(s)
+
+    def field(self, name, itime=None):
+        """Band-local halo'd array of a named field."""
+        itime = self.old.value if itime is None else itime
+        a = np.zeros(self.band_shape(FIELD_LOC[name]))
+        self._chk(self.lib.gmc_get_field(self.h, itime, name.encode(), abi.dptr(a)))
+        return a
+
+    def get_tracers(self):
+        q = np.zeros((self.host.cfg.ntracers,) + self.band_shape("cell"))
+        self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
+        return q
+
+
+def scatter_rows(host, cfg, band_arr, glob, loc):
+    """Copy the owned rows of a band-local halo'd array into the global halo'd array."""
+    hy = host.hy
+    half = loc.split("+")[0] in ("lat", "vtx")
+    jend = cfg.lat_iend - 1 if (half and cfg.lat_iend == host.nlat) else cfg.lat_iend
+    n = jend - cfg.lat_ibeg + 1
+    if loc == "2d":
+        glob[cfg.lat_ibeg - 1 + hy: cfg.lat_ibeg - 1 + hy + n] = band_arr[hy:hy + n]
+    else:
+        glob[:, cfg.lat_ibeg - 1 + hy: cfg.lat_ibeg - 1 + hy + n] = band_arr[:, hy:hy + n]
+
+
+class GmcoreBandGroup:
+    """All latitude bands in ONE process on ONE device (gmc_group_link): the single-GPU stand-in for
+    the N-rank run, used to check that results do not depend on the band count."""
+
+    def __init__(self, host, nbands, device=0):
+        self.host = host
+        self.bands = [GmcoreBand(host, r, nbands, device) for r in range(nbands)]
+        self.lib = self.bands[0].lib
+        arr = (C.c_void_p * nbands)(*[b.h for b in self.bands])
+        if self.lib.gmc_group_link(arr, nbands) != 0:
+            self.bands[0]._chk(1)
+        self.lead = self.bands[0]
+
+    def set_state(self, ic):
+        for b in self.bands:
+            b.set_state(ic)
+
+    def set_tracers(self, q):
+        for b in self.bands:
+            b.set_tracers(q)
+
+    def prepare_run(self):
+        self.lead.prepare_run()
+
+    def run_steps(self, n, diag=True):
+        d = self.lead.run_steps(n, diag)
+        for b in self.bands[1:]:
+            b.old.value, b.new.value, b.time_step.value = self.lead.old.value, self.lead.new.value, self.lead.time_step.value
+        return d
+
+    def diagnose(self):
+        return self.lead.diagnose()
+
+    def field(self, name):
+        loc = FIELD_LOC[name]
+        g = np.zeros(self.host.shape(loc))
+        for b in self.bands:
+            scatter_rows(self.host, b.cfg, b.field(name), g, loc)
+        return g
+
+    def get_tracers(self):
+        g = np.zeros((self.host.cfg.ntracers,) + self.host.shape("cell"))
+        for b in self.bands:
+            qb = b.get_tracers()
+            for l in range(g.shape[0]):
+                scatter_rows(self.host, b.cfg, qb[l], g[l], "cell")
+        return g
+
+    def close(self):
+        for b in self.bands:
+            b.close()

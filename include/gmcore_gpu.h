@@ -124,6 +124,16 @@ int gmc_diagnose(gmc_handle* h, int itime, double out[8]);
  * unknown name. */
 int gmc_get_field(gmc_handle* h, int itime, const char* name, double* buf);
 
+/* Latitude bands (the 1-D latitude decomposition of process_mod.F90:93-139; halo exchange =
+ * fill_halo S/N of parallel_mod.F90:501-527).  Each band is one handle created with its own
+ * lat_ibeg/lat_iend, rank, nranks (hydrostatic core).  Either link all bands of a single process
+ * (same device) with gmc_group_link and drive them through hs[0], or run one process per GPU:
+ * rank 0 calls gmc_nccl_unique_id, the host broadcasts the 128 bytes (MPI_Bcast in GMCORE),
+ * every rank calls gmc_nccl_init; diagnose then returns globally reduced sums on every rank. */
+int gmc_group_link(gmc_handle** hs, int n);
+int gmc_nccl_unique_id(char id[128]);
+int gmc_nccl_init(gmc_handle* h, const char id[128]);
+
 int gmc_synchronize(gmc_handle* h);
 /* Device milliseconds spent in, and kernels launched by, calls on this handle
  * since the last reset (CUDA events on the handle's stream). */
