@@ -267,6 +267,36 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
         return q
 
+    def download_state(self, itime=None):
+        itime = self.old.value if itime is None else itime
+        u = np.zeros(self.band_shape("lon")); v = np.zeros(self.band_shape("lat")); s = np.zeros(self.band_shape("cell"))
+        phs = np.zeros(self.band_shape("2d"))
+        self._chk(self.lib.gmc_download_state(self.h, itime, abi.dptr(u), abi.dptr(v), abi.dptr(s), abi.dptr(phs)))
+        return {"u_lon": u, "v_lat": v, "pt_or_gz": s, "phs": phs}
+
+    # one process per GPU: NCCL bootstrap (the host broadcasts the id; MPI_Bcast in GMCORE)
+    def nccl_unique_id(self):
+        buf = C.create_string_buffer(128)
+        if self.lib.gmc_nccl_unique_id(buf) != 0:
+            raise RuntimeError("gmc_nccl_unique_id failed (libnccl not loaded)")
+        return buf.raw
+
+    def nccl_init(self, uid):
+        self._chk(self.lib.gmc_nccl_init(self.h, uid))
+
+
+def make_band_nccl(host, rank, world, device):
+    """torch.distributed-launched rank -> its latitude band with the NCCL transport set up."""
+    import torch
+    import torch.distributed as dist
+    band = GmcoreBand(host, rank, world, device)
+    t = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{device}")
+    if rank == 0:
+        t = torch.frombuffer(bytearray(band.nccl_unique_id()), dtype=torch.uint8).to(f"cuda:{device}")
+    dist.broadcast(t, src=0)
+    band.nccl_init(bytes(t.cpu().numpy().tobytes()))
+    return band
+
 
 def scatter_rows(host, cfg, band_arr, glob, loc):
     """Copy the owned rows of a band-local halo'd array into the global halo'd array."""
