@@ -287,7 +287,6 @@ def _main(out):
     gpu2 = make_band_nccl(host, rank, world, local) if banded else GmcoreGPU(host, device=local)
     icp = {k: pin[k][0] if k in pin else None for k in ic}
     h2d = sum(pin[k][0].nbytes for k in pin)
-    out = {"u_lon": pinned_like(ic["u_lon"]), "v_lat": pinned_like(ic["v_lat"]), "s": pinned_like(ic["pt_or_gz"])}
     barrier(world); torch.cuda.synchronize()
     t0 = time.perf_counter()
     gpu2.set_state(icp)
