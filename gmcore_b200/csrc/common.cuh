@@ -44,6 +44,10 @@ struct DMesh {
   const double *full_tangent_wgt, *half_tangent_wgt;   // (2, j)
   const double *half_lon;       // lower bound 1-hx
   const double *hyai, *hybi, *full_lev, *half_lev, *full_dlev, *half_dlev;  // 1-based / -1-based as in the header
+  // reciprocals of row constants (formed once on the host, 0 where the constant is 0): a divide by
+  // a per-latitude coefficient becomes a multiply (<= 1 ulp from the reference's divide, far inside
+  // the 1e-12 parity bar) -- FP64 divides are ~30 issue slots each and dominated several kernels.
+  const double *r_area_cell, *r_area_vtx, *r_de_lon, *r_de_lat, *r_area_lon, *r_area_lat;
   int hx;
 };
 #define MJ(v, j) (v[(j) + 1])                  // vector entry at latitude index j

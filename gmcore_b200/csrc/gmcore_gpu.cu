@@ -117,6 +117,16 @@ int gmc_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
   if (!rc) rc = dev_upload(h, &M.full_tangent_wgt, mv->full_tangent_wgt, 2 * nf);
   if (!rc) rc = dev_upload(h, &M.half_tangent_wgt, mv->half_tangent_wgt, 2 * nh);
   if (!rc) rc = dev_upload(h, &M.half_lon, mv->half_lon, nl);
+  {
+    auto recip = [&](const double** dst, const double* src, size_t n) {
+      std::vector<double> r(n);
+      for (size_t q = 0; q < n; ++q) r[q] = src[q] != 0.0 ? 1.0 / src[q] : 0.0;
+      if (!rc) rc = dev_upload(h, dst, r.data(), n);
+    };
+    recip(&M.r_area_cell, mv->area_cell, nf); recip(&M.r_area_vtx, mv->area_vtx, nh);
+    recip(&M.r_de_lon, mv->de_lon, nf); recip(&M.r_de_lat, mv->de_lat, nh);
+    recip(&M.r_area_lon, mv->area_lon, nf); recip(&M.r_area_lat, mv->area_lat, nh);
+  }
   if (c.baroclinic) {
     if (!mv->hyai) { snprintf(h->err, sizeof(h->err), "hybrid coefficients missing"); return 1; }
     if (!rc) rc = dev_upload(h, &M.hyai, mv->hyai, (size_t)c.nlev + 1);

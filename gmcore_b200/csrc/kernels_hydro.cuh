@@ -38,8 +38,8 @@ __device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1
   const double dfl = slope_mono(fm2, fm1, f);
   df = slope_mono(fm1, f, fp1);
   const double dfr = slope_mono(f, fp1, fp2);
-  fl = 0.5 * (fm1 + f) + (dfl - df) / 6.0;
-  double fr = 0.5 * (fp1 + f) + (df - dfr) / 6.0;
+  fl = 0.5 * (fm1 + f) + (dfl - df) * (1.0 / 6.0);
+  double fr = 0.5 * (fp1 + f) + (df - dfr) * (1.0 / 6.0);
   fl = f - fsign(dmin(fabs(df), fabs(fl - f)), df);
   fr = f + fsign(dmin(fabs(df), fabs(fr - f)), df);
   f6 = 6 * f - 3 * (fl + fr);
@@ -48,7 +48,7 @@ __device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1
 // The PPM flux integral shared by the three directions (ffsl_mod.F90:831-851).
 __device__ __forceinline__ double ppm_integral(double sm, double ml, double dm, double m6, double s1, double s2) {
   const double ds1 = s2 - s1, ds2 = s2 * s2 - s1 * s1, ds3 = s2 * s2 * s2 - s1 * s1 * s1;
-  return sm + ml * ds1 + 0.5 * dm * ds2 + m6 * (ds2 / 2.0 - ds3 / 3.0);
+  return sm + ml * ds1 + 0.5 * dm * ds2 + m6 * (ds2 * 0.5 - ds3 * (1.0 / 3.0));
 }
 
 // ---- RK4 departure-point CFL + divx/divy (adv_batch_mod.F90:253-373) ---------------
@@ -62,43 +62,53 @@ __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
   if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
+  const int c = gidx(g, i, j, k), rb = c - i;
   const int i1 = i + 1;                       // Fortran index
   const double* __restrict__ hl = M.half_lon + (M.hx - 1);   // hl[l] = half_lon(l), l Fortran index
-  if (j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1) {
-    const double dx = MJ(M.de_lon, j), cl = MJ(M.full_cos_lat, j);
-    const double x0 = a.radius * hl[i1] * cl;
-    const double u1 = __ldg(a.u + c);
-    double x = x0 + a.dt / 2 * u1;
-    double us[3];
+  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;   // block-uniform
+  const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
+  const double* __restrict__ ur = a.u + rb;
+  // The x and y RK4 chains are independent: their three dependent gathers are interleaved stage
+  // by stage so that both are in flight together.  Divides by the row constants dx, dy,
+  // area_cell are multiplies by host-formed reciprocals.
+  const double rdx = MJ(M.r_de_lon, j), cl = MJ(M.full_cos_lat, j), rcl = a.radius * cl;
+  const double rdy = doy ? MJ(M.r_de_lat, j) : 0.0;
+  const double u1 = dox ? __ldg(ur + i) : 0.0;
+  const double v1 = doy ? __ldg(a.v + c) : 0.0;
+  const double x0 = rcl * hl[i1], y0 = doy ? a.radius * MJ(M.half_lat, j) : 0.0;
+  double x = x0 + a.dt / 2 * u1, y = y0 + a.dt / 2 * v1;
+  double us[3], vs[3];
 #pragma unroll
-    for (int s = 0; s < 3; ++s) {
-      const int l = (int)floor(i1 + (x - x0) / dx);
-      const double ua = ldW(a.u, g, wrapi(l - 1, g.nlon), j, k), ub = ldW(a.u, g, wrapi(l, g.nlon), j, k);
-      us[s] = ((a.radius * hl[l + 1] * cl - x) * ua + (x - a.radius * hl[l] * cl) * ub) / dx;
-      x = x0 + (s == 1 ? a.dt : a.dt / 2) * us[s];
+  for (int s = 0; s < 3; ++s) {
+    const double h = s == 1 ? a.dt : a.dt / 2;
+    double ua = 0, ub = 0, va = 0, vb = 0;
+    int lx = 0, ly = 0; bool inr = false;
+    if (dox) {
+      lx = (int)floor(i1 + (x - x0) * rdx);
+      ua = __ldg(ur + wrapi(lx - 1, g.nlon)); ub = __ldg(ur + wrapi(lx, g.nlon));
     }
-    const double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) / 6 * a.dt / dx;
+    if (doy) {
+      ly = (int)floor(j + (y - y0) * rdy);
+      inr = !(ly < 1 || ly > g.nhalf - 1);
+      if (inr) { va = ldW(a.v, g, i, ly, k); vb = ldW(a.v, g, i, ly + 1, k); }
+    }
+    if (dox) { us[s] = ((rcl * hl[lx + 1] - x) * ua + (x - rcl * hl[lx]) * ub) * rdx; x = x0 + h * us[s]; }
+    if (doy) {
+      vs[s] = inr ? ((a.radius * MJ(M.half_lat, ly + 1) - y) * va + (y - a.radius * MJ(M.half_lat, ly)) * vb) * rdy : v1;
+      y = y0 + h * vs[s];
+    }
+  }
+  if (dox) {
+    const double rac = MJ(M.r_area_cell, j);
+    const double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) * (1.0 / 6.0) * a.dt * rdx;
     a.cflx[c] = cf;
     if (fabs(cf) > M.hx) atomicOr(a.flags, 1);
-    const double um = ldW(a.u, g, i - 1, j, k);
-    a.divx[c] = (u1 - um) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
-    a.divy[c] = (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+    const double um = __ldg(ur + wrapi(i - 1, g.nlon));
+    a.divx[c] = (u1 - um) * MJ(M.le_lon, j) * rac;
+    a.divy[c] = (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) * rac;
   }
-  if (j <= g.nhalf && j >= a.jy0 && j <= a.jy1) {
-    const double dy = MJ(M.de_lat, j);
-    const double y0 = a.radius * MJ(M.half_lat, j);
-    const double v1 = __ldg(a.v + c);
-    double y = y0 + a.dt / 2 * v1;
-    double vs[3];
-#pragma unroll
-    for (int s = 0; s < 3; ++s) {
-      const int l = (int)floor(j + (y - y0) / dy);
-      if (l < 1 || l > g.nhalf - 1) vs[s] = v1;
-      else vs[s] = ((a.radius * MJ(M.half_lat, l + 1) - y) * ldW(a.v, g, i, l, k) + (y - a.radius * MJ(M.half_lat, l)) * ldW(a.v, g, i, l + 1, k)) / dy;
-      y = y0 + (s == 1 ? a.dt : a.dt / 2) * vs[s];
-    }
-    const double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) / 6 * a.dt / dy;
+  if (doy) {
+    const double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) * (1.0 / 6.0) * a.dt * rdy;
     a.cfly[c] = cf;
     if (fabs(cf) > 1) atomicOr(a.flags, 2);
   }
@@ -239,36 +249,49 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
   if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
-  if (j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1) {
-    const double cx = __ldg(a.cflx + c);
+  const int c = gidx(g, i, j, k), rb = c - i;
+  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;
+  const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
+  // Phase 1: the four independent loads (CFL numbers and advecting velocities) go out together,
+  // phase 2: both 5-point upwind stencils -- two dependent memory round trips per thread, not four.
+  const double cx = dox ? __ldg(a.cflx + c) : 0.0;
+  const double cy = doy ? __ldg(a.cfly + c) : 0.0;
+  const double uu = dox ? __ldg(a.u + c) : 0.0;
+  const double vv = doy ? __ldg(a.v + c) : 0.0;
+  const int ci = (int)cx;
+  const int iu = wrapi(cx > 0 ? i - ci : i - ci + 1, g.nlon);
+  const int ju = cy > 0 ? j : j + 1;
+  double x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0, y0 = 0, y1 = 0, y2 = 0, y3 = 0, y4 = 0;
+  const double* __restrict__ mxr = a.mx + rb;
+  if (cx != 0) {
+    x0 = __ldg(mxr + wrapi(iu - 2, g.nlon)); x1 = __ldg(mxr + wrapi(iu - 1, g.nlon)); x2 = __ldg(mxr + iu);
+    x3 = __ldg(mxr + wrapi(iu + 1, g.nlon)); x4 = __ldg(mxr + wrapi(iu + 2, g.nlon));
+  }
+  if (cy != 0) {
+    y0 = ldF(a.my, g, i, ju - 2, k); y1 = ldF(a.my, g, i, ju - 1, k); y2 = ldF(a.my, g, i, ju, k);
+    y3 = ldF(a.my, g, i, ju + 1, k); y4 = ldF(a.my, g, i, ju + 2, k);
+  }
+  if (dox) {
     double flux = 0;
     if (cx != 0) {
-      const int ci = (int)cx;
       const double cf = cx - ci;
-      int iu; double s1, s2, sm = 0;
-      if (cx > 0) { iu = i - ci; s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += ldW(a.mx, g, wrapi(l, g.nlon), j, k); }
-      else { iu = i - ci + 1; s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += ldW(a.mx, g, wrapi(l, g.nlon), j, k); }
-      iu = wrapi(iu, g.nlon);
+      double s1, s2, sm = 0;
+      if (cx > 0) { s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, g.nlon)); }
+      else { s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, g.nlon)); }
       double ml, dm, m6;
-      ppm(ldW(a.mx, g, iu - 2, j, k), ldW(a.mx, g, iu - 1, j, k), ldW(a.mx, g, iu, j, k), ldW(a.mx, g, iu + 1, j, k),
-          ldW(a.mx, g, iu + 2, j, k), ml, dm, m6);
-      const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);
-      flux = (cx > 0 ? __ldg(a.u + c) : -__ldg(a.u + c)) * integ / cx;
+      ppm(x0, x1, x2, x3, x4, ml, dm, m6);
+      flux = (cx > 0 ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2) / cx;
     }
     a.mfx[c] = flux;
   }
-  if (j <= g.nhalf && j >= a.jy0 && j <= a.jy1) {
-    const double cy = __ldg(a.cfly + c);
+  if (doy) {
     double flux = 0;
     if (cy != 0) {
-      int ju; double s1, s2;
-      if (cy > 0) { ju = j; s1 = 1 - cy; s2 = 1; } else { ju = j + 1; s1 = 0; s2 = -cy; }
+      double s1, s2;
+      if (cy > 0) { s1 = 1 - cy; s2 = 1; } else { s1 = 0; s2 = -cy; }
       double ml, dm, m6;
-      ppm(ldF(a.my, g, i, ju - 2, k), ldF(a.my, g, i, ju - 1, k), ldF(a.my, g, i, ju, k), ldF(a.my, g, i, ju + 1, k),
-          ldF(a.my, g, i, ju + 2, k), ml, dm, m6);
-      const double integ = ppm_integral(0.0, ml, dm, m6, s1, s2);
-      flux = (cy > 0 ? __ldg(a.v + c) : -__ldg(a.v + c)) * integ / cy;
+      ppm(y0, y1, y2, y3, y4, ml, dm, m6);
+      flux = (cy > 0 ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2) / cy;
     }
     a.mfy[c] = flux;
   }

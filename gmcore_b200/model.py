@@ -26,7 +26,8 @@ def load_library():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = os.path.join(_LIBDIR, "libgmcore_b200.so")
+    # GMCORE_B200_LIB: alternative build of the same library (kernel A/B experiments, tools/kprof.py)
+    path = os.environ.get("GMCORE_B200_LIB") or os.path.join(_LIBDIR, "libgmcore_b200.so")
     if not os.path.exists(path):
         raise RuntimeError(f"{path} missing: the CUDA extension is not built (make gpu); no CPU fallback exists")
     lib = C.CDLL(path)
