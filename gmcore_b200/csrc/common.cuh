@@ -35,7 +35,22 @@ __device__ __forceinline__ int wrapi(int i, int nlon) {
 
 // Per-latitude coefficient vectors (mesh_type, src/dynamics/mesh_mod.F90:84-110),
 // stored with the reference's lower bound 1-hy = -1, so entry j lives at [j+1].
+// All per-latitude constants of one row packed together (array of structs over j, same lower
+// bound as the vectors: entry j at rows[j+1]).  A kernel forms ONE address (&rows[j+1]) and reaches
+// every coefficient of rows j-1, j, j+1 with immediate offsets, instead of one 64-bit address
+// computation per coefficient vector (the integer pipe was the busiest one in the stencil kernels).
+struct RowCoef {
+  // full-lat row j
+  double area_cell, r_area_cell, area_lon_west, area_lon_east, area_lon_north, area_lon_south, r_area_lon;
+  double de_lon, r_de_lon, le_lon, full_cos_lat, full_sin_lat, ftw1, ftw2, sub1, sub2;
+  // half-lat row j
+  double area_lat_west, area_lat_east, area_lat_north, area_lat_south, r_area_lat, r_area_vtx;
+  double de_lat, r_de_lat, le_lat, half_f, htw1, htw2, half_lat, area_lon, area_lat, pad_;
+};
+static_assert(sizeof(RowCoef) == 256, "RowCoef is one 256-byte line pair");
+
 struct DMesh {
+  const RowCoef* rows;
   const double *full_lat, *half_lat, *full_cos_lat, *half_cos_lat, *full_sin_lat, *half_sin_lat;
   const double *area_cell, *area_lon, *area_lon_west, *area_lon_east, *area_lon_north, *area_lon_south;
   const double *area_lat, *area_lat_west, *area_lat_east, *area_lat_north, *area_lat_south, *area_vtx;
@@ -58,6 +73,18 @@ struct DFilter {
   const int* ngrid_lat; const double* wgt_lat; int ld_lat;
   int max_hn;
 };
+
+// 2-D thread tiles for the horizontal stencil kernels: TBX threads along longitude x (128/TBX) latitude
+// rows per block, so that the j-1 / j+1 neighbours of a warp's row are fetched by warps of the
+// same block (L1 hits instead of L2 round trips).
+#ifndef TBX
+#define TBX 32
+#endif
+static inline dim3 tile_block() { return dim3(TBX, 128 / TBX, 1); }
+static inline dim3 tile_grid(const Geo& g, int nk) {
+  const dim3 b = tile_block();
+  return dim3((g.nlon + b.x - 1) / b.x, (g.je - g.jb + 1 + b.y - 1) / b.y, nk);
+}
 
 #define CUDA_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { \
   snprintf(h->err, sizeof(h->err), "%s:%d %s: %s", __FILE__, __LINE__, #x, cudaGetErrorString(e_)); return 1; } } while (0)

@@ -126,6 +126,28 @@ int gmc_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
     recip(&M.r_area_cell, mv->area_cell, nf); recip(&M.r_area_vtx, mv->area_vtx, nh);
     recip(&M.r_de_lon, mv->de_lon, nf); recip(&M.r_de_lat, mv->de_lat, nh);
     recip(&M.r_area_lon, mv->area_lon, nf); recip(&M.r_area_lat, mv->area_lat, nh);
+    std::vector<RowCoef> rows(nf);
+    auto rc1 = [](double x) { return x != 0.0 ? 1.0 / x : 0.0; };
+    for (size_t q = 0; q < nf; ++q) {
+      RowCoef& r = rows[q]; memset(&r, 0, sizeof(r));
+      r.area_cell = mv->area_cell[q]; r.r_area_cell = rc1(r.area_cell);
+      r.area_lon_west = mv->area_lon_west[q]; r.area_lon_east = mv->area_lon_east[q];
+      r.area_lon_north = mv->area_lon_north[q]; r.area_lon_south = mv->area_lon_south[q];
+      r.area_lon = mv->area_lon[q]; r.r_area_lon = rc1(r.area_lon);
+      r.de_lon = mv->de_lon[q]; r.r_de_lon = rc1(r.de_lon); r.le_lon = mv->le_lon[q];
+      r.full_cos_lat = mv->full_cos_lat[q]; r.full_sin_lat = mv->full_sin_lat[q];
+      r.ftw1 = mv->full_tangent_wgt[2 * q]; r.ftw2 = mv->full_tangent_wgt[2 * q + 1];
+      r.sub1 = mv->area_subcell[2 * q]; r.sub2 = mv->area_subcell[2 * q + 1];
+      if (q < nh) {
+        r.area_lat_west = mv->area_lat_west[q]; r.area_lat_east = mv->area_lat_east[q];
+        r.area_lat_north = mv->area_lat_north[q]; r.area_lat_south = mv->area_lat_south[q];
+        r.area_lat = mv->area_lat[q]; r.r_area_lat = rc1(r.area_lat); r.r_area_vtx = rc1(mv->area_vtx[q]);
+        r.de_lat = mv->de_lat[q]; r.r_de_lat = rc1(r.de_lat); r.le_lat = mv->le_lat[q];
+        r.half_f = mv->half_f[q]; r.htw1 = mv->half_tangent_wgt[2 * q]; r.htw2 = mv->half_tangent_wgt[2 * q + 1];
+        r.half_lat = mv->half_lat[q];
+      }
+    }
+    if (!rc) rc = dev_upload(h, &M.rows, rows.data(), nf);
   }
   if (c.baroclinic) {
     if (!mv->hyai) { snprintf(h->err, sizeof(h->err), "hybrid coefficients missing"); return 1; }

@@ -26,6 +26,16 @@ __device__ __forceinline__ double ldW(const double* __restrict__ p, const Geo& g
   return __ldg(p + gidx(g, wrapi(i, g.nlon), j, k));
 }
 
+// Blocks whose i-1 .. i+1 (or +-2) neighbourhood stays inside the row skip the periodic wrap: the
+// neighbour offsets become compile-time immediates off one base address per (array, row).
+template <bool EDGE> __device__ __forceinline__ int wrapE(int i, int n) { return EDGE ? wrapi(i, n) : i; }
+__device__ __forceinline__ bool edge_block(int n, int reach) {
+  return blockIdx.x == 0 || (int)((blockIdx.x + 1) * blockDim.x) + reach > n;
+}
+// a / b for a field divisor: correctly rounded reciprocal then one multiply (<= 1 ulp off the IEEE
+// divide, about half its instruction count).
+__device__ __forceinline__ double qdiv(double a, double b) { return a * __drcp_rn(b); }
+
 // m_lon / m_lat / m_vtx are pure functions of m (interp_mod.F90:233-275,438-463);
 // they are recomputed where needed instead of being stored (bit-identical).
 __device__ __forceinline__ double m_lon_at(const double* __restrict__ m, const Geo& g, int i, int j, int k) {
@@ -55,54 +65,73 @@ struct Fwd1Args {
 
 // K1: calc_mf (:545-610) + calc_ke (:234-317) + calc_div (:368-377) + calc_vor/calc_pv
 // (:630-639,693-699) on all non-pole-special points.
-__global__ void __launch_bounds__(128) k_fwd1(Geo g, DMesh M, Fwd1Args a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
-  const bool pole_row = (j == 1 || j == g.nlat);
-  if (!pole_row) {
+#ifndef FWD1_MINB
+#define FWD1_MINB 8
+#endif
+template <bool EDGE> __device__ __forceinline__ void fwd1_body(const Geo& g, const DMesh& M, const Fwd1Args& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k);
+  const int dm = wrapE<EDGE>(i - 1, n) - i, dp = wrapE<EDGE>(i + 1, n) - i;   // -1 / +1 away from the row ends
+  const bool full = j > 1 && j < g.nlat;     // non-pole full-lat row (warp-uniform)
+  const bool half = j <= g.nhalf;
+  // One memory phase: the 20 distinct neighbours of u, v, m are loaded up front into registers
+  // (rows j-1 and j+1 always exist on the device: >= 2 halo rows); everything below is register
+  // arithmetic in the reference's operation order.
+  const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
+  const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
+  const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
+  const double m_m = __ldg(mr + dm), m_0 = __ldg(mr), m_p = __ldg(mr + dp);
+  const double m_mn = __ldg(mr + n + dm), m_0n = __ldg(mr + n), m_pn = __ldg(mr + n + dp);
+  double u_ms = 0, u_0s = 0, v_m = 0, v_ms = 0, v_0s = 0, v_ps = 0, m_0s = 0, m_ps = 0;
+  if (full) {
+    u_ms = __ldg(ur - n + dm); u_0s = __ldg(ur - n);
+    v_m = __ldg(vr + dm); v_ms = __ldg(vr - n + dm); v_0s = __ldg(vr - n); v_ps = __ldg(vr - n + dp);
+    m_0s = __ldg(mr - n); m_ps = __ldg(mr - n + dp);
+  }
+  const double mlon = (m_0 + m_p) * 0.5;            // m_lon(i,j)
+  const double mlat = (m_0 + m_0n) * 0.5;           // m_lat(i,j)
+  if (full) {
     // full-lat, non-pole row: mfx_lon, v_lon, ke, div
-    const double u0 = ldW(a.u, g, i, j, k), um = ldW(a.u, g, i - 1, j, k);
-    const double v0 = ldW(a.v, g, i, j, k), vs = ldW(a.v, g, i, j - 1, k);
-    const double mlon = m_lon_at(a.m, g, i, j, k);
-    a.mfx_lon[c] = mlon * u0;
-    const double mfy_lon = MJ2(M.full_tangent_wgt, 1, j) * (mfy_at(a.m, a.v, g, i, j - 1, k) + mfy_at(a.m, a.v, g, i + 1, j - 1, k)) +
-                           MJ2(M.full_tangent_wgt, 2, j) * (mfy_at(a.m, a.v, g, i, j, k) + mfy_at(a.m, a.v, g, i + 1, j, k));
-    a.v_lon[c] = mfy_lon / mlon;
-    double ke = (MJ(M.area_lon_west, j) * (um * um) + MJ(M.area_lon_east, j) * (u0 * u0) +
-                 MJ(M.area_lat_north, j - 1) * (vs * vs) + MJ(M.area_lat_south, j) * (v0 * v0)) / MJ(M.area_cell, j);
+    const double rac = R->r_area_cell;
+    a.mfx_lon[c] = mlon * u_0;
+    const double mfy_lon = R->ftw1 * (((m_0s + m_0) * 0.5) * v_0s + ((m_ps + m_p) * 0.5) * v_ps) +
+                           R->ftw2 * (mlat * v_0 + ((m_p + m_pn) * 0.5) * v_p);
+    a.v_lon[c] = qdiv(mfy_lon, mlon);
+    double ke = (R->area_lon_west * (u_m * u_m) + R->area_lon_east * (u_0 * u_0) +
+                 R[-1].area_lat_north * (v_0s * v_0s) + R->area_lat_south * (v_0 * v_0)) * rac;
     if (a.ke_scheme == 2) {
-      const double vm = ldW(a.v, g, i - 1, j, k), vp = ldW(a.v, g, i + 1, j, k);
-      const double vsm = ldW(a.v, g, i - 1, j - 1, k), vsp = ldW(a.v, g, i + 1, j - 1, k);
-      const double umn = ldW(a.u, g, i - 1, j + 1, k), u0n = ldW(a.u, g, i, j + 1, k);
-      const double ums = ldW(a.u, g, i - 1, j - 1, k), u0s = ldW(a.u, g, i, j - 1, k);
-      const double kv1 = (MJ(M.area_lat_east, j) * (vm * vm) + MJ(M.area_lat_west, j) * (v0 * v0) +
-                          MJ(M.area_lon_north, j) * (um * um) + MJ(M.area_lon_south, j + 1) * (umn * umn)) / MJ(M.area_vtx, j);
-      const double kv2 = (MJ(M.area_lat_east, j - 1) * (vsm * vsm) + MJ(M.area_lat_west, j - 1) * (vs * vs) +
-                          MJ(M.area_lon_north, j - 1) * (ums * ums) + MJ(M.area_lon_south, j) * (um * um)) / MJ(M.area_vtx, j - 1);
-      const double kv3 = (MJ(M.area_lat_east, j - 1) * (vs * vs) + MJ(M.area_lat_west, j - 1) * (vsp * vsp) +
-                          MJ(M.area_lon_north, j - 1) * (u0s * u0s) + MJ(M.area_lon_south, j) * (u0 * u0)) / MJ(M.area_vtx, j - 1);
-      const double kv4 = (MJ(M.area_lat_east, j) * (v0 * v0) + MJ(M.area_lat_west, j) * (vp * vp) +
-                          MJ(M.area_lon_north, j) * (u0 * u0) + MJ(M.area_lon_south, j + 1) * (u0n * u0n)) / MJ(M.area_vtx, j);
-      ke = (1.0 - a.ke_cell_wgt) * ((kv1 + kv4) * MJ2(M.area_subcell, 2, j) + (kv2 + kv3) * MJ2(M.area_subcell, 1, j)) / MJ(M.area_cell, j) +
-           a.ke_cell_wgt * ke;
+      const double rv = R->r_area_vtx, rvs = R[-1].r_area_vtx;
+      const double ae = R->area_lat_east, aw = R->area_lat_west, aes = R[-1].area_lat_east, aws = R[-1].area_lat_west;
+      const double an = R->area_lon_north, asn = R[1].area_lon_south, ans = R[-1].area_lon_north, as0 = R->area_lon_south;
+      const double kv1 = (ae * (v_m * v_m) + aw * (v_0 * v_0) + an * (u_m * u_m) + asn * (u_mn * u_mn)) * rv;
+      const double kv2 = (aes * (v_ms * v_ms) + aws * (v_0s * v_0s) + ans * (u_ms * u_ms) + as0 * (u_m * u_m)) * rvs;
+      const double kv3 = (aes * (v_0s * v_0s) + aws * (v_ps * v_ps) + ans * (u_0s * u_0s) + as0 * (u_0 * u_0)) * rvs;
+      const double kv4 = (ae * (v_0 * v_0) + aw * (v_p * v_p) + an * (u_0 * u_0) + asn * (u_0n * u_0n)) * rv;
+      ke = (1.0 - a.ke_cell_wgt) * ((kv1 + kv4) * R->sub2 + (kv2 + kv3) * R->sub1) * rac + a.ke_cell_wgt * ke;
     }
     a.ke[c] = ke;
-    a.div[c] = ((u0 * MJ(M.le_lon, j) - um * MJ(M.le_lon, j)) + (v0 * MJ(M.le_lat, j) - vs * MJ(M.le_lat, j - 1))) / MJ(M.area_cell, j);
+    a.div[c] = ((u_0 * R->le_lon - u_m * R->le_lon) + (v_0 * R->le_lat - v_0s * R[-1].le_lat)) * rac;
   }
-  if (j <= g.nhalf) {
-    // half-lat row: mfy_lat, u_lat, pv
-    const double mlat = m_lat_at(a.m, g, i, j, k);
-    const double v0 = ldW(a.v, g, i, j, k);
-    a.mfy_lat[c] = mlat * v0;
-    const double mfx_lat = MJ2(M.half_tangent_wgt, 1, j) * (mfx_at(a.m, a.u, g, i - 1, j, k) + mfx_at(a.m, a.u, g, i, j, k)) +
-                           MJ2(M.half_tangent_wgt, 2, j) * (mfx_at(a.m, a.u, g, i - 1, j + 1, k) + mfx_at(a.m, a.u, g, i, j + 1, k));
-    a.u_lat[c] = mfx_lat / mlat;
-    const double vor = (ldW(a.u, g, i, j, k) * MJ(M.de_lon, j) - ldW(a.u, g, i, j + 1, k) * MJ(M.de_lon, j + 1) +
-                        ldW(a.v, g, i + 1, j, k) * MJ(M.de_lat, j) - v0 * MJ(M.de_lat, j)) / MJ(M.area_vtx, j);
-    a.pv[c] = (vor + MJ(M.half_f, j)) / m_vtx_at(a.m, g, M, i, j, k);
+  if (half) {
+    // half-lat row: mfy_lat, u_lat, pv.  mfx_lon is 0 on pole rows (never computed by the reference).
+    a.mfy_lat[c] = mlat * v_0;
+    const bool n0 = j + 1 < g.nlat;
+    const double fx_m = full ? ((m_m + m_0) * 0.5) * u_m : 0.0, fx_0 = full ? mlon * u_0 : 0.0;
+    const double fx_mn = n0 ? ((m_mn + m_0n) * 0.5) * u_mn : 0.0, fx_0n = n0 ? ((m_0n + m_pn) * 0.5) * u_0n : 0.0;
+    const double mfx_lat = R->htw1 * (fx_m + fx_0) + R->htw2 * (fx_mn + fx_0n);
+    a.u_lat[c] = qdiv(mfx_lat, mlat);
+    const double rv = R->r_area_vtx;
+    const double vor = (u_0 * R->de_lon - u_0n * R[1].de_lon + v_p * R->de_lat - v_0 * R->de_lat) * rv;
+    const double mvtx = ((m_0 + m_p) * R->sub2 + (m_0n + m_pn) * R[1].sub1) * rv;
+    a.pv[c] = qdiv(vor + R->half_f, mvtx);
   }
+}
+__global__ void __launch_bounds__(128, FWD1_MINB) k_fwd1(Geo g, DMesh M, Fwd1Args a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 1)) fwd1_body<true>(g, M, a, i, j, k); else fwd1_body<false>(g, M, a, i, j, k);
 }
 
 // Pole rows: zonal means replace the stencils (calc_ke :320-349, calc_div :378-407,
@@ -201,45 +230,73 @@ struct TendArgs {
   const double *gz_old, *pole_dmf; double *gz_new; double dt, grav;
   int coriolis_scheme, swm;
 };
-__global__ void __launch_bounds__(128) k_tend(Geo g, DMesh M, TendArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
-  const bool pole_row = (j == 1 || j == g.nlat);
-  if (!pole_row) {
-    const double pl = __ldg(a.pv_lon + c);
-    const double qhv = (MJ2(M.full_tangent_wgt, 1, j) * (ldW(a.mfy_lat, g, i, j - 1, k) * (pl + ldW(a.pv_lat, g, i, j - 1, k)) +
-                                                          ldW(a.mfy_lat, g, i + 1, j - 1, k) * (pl + ldW(a.pv_lat, g, i + 1, j - 1, k))) +
-                        MJ2(M.full_tangent_wgt, 2, j) * (ldW(a.mfy_lat, g, i, j, k) * (pl + ldW(a.pv_lat, g, i, j, k)) +
-                                                          ldW(a.mfy_lat, g, i + 1, j, k) * (pl + ldW(a.pv_lat, g, i + 1, j, k)))) * 0.5;
-    const double ke0 = __ldg(a.ke + c);
-    const double dkedlon = (ldW(a.ke, g, i + 1, j, k) - ke0) / MJ(M.de_lon, j);
+#ifndef TEND_MINB
+#define TEND_MINB 1
+#endif
+template <bool EDGE> __device__ __forceinline__ void tend_body(const Geo& g, const DMesh& M, const TendArgs& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k);
+  const int dm = wrapE<EDGE>(i - 1, n) - i, dp = wrapE<EDGE>(i + 1, n) - i;
+  const bool full = j > 1 && j < g.nlat, half = j <= g.nhalf;     // warp-uniform
+  const bool hyd = a.we_lev != nullptr;
+  const int pl = (int)g.plane;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  // ---- one memory phase: every distinct neighbour is loaded once, up front -------------------
+  const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
+  const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
+  const double* __restrict__ ker = a.ke + c;
+  const double ke0 = __ldg(ker);
+  const double plo_0 = __ldg(po), pla_0 = half ? __ldg(pa) : 0.0;
+  double fy_0 = 0, fy_p = 0, fy_0s = 0, fy_ps = 0, pla_p = 0, pla_0s = 0, pla_ps = 0, ke_p = 0;
+  if (full) {
+    fy_0 = __ldg(fy); fy_p = __ldg(fy + dp); fy_0s = __ldg(fy - n); fy_ps = __ldg(fy - n + dp);
+    pla_p = __ldg(pa + dp); pla_0s = __ldg(pa - n); pla_ps = __ldg(pa - n + dp);
+    ke_p = __ldg(ker + dp);
+  }
+  const bool s0 = j > 1, n0 = j + 1 < g.nlat;
+  double fx_m = 0, fx_0 = 0, fx_mn = 0, fx_0n = 0, plo_m = 0, plo_mn = 0, plo_0n = 0, ke_n = 0;
+  if (half) {
+    if (s0) { fx_m = __ldg(fx + dm); fx_0 = __ldg(fx); plo_m = __ldg(po + dm); }
+    if (n0) { fx_mn = __ldg(fx + n + dm); fx_0n = __ldg(fx + n); plo_mn = __ldg(po + n + dm); plo_0n = __ldg(po + n); }
+    ke_n = __ldg(ker + n);
+  }
+  double m_0 = 0, m_p = 0, m_n = 0, u0 = 0, u_up = 0, u_dn = 0, v0 = 0, v_up = 0, v_dn = 0;
+  double w_0 = 0, w_p = 0, w_n = 0, w1_0 = 0, w1_p = 0, w1_n = 0;
+  if (hyd) {
+    const double* __restrict__ mr = a.m + c; const double* __restrict__ wr = a.we_lev + c;
+    const bool kup = k > 0, kdn = k < g.nlev - 1;
+    m_0 = __ldg(mr);
+    w_0 = __ldg(wr); w1_0 = __ldg(wr + pl);
+    if (full) {
+      m_p = __ldg(mr + dp); w_p = __ldg(wr + dp); w1_p = __ldg(wr + pl + dp);
+      u0 = __ldg(a.u_f + c); if (kdn) u_dn = __ldg(a.u_f + c + pl); if (kup) u_up = __ldg(a.u_f + c - pl);
+    }
+    if (half) {
+      m_n = __ldg(mr + n); w_n = __ldg(wr + n); w1_n = __ldg(wr + pl + n);
+      v0 = __ldg(a.v_f + c); if (kdn) v_dn = __ldg(a.v_f + c + pl); if (kup) v_up = __ldg(a.v_f + c - pl);
+    }
+  }
+  // ---- du (lon edges of full-lat rows) ---------------------------------------------------------
+  if (full) {
+    const double qhv = (R->ftw1 * (fy_0s * (plo_0 + pla_0s) + fy_ps * (plo_0 + pla_ps)) +
+                        R->ftw2 * (fy_0 * (plo_0 + pla_0) + fy_p * (plo_0 + pla_p))) * 0.5;
+    const double dkedlon = (ke_p - ke0) * R->r_de_lon;
     double du = qhv - dkedlon;
-    if (a.we_lev) {
+    if (hyd) {
       // calc_wedudlev_wedvdlev (:1145-1180) with we_lev_lon from interp_mod.F90:361-369
-      const int kb = 0, ke = g.nlev - 1;
-      const double aw = MJ(M.area_lon_west, j), ae = MJ(M.area_lon_east, j), al = MJ(M.area_lon, j);
-      const double mlon = m_lon_at(a.m, g, i, j, k);
-      const double u0 = __ldg(a.u_f + c);
+      const double aw = R->area_lon_west, ae = R->area_lon_east, ral = R->r_area_lon;
+      const double mlon = (m_0 + m_p) * 0.5;
+      const double wl1 = (aw * w1_0 + ae * w1_p) * ral, wl0 = (aw * w_0 + ae * w_p) * ral;
       double w;
-      if (k > kb && k < ke) {
-        const double wl1 = (aw * ldW(a.we_lev, g, i, j, k + 1) + ae * ldW(a.we_lev, g, i + 1, j, k + 1)) / al;
-        const double wl0 = (aw * ldW(a.we_lev, g, i, j, k) + ae * ldW(a.we_lev, g, i + 1, j, k)) / al;
-        w = (wl1 * (ldW(a.u_f, g, i, j, k + 1) - u0) + wl0 * (u0 - ldW(a.u_f, g, i, j, k - 1))) / mlon / 2.0;
-      } else if (k == kb) {
-        const double wl1 = (aw * ldW(a.we_lev, g, i, j, k + 1) + ae * ldW(a.we_lev, g, i + 1, j, k + 1)) / al;
-        w = (wl1 * (ldW(a.u_f, g, i, j, k + 1) - u0)) / mlon / 2.0;
-      } else {
-        const double wl0 = (aw * ldW(a.we_lev, g, i, j, k) + ae * ldW(a.we_lev, g, i + 1, j, k)) / al;
-        w = (wl0 * (u0 - ldW(a.u_f, g, i, j, k - 1))) / mlon / 2.0;
-      }
-      du = du - w;
+      if (k > 0 && k < g.nlev - 1) w = wl1 * (u_dn - u0) + wl0 * (u0 - u_up);
+      else if (k == 0) w = wl1 * (u_dn - u0);
+      else w = wl0 * (u0 - u_up);
+      du = du - qdiv(w, mlon) * 0.5;
     }
     a.du[c] = du;
     if (a.swm) {
-      const double dmfdlon = (__ldg(a.mfx_lon + c) - ldW(a.mfx_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
-      const double dmfdlat = (__ldg(a.mfy_lat + c) * MJ(M.le_lat, j) - ldW(a.mfy_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+      const double rac = R->r_area_cell;
+      const double dmfdlon = (__ldg(fx) - __ldg(fx + dm)) * R->le_lon * rac;
+      const double dmfdlat = (fy_0 * R->le_lat - fy_0s * R[-1].le_lat) * rac;
       const double dgz = -(dmfdlon + dmfdlat) * a.grav;
       a.gz_new[c] = __ldg(a.gz_old + c) + a.dt * dgz;
     }
@@ -247,38 +304,31 @@ __global__ void __launch_bounds__(128) k_tend(Geo g, DMesh M, TendArgs a) {
     const double dgz = -(0.0 + __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k)) * a.grav;
     a.gz_new[c] = __ldg(a.gz_old + c) + a.dt * dgz;
   }
-  if (j <= g.nhalf) {
-    const double pt = __ldg(a.pv_lat + c);
-    // mfx_lon on pole rows is 0 (never computed by the reference)
-    const bool s0 = j > 1, n0 = j + 1 < g.nlat;
-    const double mx_a = s0 ? ldW(a.mfx_lon, g, i - 1, j, k) : 0.0, mx_b = s0 ? __ldg(a.mfx_lon + c) : 0.0;
-    const double mx_c = n0 ? ldW(a.mfx_lon, g, i - 1, j + 1, k) : 0.0, mx_d = n0 ? ldW(a.mfx_lon, g, i, j + 1, k) : 0.0;
-    const double pl_a = s0 ? ldW(a.pv_lon, g, i - 1, j, k) : 0.0, pl_b = s0 ? __ldg(a.pv_lon + c) : 0.0;
-    const double pl_c = n0 ? ldW(a.pv_lon, g, i - 1, j + 1, k) : 0.0, pl_d = n0 ? ldW(a.pv_lon, g, i, j + 1, k) : 0.0;
-    const double qhu = (MJ2(M.half_tangent_wgt, 1, j) * (mx_a * (pt + pl_a) + mx_b * (pt + pl_b)) +
-                        MJ2(M.half_tangent_wgt, 2, j) * (mx_c * (pt + pl_c) + mx_d * (pt + pl_d))) * 0.5;
-    const double dkedlat = (ldW(a.ke, g, i, j + 1, k) - __ldg(a.ke + c)) / MJ(M.de_lat, j);
+  // ---- dv (lat edges) ---------------------------------------------------------------------------
+  if (half) {
+    // mfx_lon / pv_lon terms on pole rows are 0 (never computed by the reference)
+    const double pl_b = s0 ? plo_0 : 0.0;
+    const double qhu = (R->htw1 * (fx_m * (pla_0 + plo_m) + fx_0 * (pla_0 + pl_b)) +
+                        R->htw2 * (fx_mn * (pla_0 + plo_mn) + fx_0n * (pla_0 + plo_0n))) * 0.5;
+    const double dkedlat = (ke_n - ke0) * R->r_de_lat;
     double dv = -qhu - dkedlat;
-    if (a.we_lev) {
+    if (hyd) {
       // :1181-1214 with we_lev_lat from interp_mod.F90:426-434
-      const int kb = 0, ke = g.nlev - 1;
-      const double an = MJ(M.area_lat_north, j), as = MJ(M.area_lat_south, j), al = MJ(M.area_lat, j);
-      const double mlat = m_lat_at(a.m, g, i, j, k);
-      const double v0 = __ldg(a.v_f + c);
+      const double an = R->area_lat_north, as = R->area_lat_south, ral = R->r_area_lat;
+      const double mlat = (m_0 + m_n) * 0.5;
+      const double wl1 = (an * w1_n + as * w1_0) * ral, wl0 = (an * w_n + as * w_0) * ral;
       double w;
-      if (k > kb && k < ke) {
-        const double wl1 = (an * ldW(a.we_lev, g, i, j + 1, k + 1) + as * ldW(a.we_lev, g, i, j, k + 1)) / al;
-        const double wl0 = (an * ldW(a.we_lev, g, i, j + 1, k) + as * ldW(a.we_lev, g, i, j, k)) / al;
-        w = (wl1 * (ldW(a.v_f, g, i, j, k + 1) - v0) + wl0 * (v0 - ldW(a.v_f, g, i, j, k - 1))) / mlat / 2.0;
-      } else if (k == kb) {
-        const double wl1 = (an * ldW(a.we_lev, g, i, j + 1, k + 1) + as * ldW(a.we_lev, g, i, j, k + 1)) / al;
-        w = (wl1 * (ldW(a.v_f, g, i, j, k + 1) - v0)) / mlat / 2.0;
-      } else {
-        const double wl0 = (an * ldW(a.we_lev, g, i, j + 1, k) + as * ldW(a.we_lev, g, i, j, k)) / al;
-        w = (wl0 * (v0 - ldW(a.v_f, g, i, j, k - 1))) / mlat / 2.0;
-      }
-      dv = dv - w;
+      if (k > 0 && k < g.nlev - 1) w = wl1 * (v_dn - v0) + wl0 * (v0 - v_up);
+      else if (k == 0) w = wl1 * (v_dn - v0);
+      else w = wl0 * (v0 - v_up);
+      dv = dv - qdiv(w, mlat) * 0.5;
     }
     a.dv[c] = dv;
   }
+}
+__global__ void __launch_bounds__(128, TEND_MINB) k_tend(Geo g, DMesh M, TendArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 1)) tend_body<true>(g, M, a, i, j, k); else tend_body<false>(g, M, a, i, j, k);
 }
