@@ -129,19 +129,19 @@ struct BatchRef { const double *u, *v, *mfx, *mfy, *cflx, *cfly, *divx, *divy; }
 static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double* flx, double* fly, double dt) {
   const Geo gw = xg(h, 3, 4), gn = xg(h, 1, 1), g0 = h->g;
   HflxArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qmfx, h->qmfy, gw.jb, gw.je, gn.jb, gn.je};
-  LAUNCH(h, k_hflx, gridg(gw, gw.nlev), 128, 0, gw, in);
+  LAUNCH(h, k_hflx, tile_grid(gw, gw.nlev), tile_block(), 0, gw, in);
   run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);
   FfslQArgs qa{q, h->qmfx, h->qmfy, B.divx, B.divy, h->pole_work, h->qx, h->qy, dt, xg(h, 0, 1).jb, xg(h, 0, 1).je};
-  LAUNCH(h, k_ffsl_q, gridg(gw, gw.nlev), 128, 0, gw, h->M, qa);
+  LAUNCH(h, k_ffsl_q, tile_grid(gw, gw.nlev), tile_block(), 0, gw, h->M, qa);
   HflxArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, g0.jb, xg(h, 0, 1).je, gn.jb, gn.je};
-  LAUNCH(h, k_hflx, gridg(gn, gn.nlev), 128, 0, gn, out);
+  LAUNCH(h, k_hflx, tile_grid(gn, gn.nlev), tile_block(), 0, gn, out);
 }
 
 // RK4 CFL numbers + divx/divy of a batch: x part on rows jb-3..je+4, y part on half rows jb-1..je+1
 static void run_cfl(gmc_handle* h, const double* u, const double* v, double* cflx, double* cfly, double* divx, double* divy, double dt) {
   const Geo gw = xg(h, 3, 4), gn = xg(h, 1, 1);
   CflArgs c{u, v, cflx, cfly, divx, divy, dt, h->cfg.radius, h->dflags, gw.jb, gw.je, gn.jb, gn.je};
-  LAUNCH(h, k_cfl, gridg(gw, gw.nlev), 128, 0, gw, h->M, c);
+  LAUNCH(h, k_cfl, tile_grid(gw, gw.nlev), tile_block(), 0, gw, h->M, c);
   run_pole_sum(h, v, nullptr, divy, 1);
 }
 
@@ -158,7 +158,7 @@ static void run_forward_prepare_x(gmc_handle* h, DState& S) {
     LAUNCH(h, k_pole1, dim3(h->g.nlev, 2), 256, 0, h->g, h->M, p);
   }
   PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv};
-  LAUNCH(h, k_pv_edge, gridg(g1, g1.nlev), 128, 0, g1, e);
+  LAUNCH(h, k_pv_edge, tile_grid(g1, g1.nlev), tile_block(), 0, g1, e);
 }
 
 // One hydrostatic step(old, star, new, dt), compute part.  In band mode the caller then
@@ -190,7 +190,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   UvArgs u{};
   u.ph_exn_lev = nw.ph_exn_lev; u.gz_lev = nw.gz_lev; u.du_fwd = h->du; u.dv_fwd = h->dv;
   u.u_old = old_.u; u.v_old = old_.v; u.u_new = nw.u; u.v_new = nw.v; u.dt = dt; u.swm = 0; u.blend = 0;
-  LAUNCH(h, k_uv_update, gridg(g, g.nlev), 128, 0, g, h->M, u);
+  LAUNCH(h, k_uv_update_h, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, u);
   run_filter(h, nw.u, 0, g.nlev, -1, nullptr, GMC_SMALL_FILTER2, nw.u);
   run_filter(h, nw.v, 1, g.nlev, -1, nullptr, GMC_SMALL_FILTER2, nw.v);
   if (g.has_south || g.has_north) LAUNCH(h, k_v_pole_blend, dim3((g.nlon + 127) / 128, g.nlev, 2), 128, 0, g, nw.v);

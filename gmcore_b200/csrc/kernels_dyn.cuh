@@ -186,36 +186,47 @@ struct PvEdgeArgs {
   double *pv_lon, *pv_lat;
   int scheme, order; double wgt;
 };
+template <bool EDGE> __device__ __forceinline__ void pv_edge_body(const Geo& g, const PvEdgeArgs& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k);
+  const double eps = 2.220446049250313e-16;
+  const bool full = j > 1 && j < g.nlat, half = j <= g.nhalf;      // warp-uniform
+  const bool up = a.scheme != 0, o3 = a.order != 1;
+  const double* __restrict__ pv = a.pv + c;
+  // one memory phase: the pv cross (4 rows x 4 columns of it) and the four wind components
+  double pm1 = 0, p0 = 0, pm2 = 0, pp1 = 0, vt = 0, un = 0;
+  if (full) {
+    if (j >= 3 && j + 1 <= g.nhalf) { pm1 = __ldg(pv - n); p0 = __ldg(pv); if (up && o3) { pm2 = __ldg(pv - 2 * n); pp1 = __ldg(pv + n); } }
+    else { pm1 = ldH(a.pv, g, i, j - 1, k); p0 = ldH(a.pv, g, i, j, k); if (up && o3) { pm2 = ldH(a.pv, g, i, j - 2, k); pp1 = ldH(a.pv, g, i, j + 1, k); } }
+    if (up) { vt = __ldg(a.v_lon + c); un = __ldg(a.u + c); }
+  }
+  double qm1 = 0, q0 = 0, qm2 = 0, qp1 = 0, ut = 0, vn = 0;
+  if (half) {
+    qm1 = __ldg(pv + (wrapE<EDGE>(i - 1, n) - i)); q0 = full && j >= 3 && j + 1 <= g.nhalf ? p0 : __ldg(pv);
+    if (up && o3) { qm2 = __ldg(pv + (wrapE<EDGE>(i - 2, n) - i)); qp1 = __ldg(pv + (wrapE<EDGE>(i + 1, n) - i)); }
+    if (up) { ut = __ldg(a.u_lat + c); vn = __ldg(a.v + c); }
+  }
+  if (full) {
+    if (!up) a.pv_lon[c] = 0.5 * (p0 + pm1);
+    else {
+      const double b = qdiv(fabs(vt), sqrt(un * un + vt * vt) + eps);
+      const double upw = o3 ? upwind3(sign1(vt), a.wgt, pm2, pm1, p0, pp1) : upwind1(sign1(vt), a.wgt, pm1, p0);
+      a.pv_lon[c] = b * upw + (1 - b) * 0.5 * (pm1 + p0);
+    }
+  }
+  if (half) {
+    if (!up) a.pv_lat[c] = 0.5 * (qm1 + q0);
+    else {
+      const double b = qdiv(fabs(ut), sqrt(ut * ut + vn * vn) + eps);
+      const double upw = o3 ? upwind3(sign1(ut), a.wgt, qm2, qm1, q0, qp1) : upwind1(sign1(ut), a.wgt, qm1, q0);
+      a.pv_lat[c] = b * upw + (1 - b) * 0.5 * (qm1 + q0);
+    }
+  }
+}
 __global__ void __launch_bounds__(128) k_pv_edge(Geo g, PvEdgeArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
-  const double eps = 2.220446049250313e-16;
-  if (j > 1 && j < g.nlat) {
-    const double pm1 = ldH(a.pv, g, i, j - 1, k), p0 = ldH(a.pv, g, i, j, k);
-    if (a.scheme == 0) {
-      a.pv_lon[c] = 0.5 * (p0 + pm1);
-    } else {
-      const double vt = __ldg(a.v_lon + c), un = __ldg(a.u + c);
-      const double b = fabs(vt) / (sqrt(un * un + vt * vt) + eps);
-      const double up = a.order == 1 ? upwind1(sign1(vt), a.wgt, pm1, p0)
-                                     : upwind3(sign1(vt), a.wgt, ldH(a.pv, g, i, j - 2, k), pm1, p0, ldH(a.pv, g, i, j + 1, k));
-      a.pv_lon[c] = b * up + (1 - b) * 0.5 * (pm1 + p0);
-    }
-  }
-  if (j <= g.nhalf) {
-    const double pm1 = ldW(a.pv, g, i - 1, j, k), p0 = __ldg(a.pv + c);
-    if (a.scheme == 0) {
-      a.pv_lat[c] = 0.5 * (pm1 + p0);
-    } else {
-      const double ut = __ldg(a.u_lat + c), vn = __ldg(a.v + c);
-      const double b = fabs(ut) / (sqrt(ut * ut + vn * vn) + eps);
-      const double up = a.order == 1 ? upwind1(sign1(ut), a.wgt, pm1, p0)
-                                     : upwind3(sign1(ut), a.wgt, ldW(a.pv, g, i - 2, j, k), pm1, p0, ldW(a.pv, g, i + 1, j, k));
-      a.pv_lat[c] = b * up + (1 - b) * 0.5 * (pm1 + p0);
-    }
-  }
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 2) || blockIdx.x * blockDim.x < 2) pv_edge_body<true>(g, a, i, j, k); else pv_edge_body<false>(g, a, i, j, k);
 }
 
 // K3: calc_coriolis (:846-906) + calc_grad_ke (:908-937) [+ vertical advection terms

@@ -60,12 +60,12 @@ struct CflArgs {
 };
 __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
   const int c = gidx(g, i, j, k), rb = c - i;
   const int i1 = i + 1;                       // Fortran index
   const double* __restrict__ hl = M.half_lon + (M.hx - 1);   // hl[l] = half_lon(l), l Fortran index
-  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;   // block-uniform
+  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;   // warp-uniform
   const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
   const double* __restrict__ ur = a.u + rb;
   // The x and y RK4 chains are independent: their three dependent gathers are interleaved stage
@@ -247,10 +247,10 @@ struct HflxArgs {
 };
 __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const int c = gidx(g, i, j, k), rb = c - i;
-  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  const int n = g.nlon, c = gidx(g, i, j, k), rb = c - i;
+  const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;     // warp-uniform
   const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
   // Phase 1: the four independent loads (CFL numbers and advecting velocities) go out together,
   // phase 2: both 5-point upwind stencils -- two dependent memory round trips per thread, not four.
@@ -259,28 +259,33 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
   const double uu = dox ? __ldg(a.u + c) : 0.0;
   const double vv = doy ? __ldg(a.v + c) : 0.0;
   const int ci = (int)cx;
-  const int iu = wrapi(cx > 0 ? i - ci : i - ci + 1, g.nlon);
+  const int iu = wrapi(cx > 0 ? i - ci : i - ci + 1, n);
   const int ju = cy > 0 ? j : j + 1;
   double x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0, y0 = 0, y1 = 0, y2 = 0, y3 = 0, y4 = 0;
   const double* __restrict__ mxr = a.mx + rb;
   if (cx != 0) {
-    x0 = __ldg(mxr + wrapi(iu - 2, g.nlon)); x1 = __ldg(mxr + wrapi(iu - 1, g.nlon)); x2 = __ldg(mxr + iu);
-    x3 = __ldg(mxr + wrapi(iu + 1, g.nlon)); x4 = __ldg(mxr + wrapi(iu + 2, g.nlon));
+    x0 = __ldg(mxr + wrapi(iu - 2, n)); x1 = __ldg(mxr + wrapi(iu - 1, n)); x2 = __ldg(mxr + iu);
+    x3 = __ldg(mxr + wrapi(iu + 1, n)); x4 = __ldg(mxr + wrapi(iu + 2, n));
   }
   if (cy != 0) {
-    y0 = ldF(a.my, g, i, ju - 2, k); y1 = ldF(a.my, g, i, ju - 1, k); y2 = ldF(a.my, g, i, ju, k);
-    y3 = ldF(a.my, g, i, ju + 1, k); y4 = ldF(a.my, g, i, ju + 2, k);
+    if (j >= 3 && j + 3 <= g.nlat) {   // away from the poles: no mirror, rows at fixed strides from one address
+      const double* __restrict__ myc = a.my + c + (ju - j) * n;
+      y0 = __ldg(myc - 2 * n); y1 = __ldg(myc - n); y2 = __ldg(myc); y3 = __ldg(myc + n); y4 = __ldg(myc + 2 * n);
+    } else {
+      y0 = ldF(a.my, g, i, ju - 2, k); y1 = ldF(a.my, g, i, ju - 1, k); y2 = ldF(a.my, g, i, ju, k);
+      y3 = ldF(a.my, g, i, ju + 1, k); y4 = ldF(a.my, g, i, ju + 2, k);
+    }
   }
   if (dox) {
     double flux = 0;
     if (cx != 0) {
       const double cf = cx - ci;
       double s1, s2, sm = 0;
-      if (cx > 0) { s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, g.nlon)); }
-      else { s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, g.nlon)); }
+      if (cx > 0) { s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+      else { s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
       double ml, dm, m6;
       ppm(x0, x1, x2, x3, x4, ml, dm, m6);
-      flux = (cx > 0 ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2) / cx;
+      flux = qdiv((cx > 0 ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
     }
     a.mfx[c] = flux;
   }
@@ -291,7 +296,7 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
       if (cy > 0) { s1 = 1 - cy; s2 = 1; } else { s1 = 0; s2 = -cy; }
       double ml, dm, m6;
       ppm(y0, y1, y2, y3, y4, ml, dm, m6);
-      flux = (cy > 0 ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2) / cy;
+      flux = qdiv((cy > 0 ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
     }
     a.mfy[c] = flux;
   }
@@ -299,21 +304,30 @@ __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
 
 // Intermediate fields of the inner advective step (ffsl_mod.F90:354-406)
 struct FfslQArgs { const double *q, *qmfx, *qmfy, *divx, *divy, *pole; double *qx, *qy; double dt; int jy0, jy1; /* rows of qy */ };
-__global__ void __launch_bounds__(128) k_ffsl_q(Geo g, DMesh M, FfslQArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
+template <bool EDGE> __device__ __forceinline__ void ffsl_q_body(const Geo& g, const DMesh& M, const FfslQArgs& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k);
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
   const double q = __ldg(a.q + c);
   if (j > 1 && j < g.nlat) {
-    a.qx[c] = q - 0.5 * ((__ldg(a.qmfx + c) - ldW(a.qmfx, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j) - __ldg(a.divx + c) * q) * a.dt;
-    if (j >= a.jy0 && j <= a.jy1) a.qy[c] = q - 0.5 * ((__ldg(a.qmfy + c) * MJ(M.le_lat, j) - ldW(a.qmfy, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j) - __ldg(a.divy + c) * q) * a.dt;
+    const bool doy = j >= a.jy0 && j <= a.jy1;
+    const double fx0 = __ldg(a.qmfx + c), fxm = __ldg(a.qmfx + c + (wrapE<EDGE>(i - 1, n) - i)), dx = __ldg(a.divx + c);
+    double fy0 = 0, fys = 0, dy = 0;
+    if (doy) { fy0 = __ldg(a.qmfy + c); fys = __ldg(a.qmfy + c - n); dy = __ldg(a.divy + c); }
+    const double rac = R->r_area_cell;
+    a.qx[c] = q - 0.5 * ((fx0 - fxm) * R->le_lon * rac - dx * q) * a.dt;
+    if (doy) a.qy[c] = q - 0.5 * ((fy0 * R->le_lat - fys * R[-1].le_lat) * rac - dy * q) * a.dt;
   } else {
     const double pole = __ldg(a.pole + (j == 1 ? 0 : g.nlev) + k);
     const double t = 0.5 * (pole - __ldg(a.divy + c) * q) * a.dt;
     a.qx[c] = q;
     a.qy[c] = j == 1 ? q - t : q + t;
   }
+}
+__global__ void __launch_bounds__(128) k_ffsl_q(Geo g, DMesh M, FfslQArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 1)) ffsl_q_body<true>(g, M, a, i, j, k); else ffsl_q_body<false>(g, M, a, i, j, k);
 }
 
 // ---- FFSL vertical PPM flux (vflx_ppm_cell, ffsl_mod.F90:883-941) --------------------

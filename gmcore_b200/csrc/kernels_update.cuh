@@ -105,6 +105,35 @@ __global__ void __launch_bounds__(128) k_uv_update(Geo g, DMesh M, UvArgs a) {
     a.v_new[c] = v;
   }
 }
+// Hydrostatic specialisation: Lin97 PGF on both edges from one up-front load of the 6 distinct
+// (ph_exn_lev, gz_lev) corner pairs; /de_lon, /de_lat are reciprocal multiplies.
+template <bool EDGE> __device__ __forceinline__ void uv_h_body(const Geo& g, const DMesh& M, const UvArgs& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k), pl = (int)g.plane;
+  const int dp = wrapE<EDGE>(i + 1, n) - i;
+  const bool full = j > 1 && j < g.nlat, half = j <= g.nhalf;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double* __restrict__ pe = a.ph_exn_lev + c; const double* __restrict__ gz = a.gz_lev + c;
+  const double p00 = __ldg(pe), p01 = __ldg(pe + pl), g00 = __ldg(gz), g01 = __ldg(gz + pl);
+  double pp0 = 0, pp1 = 0, gp0 = 0, gp1 = 0, pn0 = 0, pn1 = 0, gn0 = 0, gn1 = 0, duf = 0, dvf = 0, uo = 0, vo = 0;
+  if (full) { pp0 = __ldg(pe + dp); pp1 = __ldg(pe + pl + dp); gp0 = __ldg(gz + dp); gp1 = __ldg(gz + pl + dp); duf = __ldg(a.du_fwd + c); uo = __ldg(a.u_old + c); }
+  if (half) { pn0 = __ldg(pe + n); pn1 = __ldg(pe + pl + n); gn0 = __ldg(gz + n); gn1 = __ldg(gz + pl + n); dvf = __ldg(a.dv_fwd + c); vo = __ldg(a.v_old + c); }
+  if (full) {
+    const double dph1 = pp1 - p00, dph2 = p01 - pp0, dgz1 = g01 - gp0, dgz2 = g00 - gp1;
+    const double pgf = qdiv(-(dph1 * dgz1 + dph2 * dgz2) * R->r_de_lon, dph1 + dph2);
+    a.u_new[c] = uo + a.dt * (duf - pgf);
+  }
+  if (half) {
+    const double dph1 = pn1 - p00, dph2 = p01 - pn0, dgz1 = g01 - gn0, dgz2 = g00 - gn1;
+    const double pgf = qdiv(-(dph1 * dgz1 + dph2 * dgz2) * R->r_de_lat, dph1 + dph2);
+    a.v_new[c] = vo + a.dt * (dvf - pgf);
+  }
+}
+__global__ void __launch_bounds__(128) k_uv_update_h(Geo g, DMesh M, UvArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 1)) uv_h_body<true>(g, M, a, i, j, k); else uv_h_body<false>(g, M, a, i, j, k);
+}
 // Pole-adjacent v blend as a separate pass (hydrostatic core: it follows small_filter2;
 // time_schemes_mod.F90:225-233).  Rows 1 and nhalf only; north uses the final j-1 row.
 __global__ void k_v_pole_blend(Geo g, double* v) {

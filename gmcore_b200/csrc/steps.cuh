@@ -22,7 +22,7 @@ static void run_forward_prepare(gmc_handle* h, DState& S) {
   Pole1Args p{S.v_f, S.m, S.u_lat, S.mfy_lat, S.ke, S.div, S.pv, h->pole_dmf, h->cfg.pv_pole_stokes};
   LAUNCH(h, k_pole1, dim3(g.nlev, 2), 256, 0, g, h->M, p);
   PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv};
-  LAUNCH(h, k_pv_edge, grid3(h, g.nlev), 128, 0, g, e);
+  LAUNCH(h, k_pv_edge, tile_grid(g, g.nlev), tile_block(), 0, g, e);
 }
 
 static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, int f1, double* out1, int f2, double* out2,
