@@ -63,6 +63,7 @@ struct DMesh {
   // a per-latitude coefficient becomes a multiply (<= 1 ulp from the reference's divide, far inside
   // the 1e-12 parity bar) -- FP64 divides are ~30 issue slots each and dominated several kernels.
   const double *r_area_cell, *r_area_vtx, *r_de_lon, *r_de_lat, *r_area_lon, *r_area_lat;
+  const double *r_full_dlev;   // 1 / full_dlev, same bounds (-1 : nlev+2)
   int hx;
 };
 #define MJ(v, j) (v[(j) + 1])                  // vector entry at latitude index j

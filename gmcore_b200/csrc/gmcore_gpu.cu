@@ -157,6 +157,11 @@ int gmc_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
     if (!rc) rc = dev_upload(h, &M.half_dlev, mv->half_dlev, (size_t)c.nlev + 1);
     if (!rc) rc = dev_upload(h, &M.full_lev, mv->full_lev, (size_t)c.nlev + 4);
     if (!rc) rc = dev_upload(h, &M.full_dlev, mv->full_dlev, (size_t)c.nlev + 4);
+    {
+      std::vector<double> r((size_t)c.nlev + 4);
+      for (size_t q = 0; q < r.size(); ++q) r[q] = mv->full_dlev[q] != 0.0 ? 1.0 / mv->full_dlev[q] : 0.0;
+      if (!rc) rc = dev_upload(h, &M.r_full_dlev, r.data(), r.size());
+    }
     if (!rc) rc = hydro_set_mesh(h, mv);
   }
 #undef UPF

@@ -113,7 +113,7 @@ static void run_ph(gmc_handle* h, DState& S, const Geo& g) {
 }
 static void run_gz(gmc_handle* h, DState& S, const Geo& g) {
   GzArgs a{S.pt, S.phs_f, h->gzs, S.t, S.gz_lev, make_vc(h)};
-  LAUNCH(h, k_gz_col, gridg(g, 1, 64), 64, (size_t)g.nlev * 64 * sizeof(double), g, h->M, a);
+  LAUNCH(h, k_gz_col, gridg(g, 1), 128, 0, g, h->M, a);
 }
 static void run_pole_sum(gmc_handle* h, const double* f, double* out, double* row_out, int signed_north) {
   const Geo& g = h->g;
@@ -169,7 +169,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   run_forward_prepare_x(h, star);
   run_cfl(h, star.u_f, star.v_f, h->cflx, h->cfly, h->divx, h->divy, dt);
   WeArgs w{star.mfx_lon, star.mfy_lat, h->pole_dmf, star.m_lev, star.we_lev, h->dphs, h->cflz, dt, h->dflags};
-  LAUNCH(h, k_we_col, gridg(g01, 1), 128, 0, g01, h->M, w);
+  LAUNCH(h, k_we_col, gridg(g01, 1), 128, (size_t)(g.nlev + 1) * 128 * sizeof(double), g01, h->M, w);
   TendArgs t{};
   t.mfx_lon = star.mfx_lon; t.mfy_lat = star.mfy_lat; t.pv_lon = star.pv_lon; t.pv_lat = star.pv_lat; t.ke = star.ke;
   t.we_lev = star.we_lev; t.u_f = star.u_f; t.v_f = star.v_f; t.m = star.m; t.du = h->du; t.dv = h->dv;
@@ -179,7 +179,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   run_ffsl_h(h, B, star.pt, h->ptf_lon, h->ptf_lat, dt);
   run_pole_sum(h, h->ptf_lat, h->pole_work + 2 * g.nlev, nullptr, 1);
   PtColArgs pc{star.pt, h->ptf_lon, h->ptf_lat, h->pole_work + 2 * g.nlev, star.we_lev, h->cflz, old_.pt, old_.m, nw.pt, h->dpt, dt};
-  LAUNCH(h, k_pt_col, gridg(g01, 1), 128, 0, g01, h->M, pc);
+  LAUNCH(h, k_pt_col, gridg(g01, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g01, h->M, pc);
   // ---- update_state(tend1): rows jb..je+1 (the Lin97 PGF of half row je reads row je+1) ----
   LAUNCH(h, k_axpy2d, gridg(g01, 1), 128, 0, g01, old_.phs, h->dphs, nw.phs, dt);
   run_filter(h, nw.phs, 0, 1, GMC_BIG_FILTER, nw.phs_f, -1, nullptr, POST_NONE, nullptr, nullptr, &g01);
@@ -260,7 +260,7 @@ static void hydro_accum_wind(gmc_handle* h, int itime) {
   accum_pair(h, g, h->bwe, S.we_lev, g.nlev + 1, h->bm_lev, S.m_lev, g.nlev + 1, mode);
   if (h->we_step == 0) {
     CflzArgs c{h->bwe, h->bm_lev, h->bcflz, h->cfg.dt_adv, h->dflags};
-    LAUNCH(h, k_cflz, gridg(g, 1), 128, 0, g, h->M, c);
+    LAUNCH(h, k_cflz, gridg(g, 1), 128, (size_t)(g.nlev + 1) * 128 * sizeof(double), g, h->M, c);
   }
 }
 
@@ -286,7 +286,7 @@ static bool hydro_adv_run(gmc_handle* h, int itime, int time_step) {
       NegXArgs nx{qn, S.m, h->dflags};
       LAUNCH(h, k_negfill_x, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, nx);
       TrVArgs tv{qn, S.m, h->bwe, h->bcflz, dt_adv, h->dflags};
-      LAUNCH(h, k_tracer_v, gridg(g, 1, 64), 64, (size_t)2 * g.nlev * 64 * sizeof(double), g, tv);
+      LAUNCH(h, k_tracer_v, gridg(g, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g, tv);
       LonDampArgs ld{qn, h->lon_damp_wgt, 3};
       LAUNCH(h, k_lon_damp, dim3(g.je - g.jb + 1, g.nlev), 256, (size_t)2 * g.nlon * sizeof(double), g, ld);
     }

@@ -153,26 +153,23 @@ __device__ __forceinline__ double m_lev_at(const DMesh& M, const VC& vc, int nle
   return 0.5 * (ph_lev_at(M, vc, k1, phs) + ph_lev_at(M, vc, k1 + 1, phs)) - 0.5 * (ph_lev_at(M, vc, k1 - 1, phs) + ph_lev_at(M, vc, k1, phs));
 }
 
-// RK4 in eta for one half level (adv_batch_mod.F90:529-627).  we/ml are this column's
-// we and m_lev with stride `st` between levels (index 0 = half level 1).
-__device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const double* we, const double* ml, long long st,
+// RK4 in eta for one half level (adv_batch_mod.F90:529-627).  wm is this column's eta velocity
+// we_lev / m_lev * half_dlev per half level (index 0 = half level 1), staged in shared memory with
+// stride `st`: one divide per level instead of the reference's seven per RK4 evaluation.
+__device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const double* wm, int st,
                                          double dt, double* out, int* flags) {
   const double* hl = M.half_lev - 1;     // hl[l] = half_lev(l)
-  const double* hd = M.half_dlev - 1;
   const double* fd = M.full_dlev + 1;    // fd[l] = full_dlev(l), stored from -1
-  auto W = [&](int l) { return we[(l - 1) * st]; };
-  auto ML = [&](int l) { return ml[(l - 1) * st]; };
+  const double* rfd = M.r_full_dlev + 1;
   auto search = [&](double w, double z) {
     int l;
     if (w > 0) { for (l = k1; l <= nlev; ++l) if (hl[l] <= z && z <= hl[l + 1]) break; if (l == nlev + 1) { atomicOr(flags, 4); l = nlev; } }
     else { for (l = k1 - 1; l >= 1; --l) if (hl[l] <= z && z <= hl[l + 1]) break; if (l == 0) { atomicOr(flags, 4); l = 1; } }
     return l;
   };
-  auto interp = [&](int l, double z) {
-    return ((hl[l + 1] - z) * W(l) / ML(l) * hd[l] + (z - hl[l]) * W(l + 1) / ML(l + 1) * hd[l + 1]) / fd[l];
-  };
+  auto interp = [&](int l, double z) { return ((hl[l + 1] - z) * wm[(l - 1) * st] + (z - hl[l]) * wm[l * st]) * rfd[l]; };
   const double z0 = hl[k1];
-  const double w1 = W(k1) / ML(k1) * hd[k1];
+  const double w1 = wm[(k1 - 1) * st];
   double z = z0 + dt / 2 * w1;
   int l = search(w1, z);
   const double w2 = interp(l, z);
@@ -180,58 +177,75 @@ __device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const
   const double w3 = interp(l, z);
   z = z0 + dt * w3; l = search(w3, z);
   const double w4 = interp(l, z);
-  double deta = (w1 + 2 * w2 + 2 * w3 + w4) / 6 * dt;
+  double deta = (w1 + 2 * w2 + 2 * w3 + w4) * (1.0 / 6.0) * dt;
   int ks, ke, s;
   if (deta < 0) { ks = k1 - 1; ke = 1; s = -1; } else { ks = k1; ke = nlev; s = 1; }
   deta = fabs(deta);
   for (l = ks; s > 0 ? l <= ke : l >= ke; l += s) {
     deta = deta - fd[l];
-    if (deta < 0) { *out = s * ((1 + deta / fd[l]) + abs(l - ks)); return true; }
+    if (deta < 0) { *out = s * ((1 + deta * rfd[l]) + abs(l - ks)); return true; }
   }
   return false;
 }
 
 __global__ void __launch_bounds__(128) k_we_col(Geo g, DMesh M, WeArgs a) {
+  extern __shared__ double wm_s[];       // [nlev+1][blockDim.x]
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;
   const bool pole = (j == 1 || j == g.nlat);
-  const long long st = g.plane;
-  const long long c0 = gidx(g, i, j, 0);
-  double* we = a.we_lev + c0;
+  const int st = (int)g.plane, B = blockDim.x, n = g.nlon;
+  const int c0 = gidx(g, i, j, 0), im = wrapi(i - 1, n) - i;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double rac = R->r_area_cell, lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
+  double* wm = wm_s + threadIdx.x;
   double dphs = 0, mf = 0;
-  we[0] = 0.0;
+  // calc_grad_mf + calc_dphsdt: running sums in the reference's k order; prefix parked in shared memory
   for (int k = 0; k < g.nlev; ++k) {
     double dlon, dlat;
     if (pole) { dlon = 0.0; dlat = __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k); }
     else {
-      dlon = (__ldg(a.mfx_lon + c0 + k * st) - ldW(a.mfx_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
-      dlat = (__ldg(a.mfy_lat + c0 + k * st) * MJ(M.le_lat, j) - ldW(a.mfy_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
+      const double* fx = a.mfx_lon + c0 + k * st; const double* fy = a.mfy_lat + c0 + k * st;
+      dlon = (__ldg(fx) - __ldg(fx + im)) * lel * rac;
+      dlat = (__ldg(fy) * lea - __ldg(fy - n) * leas) * rac;
     }
     dphs = dphs - dlon - dlat;
     mf = mf + dlon + dlat;
-    we[(k + 1) * st] = mf;          // prefix over levels 1..k+1, finalised below
+    wm[(k + 1) * B] = mf;
   }
-  a.dphs[gidx(g, i, j, 0)] = dphs;
-  for (int k1 = 2; k1 <= g.nlev; ++k1) we[(k1 - 1) * st] = -(M.hybi[k1 - 1] * dphs) - we[(k1 - 1) * st];
-  we[g.nlev * st] = 0.0;
+  a.dphs[c0] = dphs;
+  // calc_we_lev, and the eta velocity of accum_we_lev
+  double* we = a.we_lev + c0;
   const double* ml = a.m_lev + c0;
+  const double* hd = M.half_dlev - 1;
+  we[0] = 0.0; wm[0] = 0.0;
+  for (int k1 = 2; k1 <= g.nlev; ++k1) {
+    const double w = -(M.hybi[k1 - 1] * dphs) - wm[(k1 - 1) * B];
+    we[(k1 - 1) * st] = w;
+    wm[(k1 - 1) * B] = qdiv(w, __ldg(ml + (k1 - 1) * st)) * hd[k1];
+  }
+  we[g.nlev * st] = 0.0; wm[g.nlev * B] = 0.0;
   for (int k1 = 2; k1 <= g.nlev; ++k1) {
     double cz;
-    if (cflz_one(M, g.nlev, k1, we, ml, st, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+    if (cflz_one(M, g.nlev, k1, wm, B, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
   }
 }
 
 // cflz for a tracer batch from its accumulated we / m_lev (adv_batch_mod.F90:526-627)
 struct CflzArgs { const double *we, *m_lev; double* cflz; double dt; int* flags; };
 __global__ void __launch_bounds__(128) k_cflz(Geo g, DMesh M, CflzArgs a) {
+  extern __shared__ double wm_s[];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;
-  const long long c0 = gidx(g, i, j, 0);
+  const int st = (int)g.plane, B = blockDim.x, c0 = gidx(g, i, j, 0);
+  double* wm = wm_s + threadIdx.x;
+  const double* hd = M.half_dlev - 1;
+  for (int k1 = 1; k1 <= g.nlev + 1; ++k1)
+    wm[(k1 - 1) * B] = qdiv(__ldg(a.we + c0 + (k1 - 1) * st), __ldg(a.m_lev + c0 + (k1 - 1) * st)) * hd[k1];
   for (int k1 = 2; k1 <= g.nlev; ++k1) {
     double cz;
-    if (cflz_one(M, g.nlev, k1, a.we + c0, a.m_lev + c0, g.plane, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * g.plane] = cz;
+    if (cflz_one(M, g.nlev, k1, wm, B, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
   }
 }
 
@@ -358,7 +372,7 @@ __device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, dou
   double ml = 0, dm = 0, m6 = 0;
   if (ku >= 1 && ku <= q.nlev) ppm(q(ku - 2), q(ku - 1), q(ku), q(ku + 1), q(ku + 2), ml, dm, m6);
   const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);
-  return (cz > 0 ? w : -w) * integ / cz;
+  return qdiv((cz > 0 ? w : -w) * integ, cz);
 }
 
 // calc_grad_ptf tail (operators_mod.F90:1040-1112) + dpt (gmcore_mod.F90:490-495) + the
@@ -371,28 +385,36 @@ struct PtColArgs {
   double dt;
 };
 __global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
+  extern __shared__ double pt_s[];       // [nlev][blockDim.x]: the pt column, loaded once
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;
   const bool pole = (j == 1 || j == g.nlat);
-  const long long st = g.plane, c0 = gidx(g, i, j, 0);
-  ColQ q{a.pt + c0, st, g.nlev, GH_LINEAR};
+  const int st = (int)g.plane, B = blockDim.x, n = g.nlon, c0 = gidx(g, i, j, 0), im = wrapi(i - 1, n) - i;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double rac = R->r_area_cell, lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
+  double* ps = pt_s + threadIdx.x;
+#pragma unroll 8
+  for (int k = 0; k < g.nlev; ++k) ps[k * B] = __ldg(a.pt + c0 + k * st);
+  ColQ q{ps, (long long)B, g.nlev, GH_LINEAR};
   double f_up = 0.0;   // ptf_lev(k), k = 1 -> 0
   for (int k = 0; k < g.nlev; ++k) {
-    const long long c = c0 + k * st;
-    double dlon, dlat;
-    if (pole) { dlon = 0.0; dlat = __ldg(a.pole_ptf + (j == 1 ? 0 : g.nlev) + k); }
-    else {
-      dlon = (__ldg(a.ptf_lon + c) - ldW(a.ptf_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) / MJ(M.area_cell, j);
-      dlat = (__ldg(a.ptf_lat + c) * MJ(M.le_lat, j) - ldW(a.ptf_lat, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) / MJ(M.area_cell, j);
-    }
+    const int c = c0 + k * st;
+    // all of this level's loads first, then the PPM arithmetic
     const int k1 = k + 2;   // lower half level of full level k+1
-    const double f_dn = k1 <= g.nlev ? vflx_one(q, k1, __ldg(a.cflz + c0 + (k1 - 1) * st), __ldg(a.we_lev + c0 + (k1 - 1) * st)) : 0.0;
+    double cz = 0, w = 0, fx0 = 0, fxm = 0, fy0 = 0, fys = 0, pdm = 0;
+    if (k1 <= g.nlev) { cz = __ldg(a.cflz + c + st); w = __ldg(a.we_lev + c + st); }
+    if (pole) pdm = __ldg(a.pole_ptf + (j == 1 ? 0 : g.nlev) + k);
+    else { fx0 = __ldg(a.ptf_lon + c); fxm = __ldg(a.ptf_lon + c + im); fy0 = __ldg(a.ptf_lat + c); fys = __ldg(a.ptf_lat + c - n); }
+    const double po = __ldg(a.pt_old + c), mo = __ldg(a.m_old + c);
+    const double dlon = pole ? 0.0 : (fx0 - fxm) * lel * rac;
+    const double dlat = pole ? pdm : (fy0 * lea - fys * leas) * rac;
+    const double f_dn = k1 <= g.nlev ? vflx_one(q, k1, cz, w) : 0.0;
     const double dlev = f_dn - f_up;
     f_up = f_dn;
     const double dpt = -dlon - dlat - dlev;
     if (a.dpt) a.dpt[c] = dpt;
-    a.ptm_new[c] = __ldg(a.pt_old + c) * __ldg(a.m_old + c) + a.dt * dpt;
+    a.ptm_new[c] = po * mo + a.dt * dpt;
   }
 }
 
@@ -416,33 +438,30 @@ __global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
 }
 
 // ---- calc_t + calc_gz_lev (operators_mod.F90:170-190,433-469) ------------------------
-// One thread per column.  The hydrostatic integral keeps the reference's summation
-// order (for each k: l = k..nlev ascending); the per-level terms are computed once and
-// parked in shared memory, so the O(nlev^2) part is additions only.
+// One thread per column, walking UP from the surface with a running sum: gz_lev(k) = gzs +
+// sum_{l=k}^{nlev} Rd t(l) log(ph_lev(l+1)/ph_lev(l)).  The reference adds each level's terms in
+// ascending l (an O(nlev^2) loop); the running suffix re-associates that sum (<= nlev ulps of the
+// column thickness, the same size as the libm-vs-CUDA pow/log differences) and needs no scratch.
 struct GzArgs { const double *pt, *phs_f, *gzs; double *t, *gz_lev; VC vc; };
-__global__ void __launch_bounds__(64) k_gz_col(Geo g, DMesh M, GzArgs a) {
-  extern __shared__ double term[];     // [nlev][blockDim.x]
+__global__ void __launch_bounds__(128) k_gz_col(Geo g, DMesh M, GzArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;
-  const long long st = g.plane, c0 = gidx(g, i, j, 0);
+  const int st = (int)g.plane, c0 = gidx(g, i, j, 0);
   const double phs = __ldg(a.phs_f + c0);
-  double pl0 = ph_lev_at(M, a.vc, 1, phs);
-  for (int k = 0; k < g.nlev; ++k) {
-    const double pl1 = ph_lev_at(M, a.vc, k + 2, phs);
-    const double ph = 0.5 * (pl0 + pl1);
-    const double t = __ldg(a.pt + c0 + k * st) * pow(ph / a.vc.p0, a.vc.kappa);
-    a.t[c0 + k * st] = t;
-    term[k * blockDim.x + threadIdx.x] = a.vc.Rd * t * log(pl1 / pl0);
-    pl0 = pl1;
-  }
   const double gzs = __ldg(a.gzs + c0);
-  for (int k = 0; k < g.nlev; ++k) {
-    double dgz = 0.0;
-    for (int l = k; l < g.nlev; ++l) dgz = dgz + term[l * blockDim.x + threadIdx.x];
-    a.gz_lev[c0 + k * st] = gzs + dgz;
-  }
+  const double rp0 = 1.0 / a.vc.p0;
   a.gz_lev[c0 + g.nlev * st] = gzs;    // T14: bottom interface = surface geopotential
+  double pl1 = ph_lev_at(M, a.vc, g.nlev + 1, phs), dgz = 0.0;
+  for (int k = g.nlev - 1; k >= 0; --k) {
+    const double pl0 = ph_lev_at(M, a.vc, k + 1, phs);
+    const double ph = 0.5 * (pl0 + pl1);
+    const double t = __ldg(a.pt + c0 + k * st) * pow(ph * rp0, a.vc.kappa);
+    a.t[c0 + k * st] = t;
+    dgz = dgz + a.vc.Rd * t * log(qdiv(pl1, pl0));
+    a.gz_lev[c0 + k * st] = gzs + dgz;
+    pl1 = pl0;
+  }
 }
 
 // ---- div_damp_run, order 2 (div_damp_mod.F90:89-139); div is recomputed from the
@@ -533,37 +552,46 @@ __global__ void __launch_bounds__(128) k_negfill_x(Geo g, NegXArgs a) {
 // vertical flux + update + negative filling in z (:259-297), one thread per column,
 // the column staged in shared memory (the update is in place).
 struct TrVArgs { double* q; const double *m, *we, *cflz; double dt; int* flags; };
-__global__ void __launch_bounds__(64) k_tracer_v(Geo g, TrVArgs a) {
-  extern __shared__ double col[];     // [2*nlev][blockDim.x]: q, then new q
+__global__ void __launch_bounds__(128) k_tracer_v(Geo g, TrVArgs a) {
+  extern __shared__ double col[];     // [nlev][blockDim.x]: the old q column
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;
-  const long long st = g.plane, c0 = gidx(g, i, j, 0);
+  const int st = (int)g.plane, c0 = gidx(g, i, j, 0);
   const int B = blockDim.x, nlev = g.nlev;
-  double* qs = col + threadIdx.x; double* qn = col + (size_t)nlev * B + threadIdx.x;
+  double* qs = col + threadIdx.x;
+#pragma unroll 8
   for (int k = 0; k < nlev; ++k) qs[k * B] = a.q[c0 + k * st];
   ColQ q{qs, (long long)B, nlev, GH_COPY};
   double f_up = 0;
+  bool neg = false;
   for (int k = 0; k < nlev; ++k) {
-    const int k1 = k + 2;
-    const double f_dn = k1 <= nlev ? vflx_one(q, k1, __ldg(a.cflz + c0 + (k1 - 1) * st), __ldg(a.we + c0 + (k1 - 1) * st)) : 0.0;
-    qn[k * B] = qs[k * B] - ((f_dn - f_up) * a.dt) / __ldg(a.m + c0 + k * st);
+    const int k1 = k + 2, c = c0 + k * st;
+    double cz = 0, w = 0;
+    if (k1 <= nlev) { cz = __ldg(a.cflz + c + st); w = __ldg(a.we + c + st); }
+    const double m = __ldg(a.m + c);
+    const double f_dn = k1 <= nlev ? vflx_one(q, k1, cz, w) : 0.0;
+    const double qn = qs[k * B] - qdiv((f_dn - f_up) * a.dt, m);
+    a.q[c] = qn;                       // the update is in place: the stencil reads the staged column
+    neg = neg || qn < 0;
     f_up = f_dn;
   }
+  if (!neg) return;
+  // negative filling in z (adv_mod.F90:275-297): rare, sequential, on this thread's own column
+  double* qn = a.q + c0; const double* mm_ = a.m + c0;
   for (int k = 0; k < nlev; ++k) {
-    if (qn[k * B] < 0) {
-      const double m0 = __ldg(a.m + c0 + k * st);
-      const double mm = k > 0 ? __ldg(a.m + c0 + (k - 1) * st) : 0.0, mp = k < nlev - 1 ? __ldg(a.m + c0 + (k + 1) * st) : 0.0;
-      const double qm0 = qn[k * B] * m0, qm1 = k > 0 ? qn[(k - 1) * B] * mm : 0.0, qm2 = k < nlev - 1 ? qn[(k + 1) * B] * mp : 0.0;
+    if (qn[k * st] < 0) {
+      const double m0 = mm_[k * st];
+      const double mm = k > 0 ? mm_[(k - 1) * st] : 0.0, mp = k < nlev - 1 ? mm_[(k + 1) * st] : 0.0;
+      const double qm0 = qn[k * st] * m0, qm1 = k > 0 ? qn[(k - 1) * st] * mm : 0.0, qm2 = k < nlev - 1 ? qn[(k + 1) * st] * mp : 0.0;
       const double h = 0.5 * qm0;
-      if (qm1 >= h && qm2 >= h) { if (qm1 > 0) qn[(k - 1) * B] = (qm1 - h) / mm; if (qm2 > 0) qn[(k + 1) * B] = (qm2 - h) / mp; }
-      else if (qm1 > qm0) { if (qm1 > 0) qn[(k - 1) * B] = (qm1 - qm0) / mm; }
-      else if (qm2 > qm0) { if (qm2 > 0) qn[(k + 1) * B] = (qm2 - qm0) / mp; }
+      if (qm1 >= h && qm2 >= h) { if (qm1 > 0) qn[(k - 1) * st] = (qm1 - h) / mm; if (qm2 > 0) qn[(k + 1) * st] = (qm2 - h) / mp; }
+      else if (qm1 > qm0) { if (qm1 > 0) qn[(k - 1) * st] = (qm1 - qm0) / mm; }
+      else if (qm2 > qm0) { if (qm2 > 0) qn[(k + 1) * st] = (qm2 - qm0) / mp; }
       else atomicOr(a.flags, 16);
-      qn[k * B] = 0;
+      qn[k * st] = 0;
     }
   }
-  for (int k = 0; k < nlev; ++k) a.q[c0 + k * st] = qn[k * B];
 }
 
 // 3 x lon_damp_on_cell(order 2) (lon_damp_mod.F90:158-177,231-236), one block per row
