@@ -26,18 +26,23 @@ __device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : 
 __device__ __forceinline__ double min3(double a, double b, double c) { return dmin(dmin(a, b), c); }
 __device__ __forceinline__ double max3(double a, double b, double c) { return dmax(dmax(a, b), c); }
 
-// ffsl_mod.F90:1183-1194 (limiter_type = 'mono')
-__device__ __forceinline__ double slope_mono(double fm1, double f, double fp1) {
-  const double df = (fp1 - fm1) * 0.5;
-  const double df_min = 2 * (f - min3(fm1, f, fp1));
-  const double df_max = 2 * (max3(fm1, f, fp1) - f);
-  return fsign(min3(fabs(df), df_min, df_max), df);
+// ffsl_mod.F90:1183-1194 (limiter_type = 'mono'): sign(df) * min(|df|, 2 (f - min3), 2 (max3 - f)).
+// With da = f - fm1, db = fp1 - f:  f - min3 = max(da, 0, -db) and max3 - f = max(-da, 0, db) exactly,
+// so the limiter is min(|df|, 2|da|, 2|db|) when da, db have the same sign and 0 at a local extremum --
+// two min-selects instead of six min/max-selects, identical values (up to the sign of a zero).
+__device__ __forceinline__ double slope_mono_d(double da, double db, double df) {
+  const double lim = dmin(fabs(df), 2 * dmin(fabs(da), fabs(db)));
+  return da * db > 0 ? copysign(lim, df) : 0.0;
 }
-// ffsl_mod.F90:1147-1173
+__device__ __forceinline__ double slope_mono(double fm1, double f, double fp1) {
+  return slope_mono_d(f - fm1, fp1 - f, (fp1 - fm1) * 0.5);
+}
+// ffsl_mod.F90:1147-1173; the four first differences are shared by the three slopes
 __device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
-  const double dfl = slope_mono(fm2, fm1, f);
-  df = slope_mono(fm1, f, fp1);
-  const double dfr = slope_mono(f, fp1, fp2);
+  const double d1 = fm1 - fm2, d2 = f - fm1, d3 = fp1 - f, d4 = fp2 - fp1;
+  const double dfl = slope_mono_d(d1, d2, (f - fm2) * 0.5);
+  df = slope_mono_d(d2, d3, (fp1 - fm1) * 0.5);
+  const double dfr = slope_mono_d(d3, d4, (fp2 - f) * 0.5);
   fl = 0.5 * (fm1 + f) + (dfl - df) * (1.0 / 6.0);
   double fr = 0.5 * (fp1 + f) + (df - dfr) * (1.0 / 6.0);
   fl = f - fsign(dmin(fabs(df), fabs(fl - f)), df);
