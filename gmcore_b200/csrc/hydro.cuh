@@ -152,7 +152,7 @@ extern "C" { static int xfer(gmc_handle* h, double* dev, double* host, int kind,
 static void run_forward_prepare_x(gmc_handle* h, DState& S) {
   const Geo g2 = xg(h, 2, 2), g1 = xg(h, 1, 1);
   Fwd1Args f{S.u_f, S.v_f, S.m, S.mfx_lon, S.mfy_lat, S.u_lat, S.v_lon, S.ke, S.pv, S.div, h->cfg.ke_scheme, h->cfg.ke_cell_wgt};
-  LAUNCH(h, k_fwd1, tile_grid(g2, g2.nlev), tile_block(), 0, g2, h->M, f);
+  LAUNCH(h, k_fwd1, tile_grid(g2, 1), tile_block(), 0, g2, h->M, f);
   if (h->g.has_south || h->g.has_north) {
     Pole1Args p{S.v_f, S.m, S.u_lat, S.mfy_lat, S.ke, S.div, S.pv, h->pole_dmf, h->cfg.pv_pole_stokes};
     LAUNCH(h, k_pole1, dim3(h->g.nlev, 2), 256, 0, h->g, h->M, p);
@@ -174,7 +174,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   t.mfx_lon = star.mfx_lon; t.mfy_lat = star.mfy_lat; t.pv_lon = star.pv_lon; t.pv_lat = star.pv_lat; t.ke = star.ke;
   t.we_lev = star.we_lev; t.u_f = star.u_f; t.v_f = star.v_f; t.m = star.m; t.du = h->du; t.dv = h->dv;
   t.coriolis_scheme = h->cfg.coriolis_scheme; t.swm = 0;
-  LAUNCH(h, k_tend, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, t);
+  LAUNCH(h, k_tend, tile_grid(g, 1), tile_block(), 0, g, h->M, t);
   BatchRef B{star.u_f, star.v_f, star.mfx_lon, star.mfy_lat, h->cflx, h->cfly, h->divx, h->divy};
   run_ffsl_h(h, B, star.pt, h->ptf_lon, h->ptf_lat, dt);
   run_pole_sum(h, h->ptf_lat, h->pole_work + 2 * g.nlev, nullptr, 1);

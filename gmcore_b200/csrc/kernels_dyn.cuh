@@ -66,72 +66,81 @@ struct Fwd1Args {
 // K1: calc_mf (:545-610) + calc_ke (:234-317) + calc_div (:368-377) + calc_vor/calc_pv
 // (:630-639,693-699) on all non-pole-special points.
 #ifndef FWD1_MINB
-#define FWD1_MINB 8
+#define FWD1_MINB 4
 #endif
-template <bool EDGE> __device__ __forceinline__ void fwd1_body(const Geo& g, const DMesh& M, const Fwd1Args& a, int i, int j, int k) {
-  const int n = g.nlon, c = gidx(g, i, j, k);
+// One thread per (i, j) marching down the levels: the ~30 row coefficients and the neighbour
+// offsets are formed once per column instead of once per point (no vertical coupling here -- the
+// loop only amortises the per-row work and keeps 32 levels of independent loads behind one thread).
+template <bool EDGE> __device__ __forceinline__ void fwd1_col(const Geo& g, const DMesh& M, const Fwd1Args& a, int i, int j) {
+  const int n = g.nlon, pl = (int)g.plane;
   const int dm = wrapE<EDGE>(i - 1, n) - i, dp = wrapE<EDGE>(i + 1, n) - i;   // -1 / +1 away from the row ends
   const bool full = j > 1 && j < g.nlat;     // non-pole full-lat row (warp-uniform)
-  const bool half = j <= g.nhalf;
-  // One memory phase: the 20 distinct neighbours of u, v, m are loaded up front into registers
-  // (rows j-1 and j+1 always exist on the device: >= 2 halo rows); everything below is register
-  // arithmetic in the reference's operation order.
-  const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
+  const bool half = j <= g.nhalf, n0 = j + 1 < g.nlat;
+  const bool ke2 = a.ke_scheme == 2;
   const RowCoef* __restrict__ R = M.rows + (j + 1);
-  const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
-  const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
-  const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
-  const double m_m = __ldg(mr + dm), m_0 = __ldg(mr), m_p = __ldg(mr + dp);
-  const double m_mn = __ldg(mr + n + dm), m_0n = __ldg(mr + n), m_pn = __ldg(mr + n + dp);
-  double u_ms = 0, u_0s = 0, v_m = 0, v_ms = 0, v_0s = 0, v_ps = 0, m_0s = 0, m_ps = 0;
-  if (full) {
-    u_ms = __ldg(ur - n + dm); u_0s = __ldg(ur - n);
-    v_m = __ldg(vr + dm); v_ms = __ldg(vr - n + dm); v_0s = __ldg(vr - n); v_ps = __ldg(vr - n + dp);
-    m_0s = __ldg(mr - n); m_ps = __ldg(mr - n + dp);
-  }
-  const double mlon = (m_0 + m_p) * 0.5;            // m_lon(i,j)
-  const double mlat = (m_0 + m_0n) * 0.5;           // m_lat(i,j)
-  if (full) {
-    // full-lat, non-pole row: mfx_lon, v_lon, ke, div
-    const double rac = R->r_area_cell;
-    a.mfx_lon[c] = mlon * u_0;
-    const double mfy_lon = R->ftw1 * (((m_0s + m_0) * 0.5) * v_0s + ((m_ps + m_p) * 0.5) * v_ps) +
-                           R->ftw2 * (mlat * v_0 + ((m_p + m_pn) * 0.5) * v_p);
-    a.v_lon[c] = qdiv(mfy_lon, mlon);
-    double ke = (R->area_lon_west * (u_m * u_m) + R->area_lon_east * (u_0 * u_0) +
-                 R[-1].area_lat_north * (v_0s * v_0s) + R->area_lat_south * (v_0 * v_0)) * rac;
-    if (a.ke_scheme == 2) {
-      const double rv = R->r_area_vtx, rvs = R[-1].r_area_vtx;
-      const double ae = R->area_lat_east, aw = R->area_lat_west, aes = R[-1].area_lat_east, aws = R[-1].area_lat_west;
-      const double an = R->area_lon_north, asn = R[1].area_lon_south, ans = R[-1].area_lon_north, as0 = R->area_lon_south;
-      const double kv1 = (ae * (v_m * v_m) + aw * (v_0 * v_0) + an * (u_m * u_m) + asn * (u_mn * u_mn)) * rv;
-      const double kv2 = (aes * (v_ms * v_ms) + aws * (v_0s * v_0s) + ans * (u_ms * u_ms) + as0 * (u_m * u_m)) * rvs;
-      const double kv3 = (aes * (v_0s * v_0s) + aws * (v_ps * v_ps) + ans * (u_0s * u_0s) + as0 * (u_0 * u_0)) * rvs;
-      const double kv4 = (ae * (v_0 * v_0) + aw * (v_p * v_p) + an * (u_0 * u_0) + asn * (u_0n * u_0n)) * rv;
-      ke = (1.0 - a.ke_cell_wgt) * ((kv1 + kv4) * R->sub2 + (kv2 + kv3) * R->sub1) * rac + a.ke_cell_wgt * ke;
+  const double rac = R->r_area_cell, ftw1 = R->ftw1, ftw2 = R->ftw2, htw1 = R->htw1, htw2 = R->htw2;
+  const double alw = R->area_lon_west, ale = R->area_lon_east, atn_s = R[-1].area_lat_north, ats = R->area_lat_south;
+  const double rv = R->r_area_vtx, rvs = R[-1].r_area_vtx;
+  const double ae = R->area_lat_east, aw = R->area_lat_west, aes = R[-1].area_lat_east, aws = R[-1].area_lat_west;
+  const double an = R->area_lon_north, asn = R[1].area_lon_south, ans = R[-1].area_lon_north, as0 = R->area_lon_south;
+  const double sub1 = R->sub1, sub2 = R->sub2, sub1n = R[1].sub1;
+  const double lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
+  const double del = R->de_lon, deln = R[1].de_lon, dea = R->de_lat, hf = R->half_f;
+  const double kw = a.ke_cell_wgt;
+  int c = gidx(g, i, j, 0);
+#pragma unroll 1
+  for (int k = 0; k < g.nlev; ++k, c += pl) {
+    // one memory phase: the 20 distinct neighbours of u, v, m (rows j-1 and j+1 always exist on the
+    // device: >= 2 halo rows); everything below is register arithmetic in the reference's order
+    const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
+    const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
+    const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
+    const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
+    const double m_m = __ldg(mr + dm), m_0 = __ldg(mr), m_p = __ldg(mr + dp);
+    const double m_mn = __ldg(mr + n + dm), m_0n = __ldg(mr + n), m_pn = __ldg(mr + n + dp);
+    double u_ms = 0, u_0s = 0, v_m = 0, v_ms = 0, v_0s = 0, v_ps = 0, m_0s = 0, m_ps = 0;
+    if (full) {
+      u_ms = __ldg(ur - n + dm); u_0s = __ldg(ur - n);
+      v_m = __ldg(vr + dm); v_ms = __ldg(vr - n + dm); v_0s = __ldg(vr - n); v_ps = __ldg(vr - n + dp);
+      m_0s = __ldg(mr - n); m_ps = __ldg(mr - n + dp);
     }
-    a.ke[c] = ke;
-    a.div[c] = ((u_0 * R->le_lon - u_m * R->le_lon) + (v_0 * R->le_lat - v_0s * R[-1].le_lat)) * rac;
-  }
-  if (half) {
-    // half-lat row: mfy_lat, u_lat, pv.  mfx_lon is 0 on pole rows (never computed by the reference).
-    a.mfy_lat[c] = mlat * v_0;
-    const bool n0 = j + 1 < g.nlat;
-    const double fx_m = full ? ((m_m + m_0) * 0.5) * u_m : 0.0, fx_0 = full ? mlon * u_0 : 0.0;
-    const double fx_mn = n0 ? ((m_mn + m_0n) * 0.5) * u_mn : 0.0, fx_0n = n0 ? ((m_0n + m_pn) * 0.5) * u_0n : 0.0;
-    const double mfx_lat = R->htw1 * (fx_m + fx_0) + R->htw2 * (fx_mn + fx_0n);
-    a.u_lat[c] = qdiv(mfx_lat, mlat);
-    const double rv = R->r_area_vtx;
-    const double vor = (u_0 * R->de_lon - u_0n * R[1].de_lon + v_p * R->de_lat - v_0 * R->de_lat) * rv;
-    const double mvtx = ((m_0 + m_p) * R->sub2 + (m_0n + m_pn) * R[1].sub1) * rv;
-    a.pv[c] = qdiv(vor + R->half_f, mvtx);
+    const double mlon = (m_0 + m_p) * 0.5;            // m_lon(i,j)
+    const double mlat = (m_0 + m_0n) * 0.5;           // m_lat(i,j)
+    if (full) {
+      // full-lat, non-pole row: mfx_lon, v_lon, ke, div
+      a.mfx_lon[c] = mlon * u_0;
+      const double mfy_lon = ftw1 * (((m_0s + m_0) * 0.5) * v_0s + ((m_ps + m_p) * 0.5) * v_ps) +
+                             ftw2 * (mlat * v_0 + ((m_p + m_pn) * 0.5) * v_p);
+      a.v_lon[c] = qdiv(mfy_lon, mlon);
+      double ke = (alw * (u_m * u_m) + ale * (u_0 * u_0) + atn_s * (v_0s * v_0s) + ats * (v_0 * v_0)) * rac;
+      if (ke2) {
+        const double kv1 = (ae * (v_m * v_m) + aw * (v_0 * v_0) + an * (u_m * u_m) + asn * (u_mn * u_mn)) * rv;
+        const double kv2 = (aes * (v_ms * v_ms) + aws * (v_0s * v_0s) + ans * (u_ms * u_ms) + as0 * (u_m * u_m)) * rvs;
+        const double kv3 = (aes * (v_0s * v_0s) + aws * (v_ps * v_ps) + ans * (u_0s * u_0s) + as0 * (u_0 * u_0)) * rvs;
+        const double kv4 = (ae * (v_0 * v_0) + aw * (v_p * v_p) + an * (u_0 * u_0) + asn * (u_0n * u_0n)) * rv;
+        ke = (1.0 - kw) * ((kv1 + kv4) * sub2 + (kv2 + kv3) * sub1) * rac + kw * ke;
+      }
+      a.ke[c] = ke;
+      a.div[c] = ((u_0 * lel - u_m * lel) + (v_0 * lea - v_0s * leas)) * rac;
+    }
+    if (half) {
+      // half-lat row: mfy_lat, u_lat, pv.  mfx_lon is 0 on pole rows (never computed by the reference).
+      a.mfy_lat[c] = mlat * v_0;
+      const double fx_m = full ? ((m_m + m_0) * 0.5) * u_m : 0.0, fx_0 = full ? mlon * u_0 : 0.0;
+      const double fx_mn = n0 ? ((m_mn + m_0n) * 0.5) * u_mn : 0.0, fx_0n = n0 ? ((m_0n + m_pn) * 0.5) * u_0n : 0.0;
+      const double mfx_lat = htw1 * (fx_m + fx_0) + htw2 * (fx_mn + fx_0n);
+      a.u_lat[c] = qdiv(mfx_lat, mlat);
+      const double vor = (u_0 * del - u_0n * deln + v_p * dea - v_0 * dea) * rv;
+      const double mvtx = ((m_0 + m_p) * sub2 + (m_0n + m_pn) * sub1n) * rv;
+      a.pv[c] = qdiv(vor + hf, mvtx);
+    }
   }
 }
 __global__ void __launch_bounds__(128, FWD1_MINB) k_fwd1(Geo g, DMesh M, Fwd1Args a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y;
   if (i >= g.nlon || j > g.je) return;
-  if (edge_block(g.nlon, 1)) fwd1_body<true>(g, M, a, i, j, k); else fwd1_body<false>(g, M, a, i, j, k);
+  if (edge_block(g.nlon, 1)) fwd1_col<true>(g, M, a, i, j); else fwd1_col<false>(g, M, a, i, j);
 }
 
 // Pole rows: zonal means replace the stencils (calc_ke :320-349, calc_div :378-407,
@@ -242,104 +251,113 @@ struct TendArgs {
   int coriolis_scheme, swm;
 };
 #ifndef TEND_MINB
-#define TEND_MINB 1
+#define TEND_MINB 4
 #endif
-template <bool EDGE> __device__ __forceinline__ void tend_body(const Geo& g, const DMesh& M, const TendArgs& a, int i, int j, int k) {
-  const int n = g.nlon, c = gidx(g, i, j, k);
+// One thread per (i, j) column edge pair, marching down the levels: the row coefficients and the
+// neighbour offsets are formed once per column, and the vertical-advection operands (u_f, v_f at
+// k-1, k, k+1 and we_lev at k, k+1 on three columns) roll through registers, so each is read from
+// memory once instead of two or three times by different level-blocks.
+template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, const DMesh& M, const TendArgs& a, int i, int j) {
+  const int n = g.nlon, pl = (int)g.plane, nlev = g.nlev;
   const int dm = wrapE<EDGE>(i - 1, n) - i, dp = wrapE<EDGE>(i + 1, n) - i;
   const bool full = j > 1 && j < g.nlat, half = j <= g.nhalf;     // warp-uniform
   const bool hyd = a.we_lev != nullptr;
-  const int pl = (int)g.plane;
-  const RowCoef* __restrict__ R = M.rows + (j + 1);
-  // ---- one memory phase: every distinct neighbour is loaded once, up front -------------------
-  const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
-  const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
-  const double* __restrict__ ker = a.ke + c;
-  const double ke0 = __ldg(ker);
-  const double plo_0 = __ldg(po), pla_0 = half ? __ldg(pa) : 0.0;
-  double fy_0 = 0, fy_p = 0, fy_0s = 0, fy_ps = 0, pla_p = 0, pla_0s = 0, pla_ps = 0, ke_p = 0;
-  if (full) {
-    fy_0 = __ldg(fy); fy_p = __ldg(fy + dp); fy_0s = __ldg(fy - n); fy_ps = __ldg(fy - n + dp);
-    pla_p = __ldg(pa + dp); pla_0s = __ldg(pa - n); pla_ps = __ldg(pa - n + dp);
-    ke_p = __ldg(ker + dp);
-  }
   const bool s0 = j > 1, n0 = j + 1 < g.nlat;
-  double fx_m = 0, fx_0 = 0, fx_mn = 0, fx_0n = 0, plo_m = 0, plo_mn = 0, plo_0n = 0, ke_n = 0;
-  if (half) {
-    if (s0) { fx_m = __ldg(fx + dm); fx_0 = __ldg(fx); plo_m = __ldg(po + dm); }
-    if (n0) { fx_mn = __ldg(fx + n + dm); fx_0n = __ldg(fx + n); plo_mn = __ldg(po + n + dm); plo_0n = __ldg(po + n); }
-    ke_n = __ldg(ker + n);
-  }
-  double m_0 = 0, m_p = 0, m_n = 0, u0 = 0, u_up = 0, u_dn = 0, v0 = 0, v_up = 0, v_dn = 0;
-  double w_0 = 0, w_p = 0, w_n = 0, w1_0 = 0, w1_p = 0, w1_n = 0;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double ftw1 = R->ftw1, ftw2 = R->ftw2, htw1 = R->htw1, htw2 = R->htw2, rdl = R->r_de_lon, rda = R->r_de_lat;
+  const double aw = R->area_lon_west, ae = R->area_lon_east, ralo = R->r_area_lon;
+  const double an = R->area_lat_north, as = R->area_lat_south, rala = R->r_area_lat;
+  int c = gidx(g, i, j, 0);
+  double u0 = 0, u_up = 0, u_dn = 0, v0 = 0, v_up = 0, v_dn = 0;
+  double w_0 = 0, w_p = 0, w_n = 0, w1_0 = 0, w1_p = 0, w1_n = 0;      // we_lev(k) is 0 on the top interface
   if (hyd) {
-    const double* __restrict__ mr = a.m + c; const double* __restrict__ wr = a.we_lev + c;
-    const bool kup = k > 0, kdn = k < g.nlev - 1;
-    m_0 = __ldg(mr);
-    w_0 = __ldg(wr); w1_0 = __ldg(wr + pl);
-    if (full) {
-      m_p = __ldg(mr + dp); w_p = __ldg(wr + dp); w1_p = __ldg(wr + pl + dp);
-      u0 = __ldg(a.u_f + c); if (kdn) u_dn = __ldg(a.u_f + c + pl); if (kup) u_up = __ldg(a.u_f + c - pl);
-    }
-    if (half) {
-      m_n = __ldg(mr + n); w_n = __ldg(wr + n); w1_n = __ldg(wr + pl + n);
-      v0 = __ldg(a.v_f + c); if (kdn) v_dn = __ldg(a.v_f + c + pl); if (kup) v_up = __ldg(a.v_f + c - pl);
-    }
+    if (full) u_dn = __ldg(a.u_f + c);
+    if (half) v_dn = __ldg(a.v_f + c);
   }
-  // ---- du (lon edges of full-lat rows) ---------------------------------------------------------
-  if (full) {
-    const double qhv = (R->ftw1 * (fy_0s * (plo_0 + pla_0s) + fy_ps * (plo_0 + pla_ps)) +
-                        R->ftw2 * (fy_0 * (plo_0 + pla_0) + fy_p * (plo_0 + pla_p))) * 0.5;
-    const double dkedlon = (ke_p - ke0) * R->r_de_lon;
-    double du = qhv - dkedlon;
-    if (hyd) {
-      // calc_wedudlev_wedvdlev (:1145-1180) with we_lev_lon from interp_mod.F90:361-369
-      const double aw = R->area_lon_west, ae = R->area_lon_east, ral = R->r_area_lon;
-      const double mlon = (m_0 + m_p) * 0.5;
-      const double wl1 = (aw * w1_0 + ae * w1_p) * ral, wl0 = (aw * w_0 + ae * w_p) * ral;
-      double w;
-      if (k > 0 && k < g.nlev - 1) w = wl1 * (u_dn - u0) + wl0 * (u0 - u_up);
-      else if (k == 0) w = wl1 * (u_dn - u0);
-      else w = wl0 * (u0 - u_up);
-      du = du - qdiv(w, mlon) * 0.5;
+#pragma unroll 1
+  for (int k = 0; k < nlev; ++k, c += pl) {
+    // ---- this level's loads, all up front ---------------------------------------------------
+    const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
+    const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
+    const double* __restrict__ ker = a.ke + c;
+    const double ke0 = __ldg(ker);
+    const double plo_0 = __ldg(po), pla_0 = half ? __ldg(pa) : 0.0;
+    double fy_0 = 0, fy_p = 0, fy_0s = 0, fy_ps = 0, pla_p = 0, pla_0s = 0, pla_ps = 0, ke_p = 0;
+    if (full) {
+      fy_0 = __ldg(fy); fy_p = __ldg(fy + dp); fy_0s = __ldg(fy - n); fy_ps = __ldg(fy - n + dp);
+      pla_p = __ldg(pa + dp); pla_0s = __ldg(pa - n); pla_ps = __ldg(pa - n + dp);
+      ke_p = __ldg(ker + dp);
     }
-    a.du[c] = du;
-    if (a.swm) {
-      const double rac = R->r_area_cell;
-      const double dmfdlon = (__ldg(fx) - __ldg(fx + dm)) * R->le_lon * rac;
-      const double dmfdlat = (fy_0 * R->le_lat - fy_0s * R[-1].le_lat) * rac;
-      const double dgz = -(dmfdlon + dmfdlat) * a.grav;
+    double fx_m = 0, fx_0 = 0, fx_mn = 0, fx_0n = 0, plo_m = 0, plo_mn = 0, plo_0n = 0, ke_n = 0;
+    if (half) {
+      if (s0) { fx_m = __ldg(fx + dm); fx_0 = __ldg(fx); plo_m = __ldg(po + dm); }
+      if (n0) { fx_mn = __ldg(fx + n + dm); fx_0n = __ldg(fx + n); plo_mn = __ldg(po + n + dm); plo_0n = __ldg(po + n); }
+      ke_n = __ldg(ker + n);
+    }
+    double m_0 = 0, m_p = 0, m_n = 0;
+    if (hyd) {
+      const double* __restrict__ mr = a.m + c; const double* __restrict__ wr = a.we_lev + c + pl;   // interface k+1
+      const bool kdn = k < nlev - 1;
+      m_0 = __ldg(mr);
+      u_up = u0; u0 = u_dn; v_up = v0; v0 = v_dn;
+      w_0 = w1_0; w_p = w1_p; w_n = w1_n;
+      w1_0 = __ldg(wr);
+      if (full) { m_p = __ldg(mr + dp); w1_p = __ldg(wr + dp); if (kdn) u_dn = __ldg(a.u_f + c + pl); }
+      if (half) { m_n = __ldg(mr + n); w1_n = __ldg(wr + n); if (kdn) v_dn = __ldg(a.v_f + c + pl); }
+    }
+    // ---- du (lon edges of full-lat rows) -------------------------------------------------------
+    if (full) {
+      const double qhv = (ftw1 * (fy_0s * (plo_0 + pla_0s) + fy_ps * (plo_0 + pla_ps)) +
+                          ftw2 * (fy_0 * (plo_0 + pla_0) + fy_p * (plo_0 + pla_p))) * 0.5;
+      const double dkedlon = (ke_p - ke0) * rdl;
+      double du = qhv - dkedlon;
+      if (hyd) {
+        // calc_wedudlev_wedvdlev (:1145-1180) with we_lev_lon from interp_mod.F90:361-369
+        const double mlon = (m_0 + m_p) * 0.5;
+        const double wl1 = (aw * w1_0 + ae * w1_p) * ralo, wl0 = (aw * w_0 + ae * w_p) * ralo;
+        double w;
+        if (k > 0 && k < nlev - 1) w = wl1 * (u_dn - u0) + wl0 * (u0 - u_up);
+        else if (k == 0) w = wl1 * (u_dn - u0);
+        else w = wl0 * (u0 - u_up);
+        du = du - qdiv(w, mlon) * 0.5;
+      }
+      a.du[c] = du;
+      if (a.swm) {
+        const double rac = R->r_area_cell;
+        const double dmfdlon = (__ldg(fx) - __ldg(fx + dm)) * R->le_lon * rac;
+        const double dmfdlat = (fy_0 * R->le_lat - fy_0s * R[-1].le_lat) * rac;
+        const double dgz = -(dmfdlon + dmfdlat) * a.grav;
+        a.gz_new[c] = __ldg(a.gz_old + c) + a.dt * dgz;
+      }
+    } else if (a.swm) {
+      const double dgz = -(0.0 + __ldg(a.pole_dmf + (j == 1 ? 0 : nlev) + k)) * a.grav;
       a.gz_new[c] = __ldg(a.gz_old + c) + a.dt * dgz;
     }
-  } else if (a.swm) {
-    const double dgz = -(0.0 + __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k)) * a.grav;
-    a.gz_new[c] = __ldg(a.gz_old + c) + a.dt * dgz;
-  }
-  // ---- dv (lat edges) ---------------------------------------------------------------------------
-  if (half) {
-    // mfx_lon / pv_lon terms on pole rows are 0 (never computed by the reference)
-    const double pl_b = s0 ? plo_0 : 0.0;
-    const double qhu = (R->htw1 * (fx_m * (pla_0 + plo_m) + fx_0 * (pla_0 + pl_b)) +
-                        R->htw2 * (fx_mn * (pla_0 + plo_mn) + fx_0n * (pla_0 + plo_0n))) * 0.5;
-    const double dkedlat = (ke_n - ke0) * R->r_de_lat;
-    double dv = -qhu - dkedlat;
-    if (hyd) {
-      // :1181-1214 with we_lev_lat from interp_mod.F90:426-434
-      const double an = R->area_lat_north, as = R->area_lat_south, ral = R->r_area_lat;
-      const double mlat = (m_0 + m_n) * 0.5;
-      const double wl1 = (an * w1_n + as * w1_0) * ral, wl0 = (an * w_n + as * w_0) * ral;
-      double w;
-      if (k > 0 && k < g.nlev - 1) w = wl1 * (v_dn - v0) + wl0 * (v0 - v_up);
-      else if (k == 0) w = wl1 * (v_dn - v0);
-      else w = wl0 * (v0 - v_up);
-      dv = dv - qdiv(w, mlat) * 0.5;
+    // ---- dv (lat edges) -------------------------------------------------------------------------
+    if (half) {
+      // mfx_lon / pv_lon terms on pole rows are 0 (never computed by the reference)
+      const double pl_b = s0 ? plo_0 : 0.0;
+      const double qhu = (htw1 * (fx_m * (pla_0 + plo_m) + fx_0 * (pla_0 + pl_b)) +
+                          htw2 * (fx_mn * (pla_0 + plo_mn) + fx_0n * (pla_0 + plo_0n))) * 0.5;
+      const double dkedlat = (ke_n - ke0) * rda;
+      double dv = -qhu - dkedlat;
+      if (hyd) {
+        // :1181-1214 with we_lev_lat from interp_mod.F90:426-434
+        const double mlat = (m_0 + m_n) * 0.5;
+        const double wl1 = (an * w1_n + as * w1_0) * rala, wl0 = (an * w_n + as * w_0) * rala;
+        double w;
+        if (k > 0 && k < nlev - 1) w = wl1 * (v_dn - v0) + wl0 * (v0 - v_up);
+        else if (k == 0) w = wl1 * (v_dn - v0);
+        else w = wl0 * (v0 - v_up);
+        dv = dv - qdiv(w, mlat) * 0.5;
+      }
+      a.dv[c] = dv;
     }
-    a.dv[c] = dv;
   }
 }
 __global__ void __launch_bounds__(128, TEND_MINB) k_tend(Geo g, DMesh M, TendArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y;
   if (i >= g.nlon || j > g.je) return;
-  if (edge_block(g.nlon, 1)) tend_body<true>(g, M, a, i, j, k); else tend_body<false>(g, M, a, i, j, k);
+  if (edge_block(g.nlon, 1)) tend_col<true>(g, M, a, i, j); else tend_col<false>(g, M, a, i, j);
 }

@@ -18,7 +18,7 @@ static inline size_t filt_smem(const gmc_handle* h) { return (size_t)(h->g.nlon 
 static void run_forward_prepare(gmc_handle* h, DState& S) {
   const Geo& g = h->g;
   Fwd1Args f{S.u_f, S.v_f, S.m, S.mfx_lon, S.mfy_lat, S.u_lat, S.v_lon, S.ke, S.pv, S.div, h->cfg.ke_scheme, h->cfg.ke_cell_wgt};
-  LAUNCH(h, k_fwd1, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, f);
+  LAUNCH(h, k_fwd1, tile_grid(g, 1), tile_block(), 0, g, h->M, f);
   Pole1Args p{S.v_f, S.m, S.u_lat, S.mfy_lat, S.ke, S.div, S.pv, h->pole_dmf, h->cfg.pv_pole_stokes};
   LAUNCH(h, k_pole1, dim3(g.nlev, 2), 256, 0, g, h->M, p);
   PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv};
@@ -48,7 +48,7 @@ static void swm_step(gmc_handle* h, DState& old_, DState& star, DState& nw, doub
   t.we_lev = nullptr; t.du = h->du; t.dv = h->dv;
   t.gz_old = old_.gz; t.pole_dmf = h->pole_dmf; t.gz_new = nw.gz; t.dt = dt; t.grav = h->cfg.g;
   t.coriolis_scheme = h->cfg.coriolis_scheme; t.swm = 1;
-  LAUNCH(h, k_tend, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, t);
+  LAUNCH(h, k_tend, tile_grid(g, 1), tile_block(), 0, g, h->M, t);
   // update_state(tend1): gz_f = big(gz); gz = small1(gz); backward prepare: m = (gz - gzs)/g
   run_filter(h, nw.gz, 0, g.nlev, GMC_BIG_FILTER, nw.gz_f, GMC_SMALL_FILTER1, nw.gz, POST_SWM_M, nullptr, nw.m);
   // backward pass + update_state(tend2)
