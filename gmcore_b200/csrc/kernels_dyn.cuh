@@ -32,6 +32,12 @@ template <bool EDGE> __device__ __forceinline__ int wrapE(int i, int n) { return
 __device__ __forceinline__ bool edge_block(int n, int reach) {
   return blockIdx.x == 0 || (int)((blockIdx.x + 1) * blockDim.x) + reach > n;
 }
+// L2 prefetch of the line holding *p (no register is held while the line travels): the level-marching
+// kernels ask for level k+PF_AHEAD while they work on level k.
+#ifndef PF_AHEAD
+#define PF_AHEAD 1
+#endif
+__device__ __forceinline__ void pf_l2(const double* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // a / b for a field divisor: correctly rounded reciprocal then one multiply (<= 1 ulp off the IEEE
 // divide, about half its instruction count).
 __device__ __forceinline__ double qdiv(double a, double b) { return a * __drcp_rn(b); }
@@ -93,6 +99,7 @@ template <bool EDGE> __device__ __forceinline__ void fwd1_col(const Geo& g, cons
     // one memory phase: the 20 distinct neighbours of u, v, m (rows j-1 and j+1 always exist on the
     // device: >= 2 halo rows); everything below is register arithmetic in the reference's order
     const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
+    if (PF_AHEAD && k + PF_AHEAD < g.nlev) { pf_l2(ur + PF_AHEAD * pl); pf_l2(vr + PF_AHEAD * pl); pf_l2(mr + PF_AHEAD * pl); }
     const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
     const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
     const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
@@ -280,6 +287,10 @@ template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, cons
     const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
     const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
     const double* __restrict__ ker = a.ke + c;
+    if (PF_AHEAD && k + PF_AHEAD < nlev) {
+      pf_l2(fy + PF_AHEAD * pl); pf_l2(fx + PF_AHEAD * pl); pf_l2(pa + PF_AHEAD * pl); pf_l2(po + PF_AHEAD * pl); pf_l2(ker + PF_AHEAD * pl);
+      if (hyd) { pf_l2(a.m + c + PF_AHEAD * pl); pf_l2(a.we_lev + c + (PF_AHEAD + 1) * pl); if (k + PF_AHEAD + 1 < nlev) { pf_l2(a.u_f + c + (PF_AHEAD + 1) * pl); pf_l2(a.v_f + c + (PF_AHEAD + 1) * pl); } }
+    }
     const double ke0 = __ldg(ker);
     const double plo_0 = __ldg(po), pla_0 = half ? __ldg(pa) : 0.0;
     double fy_0 = 0, fy_p = 0, fy_0s = 0, fy_ps = 0, pla_p = 0, pla_0s = 0, pla_ps = 0, ke_p = 0;
