@@ -33,9 +33,14 @@ __device__ __forceinline__ bool edge_block(int n, int reach) {
   return blockIdx.x == 0 || (int)((blockIdx.x + 1) * blockDim.x) + reach > n;
 }
 // L2 prefetch of the line holding *p (no register is held while the line travels): the level-marching
-// kernels ask for level k+PF_AHEAD while they work on level k.
-#ifndef PF_AHEAD
-#define PF_AHEAD 1
+// kernels ask for a few levels ahead of the one they work on.  Measured at 0.25 deg L32: k_fwd1 (3 input
+// streams) 0.66 -> 0.55 ms with 2-3 levels ahead; k_tend (9 input streams) gets slower with it (the
+// prefetch instructions cost more issue slots than they hide).
+#ifndef FWD1_PF
+#define FWD1_PF 3
+#endif
+#ifndef TEND_PF
+#define TEND_PF 0
 #endif
 __device__ __forceinline__ void pf_l2(const double* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // a / b for a field divisor: correctly rounded reciprocal then one multiply (<= 1 ulp off the IEEE
@@ -99,7 +104,7 @@ template <bool EDGE> __device__ __forceinline__ void fwd1_col(const Geo& g, cons
     // one memory phase: the 20 distinct neighbours of u, v, m (rows j-1 and j+1 always exist on the
     // device: >= 2 halo rows); everything below is register arithmetic in the reference's order
     const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
-    if (PF_AHEAD && k + PF_AHEAD < g.nlev) { pf_l2(ur + PF_AHEAD * pl); pf_l2(vr + PF_AHEAD * pl); pf_l2(mr + PF_AHEAD * pl); }
+    if (FWD1_PF && k + FWD1_PF < g.nlev) { pf_l2(ur + FWD1_PF * pl); pf_l2(vr + FWD1_PF * pl); pf_l2(mr + FWD1_PF * pl); }
     const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
     const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
     const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
@@ -287,9 +292,9 @@ template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, cons
     const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
     const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
     const double* __restrict__ ker = a.ke + c;
-    if (PF_AHEAD && k + PF_AHEAD < nlev) {
-      pf_l2(fy + PF_AHEAD * pl); pf_l2(fx + PF_AHEAD * pl); pf_l2(pa + PF_AHEAD * pl); pf_l2(po + PF_AHEAD * pl); pf_l2(ker + PF_AHEAD * pl);
-      if (hyd) { pf_l2(a.m + c + PF_AHEAD * pl); pf_l2(a.we_lev + c + (PF_AHEAD + 1) * pl); if (k + PF_AHEAD + 1 < nlev) { pf_l2(a.u_f + c + (PF_AHEAD + 1) * pl); pf_l2(a.v_f + c + (PF_AHEAD + 1) * pl); } }
+    if (TEND_PF && k + TEND_PF < nlev) {
+      pf_l2(fy + TEND_PF * pl); pf_l2(fx + TEND_PF * pl); pf_l2(pa + TEND_PF * pl); pf_l2(po + TEND_PF * pl); pf_l2(ker + TEND_PF * pl);
+      if (hyd) { pf_l2(a.m + c + TEND_PF * pl); pf_l2(a.we_lev + c + (TEND_PF + 1) * pl); if (k + TEND_PF + 1 < nlev) { pf_l2(a.u_f + c + (TEND_PF + 1) * pl); pf_l2(a.v_f + c + (TEND_PF + 1) * pl); } }
     }
     const double ke0 = __ldg(ker);
     const double plo_0 = __ldg(po), pla_0 = half ? __ldg(pa) : 0.0;
