@@ -206,8 +206,17 @@ __global__ void __launch_bounds__(128) k_we_col(Geo g, DMesh M, WeArgs a) {
   double* wm = wm_s + threadIdx.x;
   double dphs = 0, mf = 0;
   // calc_grad_mf + calc_dphsdt: running sums in the reference's k order; prefix parked in shared memory
+#ifndef WECOL_PF
+#define WECOL_PF 4
+#endif
+  const bool pfl = (i & 15) == 0;      // one prefetch per 128-byte line
+#pragma unroll 4
   for (int k = 0; k < g.nlev; ++k) {
     double dlon, dlat;
+    if (WECOL_PF && pfl) {
+      pf_l2(a.m_lev + c0 + (k + 1) * st);
+      if (k + WECOL_PF < g.nlev) { pf_l2(a.mfx_lon + c0 + (k + WECOL_PF) * st); pf_l2(a.mfy_lat + c0 + (k + WECOL_PF) * st); }
+    }
     if (pole) { dlon = 0.0; dlat = __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k); }
     else {
       const double* fx = a.mfx_lon + c0 + k * st; const double* fy = a.mfy_lat + c0 + k * st;
@@ -407,6 +416,13 @@ __global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
     const int c = c0 + k * st;
     // all of this level's loads first, then the PPM arithmetic
     const int k1 = k + 2;   // lower half level of full level k+1
+#ifndef PTCOL_PF
+#define PTCOL_PF 3
+#endif
+    if (PTCOL_PF && (i & 15) == 0 && k + PTCOL_PF < g.nlev) {
+      const int cp = c + PTCOL_PF * st;
+      pf_l2(a.cflz + cp + st); pf_l2(a.we_lev + cp + st); pf_l2(a.ptf_lon + cp); pf_l2(a.ptf_lat + cp); pf_l2(a.pt_old + cp); pf_l2(a.m_old + cp);
+    }
     double cz = 0, w = 0, fx0 = 0, fxm = 0, fy0 = 0, fys = 0, pdm = 0;
     if (k1 <= g.nlev) { cz = __ldg(a.cflz + c + st); w = __ldg(a.we_lev + c + st); }
     if (pole) pdm = __ldg(a.pole_ptf + (j == 1 ? 0 : g.nlev) + k);
