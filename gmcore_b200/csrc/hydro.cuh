@@ -191,11 +191,16 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   u.ph_exn_lev = nw.ph_exn_lev; u.gz_lev = nw.gz_lev; u.du_fwd = h->du; u.dv_fwd = h->dv;
   u.u_old = old_.u; u.v_old = old_.v; u.u_new = nw.u; u.v_new = nw.v; u.dt = dt; u.swm = 0; u.blend = 0;
   LAUNCH(h, k_uv_update_h, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, u);
-  run_filter(h, nw.u, 0, g.nlev, -1, nullptr, GMC_SMALL_FILTER2, nw.u);
-  run_filter(h, nw.v, 1, g.nlev, -1, nullptr, GMC_SMALL_FILTER2, nw.v);
-  if (g.has_south || g.has_north) LAUNCH(h, k_v_pole_blend, dim3((g.nlon + 127) / 128, g.nlev, 2), 128, 0, g, nw.v);
-  run_filter(h, nw.u, 0, g.nlev, GMC_BIG_FILTER, nw.u_f, -1, nullptr);
-  run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr);
+  // small_filter2 in place, then big_filter -> u_f / v_f from the same staged row.  The two pole-adjacent
+  // v rows are blended with their neighbours first (time_schemes_mod.F90:225-233) and big-filtered after.
+  run_filter_chain(h, nw.u, 0, g.nlev, GMC_SMALL_FILTER2, nw.u, GMC_BIG_FILTER, nw.u_f);
+  const int sa = g.has_south ? 1 : -1000, sb = g.has_north ? g.nhalf : -1000;
+  run_filter_chain(h, nw.v, 1, g.nlev, GMC_SMALL_FILTER2, nw.v, GMC_BIG_FILTER, nw.v_f, sa, sb);
+  if (g.has_south || g.has_north) {
+    LAUNCH(h, k_v_pole_blend, dim3((g.nlon + 127) / 128, g.nlev, 2), 128, 0, g, nw.v);
+    if (g.has_south) { Geo gr = g; gr.hjb = gr.hje = 1; run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr, POST_NONE, nullptr, nullptr, &gr); }
+    if (g.has_north) { Geo gr = g; gr.hjb = gr.hje = g.nhalf; run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr, POST_NONE, nullptr, nullptr, &gr); }
+  }
 }
 // arrays of a state that travel at the per-stage exchange point
 static HaloSet stage_halo_set(gmc_handle* b, int it) {

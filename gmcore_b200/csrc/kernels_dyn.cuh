@@ -104,7 +104,7 @@ template <bool EDGE> __device__ __forceinline__ void fwd1_col(const Geo& g, cons
     // one memory phase: the 20 distinct neighbours of u, v, m (rows j-1 and j+1 always exist on the
     // device: >= 2 halo rows); everything below is register arithmetic in the reference's order
     const double* __restrict__ ur = a.u + c; const double* __restrict__ vr = a.v + c; const double* __restrict__ mr = a.m + c;
-    if (FWD1_PF && k + FWD1_PF < g.nlev) { pf_l2(ur + FWD1_PF * pl); pf_l2(vr + FWD1_PF * pl); pf_l2(mr + FWD1_PF * pl); }
+    if (FWD1_PF && (i & 15) == 0 && k + FWD1_PF < g.nlev) { pf_l2(ur + FWD1_PF * pl); pf_l2(vr + FWD1_PF * pl); pf_l2(mr + FWD1_PF * pl); }
     const double u_m = __ldg(ur + dm), u_0 = __ldg(ur);
     const double u_mn = __ldg(ur + n + dm), u_0n = __ldg(ur + n);
     const double v_0 = __ldg(vr), v_p = __ldg(vr + dp);
@@ -292,7 +292,7 @@ template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, cons
     const double* __restrict__ fy = a.mfy_lat + c; const double* __restrict__ fx = a.mfx_lon + c;
     const double* __restrict__ pa = a.pv_lat + c;  const double* __restrict__ po = a.pv_lon + c;
     const double* __restrict__ ker = a.ke + c;
-    if (TEND_PF && k + TEND_PF < nlev) {
+    if (TEND_PF && (i & 15) == 0 && k + TEND_PF < nlev) {
       pf_l2(fy + TEND_PF * pl); pf_l2(fx + TEND_PF * pl); pf_l2(pa + TEND_PF * pl); pf_l2(po + TEND_PF * pl); pf_l2(ker + TEND_PF * pl);
       if (hyd) { pf_l2(a.m + c + TEND_PF * pl); pf_l2(a.we_lev + c + (TEND_PF + 1) * pl); if (k + TEND_PF + 1 < nlev) { pf_l2(a.u_f + c + (TEND_PF + 1) * pl); pf_l2(a.v_f + c + (TEND_PF + 1) * pl); } }
     }

@@ -89,11 +89,11 @@ __global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
     double ua = 0, ub = 0, va = 0, vb = 0;
     int lx = 0, ly = 0; bool inr = false;
     if (dox) {
-      lx = (int)floor(i1 + (x - x0) * rdx);
+      lx = __double2int_rd(i1 + (x - x0) * rdx);
       ua = __ldg(ur + wrapi(lx - 1, g.nlon)); ub = __ldg(ur + wrapi(lx, g.nlon));
     }
     if (doy) {
-      ly = (int)floor(j + (y - y0) * rdy);
+      ly = __double2int_rd(j + (y - y0) * rdy);
       inr = !(ly < 1 || ly > g.nhalf - 1);
       if (inr) { va = ldW(a.v, g, i, ly, k); vb = ldW(a.v, g, i, ly + 1, k); }
     }

@@ -18,6 +18,9 @@ struct FilterArgs {
   DFilter f2; double* out2;     // out2 = post(f2(in))    (may be NULL, may alias in)
   int use_f1, use_f2;           // 0: plain copy for that output
   int post; const double* gzs; double grav; const double* mdiv; double* out_m;
+  // chain: out2 = f2(in) then out1 = f1(out2) from a second staged row (small_filter2 -> big_filter on u, v,
+  // time_schemes_mod.F90:216-236); f1 is skipped on rows skip_a / skip_b (the pole-adjacent v rows are blended first)
+  int chain, row2_off, skip_a, skip_b;
 };
 __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   extern __shared__ double srow[];
@@ -26,7 +29,7 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   const int n1 = a.use_f1 ? (a.half_lat ? a.f1.ngrid_lat[j + 1] : a.f1.ngrid_lon[j + 1]) : 0;
   const int n2 = a.use_f2 ? (a.half_lat ? a.f2.ngrid_lat[j + 1] : a.f2.ngrid_lon[j + 1]) : 0;
   const int hn1 = n1 > 1 ? (n1 - 1) / 2 : 0, hn2 = n2 > 1 ? (n2 - 1) / 2 : 0;
-  const int hn = hn1 > hn2 ? hn1 : hn2;
+  const int hn = a.chain ? hn2 : (hn1 > hn2 ? hn1 : hn2);
   const double* __restrict__ row = a.in + gidx(g, 0, j, k);
   const int nlon = g.nlon;
   for (int x = threadIdx.x; x < nlon + 2 * hn; x += blockDim.x) {
@@ -37,6 +40,29 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   const double* __restrict__ w1 = a.half_lat ? a.f1.wgt_lat + (size_t)(j + 1) * a.f1.ld_lat : a.f1.wgt_lon + (size_t)(j + 1) * a.f1.ld_lon;
   const double* __restrict__ w2 = a.half_lat ? a.f2.wgt_lat + (size_t)(j + 1) * a.f2.ld_lat : a.f2.wgt_lon + (size_t)(j + 1) * a.f2.ld_lon;
   const long long base = gidx(g, 0, j, k);
+  if (a.chain) {
+    double* __restrict__ srow2 = srow + a.row2_off;
+    for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
+      double s;
+      if (n2 > 1) { s = 0; const double* x = srow + i; for (int t = 0; t < n2; ++t) s += __ldg(w2 + t) * x[t]; }
+      else s = srow[i + hn];
+      a.out2[base + i] = s;
+      srow2[i + hn1] = s;
+    }
+    if (j == a.skip_a || j == a.skip_b) return;     // block-uniform
+    __syncthreads();
+    if (n1 > 1) {
+      for (int x = threadIdx.x; x < hn1; x += blockDim.x) { srow2[x] = srow2[x + nlon]; srow2[hn1 + nlon + x] = srow2[hn1 + x]; }
+      __syncthreads();
+    }
+    for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
+      double s;
+      if (n1 > 1) { s = 0; const double* x = srow2 + i; for (int t = 0; t < n1; ++t) s += __ldg(w1 + t) * x[t]; }
+      else s = srow2[i + hn1];
+      a.out1[base + i] = s;
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
     if (a.out1) {
       double s;

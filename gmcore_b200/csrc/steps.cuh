@@ -33,8 +33,23 @@ static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, 
   a.f1 = h->filt[f1 >= 0 ? f1 : 0]; a.out1 = out1; a.use_f1 = f1 >= 0;
   a.f2 = h->filt[f2 >= 0 ? f2 : 0]; a.out2 = out2; a.use_f2 = f2 >= 0;
   a.post = post; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = mdiv; a.out_m = out_m;
+  a.chain = 0; a.row2_off = 0; a.skip_a = a.skip_b = -1000;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
   LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
+}
+
+// out2 = f2(in), out1 = f1(out2) in one launch (one read of the raw row instead of two passes)
+static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int nlev, int f2, double* out2, int f1, double* out1,
+                             int skip_a = -1000, int skip_b = -1000) {
+  const Geo& g = h->g;
+  FilterArgs a;
+  a.in = in; a.half_lat = half_lat; a.nlev = nlev;
+  a.f1 = h->filt[f1]; a.out1 = out1; a.use_f1 = 1;
+  a.f2 = h->filt[f2]; a.out2 = out2; a.use_f2 = 1;
+  a.post = POST_NONE; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = nullptr; a.out_m = nullptr;
+  a.chain = 1; a.row2_off = g.nlon + 2 * h->max_hn; a.skip_a = skip_a; a.skip_b = skip_b;
+  const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
+  LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, 2 * filt_smem(h), g, a);
 }
 
 #include "hydro.cuh"
