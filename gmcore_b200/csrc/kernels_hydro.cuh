@@ -273,61 +273,74 @@ struct HflxArgs {
   double *mfx, *mfy;
   int jx0, jx1, jy0, jy1;       // rows of the x flux / half rows of the y flux (band mode)
 };
-__global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
-  if (i >= g.nlon || j > g.je) return;
+// One memory phase in the common case: |cfly| <= 1 always and |cflx| < 1 away from the poles, so the
+// upwind cell is the edge's west/east (south/north) neighbour and its 5-point stencil lies inside the
+// 6-point window i-2..i+3 (j-2..j+3), whose addresses do not depend on the CFL numbers -- the window
+// loads go out together with the CFL / velocity loads.  Lanes with |cflx| >= 1 (polar rows) re-gather
+// around their own upwind cell and add the whole-cell segment sum (ffsl_mod.F90:831-848).
+template <bool EDGE> __device__ __forceinline__ void hflx_body(const Geo& g, const HflxArgs& a, int i, int j, int k) {
   const int n = g.nlon, c = gidx(g, i, j, k), rb = c - i;
   const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;     // warp-uniform
   const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
-  // Phase 1: the four independent loads (CFL numbers and advecting velocities) go out together,
-  // phase 2: both 5-point upwind stencils -- two dependent memory round trips per thread, not four.
-  const double cx = dox ? __ldg(a.cflx + c) : 0.0;
-  const double cy = doy ? __ldg(a.cfly + c) : 0.0;
-  const double uu = dox ? __ldg(a.u + c) : 0.0;
-  const double vv = doy ? __ldg(a.v + c) : 0.0;
-  const int ci = (int)cx;
-  const int iu = wrapi(cx > 0 ? i - ci : i - ci + 1, n);
-  const int ju = cy > 0 ? j : j + 1;
-  double x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0, y0 = 0, y1 = 0, y2 = 0, y3 = 0, y4 = 0;
+  double cx = 0, uu = 0, cy = 0, vv = 0;
+  double xw0 = 0, xw1 = 0, xw2 = 0, xw3 = 0, xw4 = 0, xw5 = 0, yw0 = 0, yw1 = 0, yw2 = 0, yw3 = 0, yw4 = 0, yw5 = 0;
   const double* __restrict__ mxr = a.mx + rb;
-  if (cx != 0) {
-    x0 = __ldg(mxr + wrapi(iu - 2, n)); x1 = __ldg(mxr + wrapi(iu - 1, n)); x2 = __ldg(mxr + iu);
-    x3 = __ldg(mxr + wrapi(iu + 1, n)); x4 = __ldg(mxr + wrapi(iu + 2, n));
+  if (dox) {
+    cx = __ldg(a.cflx + c); uu = __ldg(a.u + c);
+    xw0 = __ldg(mxr + wrapE<EDGE>(i - 2, n)); xw1 = __ldg(mxr + wrapE<EDGE>(i - 1, n)); xw2 = __ldg(mxr + i);
+    xw3 = __ldg(mxr + wrapE<EDGE>(i + 1, n)); xw4 = __ldg(mxr + wrapE<EDGE>(i + 2, n)); xw5 = __ldg(mxr + wrapE<EDGE>(i + 3, n));
   }
-  if (cy != 0) {
+  if (doy) {
+    cy = __ldg(a.cfly + c); vv = __ldg(a.v + c);
     if (j >= 3 && j + 3 <= g.nlat) {   // away from the poles: no mirror, rows at fixed strides from one address
-      const double* __restrict__ myc = a.my + c + (ju - j) * n;
-      y0 = __ldg(myc - 2 * n); y1 = __ldg(myc - n); y2 = __ldg(myc); y3 = __ldg(myc + n); y4 = __ldg(myc + 2 * n);
+      const double* __restrict__ myc = a.my + c;
+      yw0 = __ldg(myc - 2 * n); yw1 = __ldg(myc - n); yw2 = __ldg(myc); yw3 = __ldg(myc + n); yw4 = __ldg(myc + 2 * n); yw5 = __ldg(myc + 3 * n);
     } else {
-      y0 = ldF(a.my, g, i, ju - 2, k); y1 = ldF(a.my, g, i, ju - 1, k); y2 = ldF(a.my, g, i, ju, k);
-      y3 = ldF(a.my, g, i, ju + 1, k); y4 = ldF(a.my, g, i, ju + 2, k);
+      yw0 = ldF(a.my, g, i, j - 2, k); yw1 = ldF(a.my, g, i, j - 1, k); yw2 = ldF(a.my, g, i, j, k);
+      yw3 = ldF(a.my, g, i, j + 1, k); yw4 = ldF(a.my, g, i, j + 2, k); yw5 = ldF(a.my, g, i, j + 3, k);
     }
   }
   if (dox) {
     double flux = 0;
     if (cx != 0) {
+      const int ci = (int)cx;
       const double cf = cx - ci;
-      double s1, s2, sm = 0;
-      if (cx > 0) { s1 = 1 - cf; s2 = 1; for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
-      else { s1 = 0; s2 = -cf; for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+      const bool pos = cx > 0;
+      double x0, x1, x2, x3, x4, sm = 0;
+      if (ci == 0) {
+        x0 = pos ? xw0 : xw1; x1 = pos ? xw1 : xw2; x2 = pos ? xw2 : xw3; x3 = pos ? xw3 : xw4; x4 = pos ? xw4 : xw5;
+      } else {
+        const int iu = wrapi(pos ? i - ci : i - ci + 1, n);
+        x0 = __ldg(mxr + wrapi(iu - 2, n)); x1 = __ldg(mxr + wrapi(iu - 1, n)); x2 = __ldg(mxr + iu);
+        x3 = __ldg(mxr + wrapi(iu + 1, n)); x4 = __ldg(mxr + wrapi(iu + 2, n));
+        if (pos) { for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+        else { for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+      }
+      const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
       double ml, dm, m6;
       ppm(x0, x1, x2, x3, x4, ml, dm, m6);
-      flux = qdiv((cx > 0 ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
+      flux = qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
     }
     a.mfx[c] = flux;
   }
   if (doy) {
     double flux = 0;
     if (cy != 0) {
-      double s1, s2;
-      if (cy > 0) { s1 = 1 - cy; s2 = 1; } else { s1 = 0; s2 = -cy; }
+      const bool pos = cy > 0;
+      const double y0 = pos ? yw0 : yw1, y1 = pos ? yw1 : yw2, y2 = pos ? yw2 : yw3, y3 = pos ? yw3 : yw4, y4 = pos ? yw4 : yw5;
+      const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
       double ml, dm, m6;
       ppm(y0, y1, y2, y3, y4, ml, dm, m6);
-      flux = qdiv((cy > 0 ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
+      flux = qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
     }
     a.mfy[c] = flux;
   }
+}
+__global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 3) || blockIdx.x * blockDim.x < 2) hflx_body<true>(g, a, i, j, k); else hflx_body<false>(g, a, i, j, k);
 }
 
 // Intermediate fields of the inner advective step (ffsl_mod.F90:354-406)
