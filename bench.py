@@ -52,11 +52,22 @@ KERNEL_PASSES = {
 # hydrostatic core (k_tend / k_uv_update read more there); k_hflx: 5 reads on the inner call
 # (mx == my) and 6 on the outer call + 2 writes -> mean 7.5
 KERNEL_PASSES_HYDRO = {
-    "k_hflx": 7.5, "k_fwd1": 3 + 7, "k_tend": 9 + 2, "k_cfl": 2 + 4, "k_pt_col": 7 + 2, "k_we_col": 3 + 2,
+    "k_hflx": 7.5, "k_fwd1": 3 + 7, "k_tend": 9 + 2, "k_cfl": 2 + 4, "k_pt_col": 7 + 1, "k_we_col": 3 + 2,
     "k_uv_update_h": 6 + 2, "k_gz_col": 1 + 2, "k_tracer_v": 4 + 1, "k_ffsl_q": 5 + 2, "k_pv_edge": 5 + 2,
     "k_ph": 0 + 3, "k_accum": 2 + 2, "k_diag_partial": 10, "k_filter_rows": 1 + 1,
 }
 L2_BYTES = 126e6
+
+
+def ncu_traffic(kernel, workload):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture of this workload
+    (profiles/r01_ncu_traffic.json, written by tools/ncu_raw_summary.py --json), or None."""
+    p = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    try:
+        t = json.load(open(p))
+        return t["kernels"][kernel]["dram_bytes_per_launch"] if t.get("workload") == workload else None
+    except Exception:
+        return None
 
 
 def measured_peak_gbs():
@@ -284,7 +295,9 @@ def _main(out):
     achieved = (passes * 8 * n3_k / (mean_ms * 1e-3) / 1e9) if passes else None
     step_gbs = wl["bytes_per_cell"] * n3 / (ms / K * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": top[0], "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None,
+                "traffic": ncu_traffic(top[0], name) if world == 1 else None,
+                "algorithmic_bytes_per_launch": (passes * 8 * n3_k) if passes else None,
                 "kernel_share_of_step": top[1][1] / tot, "kernel_mean_ms": mean_ms,
                 "whole_step_algorithmic_gbs": step_gbs, "whole_step_frac": step_gbs / (peak * (world if banded else 1)),
                 "kernels_ms_per_step": {k: v[1] / K for k, v in sorted(rep.items(), key=lambda kv: -kv[1][1])}}

@@ -2,6 +2,7 @@
 // (time_integrate and the pre-loop of gmcore_run) as sm_100a CUDA kernels.
 // There is no CPU fallback: every entry point fails if no CUDA device is usable.
 #include <algorithm>
+#include <cstdlib>
 #include "handle.cuh"
 #include "kernels_dyn.cuh"
 #include "kernels_update.cuh"
@@ -79,6 +80,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   h->stage_bytes = (size_t)(g.nlon + 2 * cfg->hx) * ((g.je - g.jb + 1) + 2 * cfg->hy) * (g.nlev + 4) * sizeof(double);
   if (!rc) { double* p; rc = dev_alloc(h, &p, h->stage_bytes / sizeof(double)); h->stage_img = p; }
   if (rc) { snprintf(g_create_err, sizeof(g_create_err), "%s", h->err); gmc_destroy(h); return 4; }
+  { const char* e = getenv("GMCORE_DEBUG_FIELDS"); h->keep_dpt = e && e[0] == '1'; }
   h->nstep = (int)(cfg->dt_adv / cfg->dt_dyn);
   h->alert_period = cfg->dt_adv; h->alert_last = -cfg->dt_adv;
   *out = h;

@@ -73,6 +73,7 @@ struct gmc_handle {
   void* nccl_comm = nullptr;          // one-process-per-GPU mode
   bool mesh_set = false, filters_set[3] = {false, false, false};
   int max_hn = 0;
+  bool keep_dpt = false;              // GMCORE_DEBUG_FIELDS=1: also store the dpt tendency (parity tests read it back)
 };
 
 

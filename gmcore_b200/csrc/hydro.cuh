@@ -178,7 +178,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   BatchRef B{star.u_f, star.v_f, star.mfx_lon, star.mfy_lat, h->cflx, h->cfly, h->divx, h->divy};
   run_ffsl_h(h, B, star.pt, h->ptf_lon, h->ptf_lat, dt);
   run_pole_sum(h, h->ptf_lat, h->pole_work + 2 * g.nlev, nullptr, 1);
-  PtColArgs pc{star.pt, h->ptf_lon, h->ptf_lat, h->pole_work + 2 * g.nlev, star.we_lev, h->cflz, old_.pt, old_.m, nw.pt, h->dpt, dt};
+  PtColArgs pc{star.pt, h->ptf_lon, h->ptf_lat, h->pole_work + 2 * g.nlev, star.we_lev, h->cflz, old_.pt, old_.m, nw.pt, h->keep_dpt ? h->dpt : nullptr, dt};
   LAUNCH(h, k_pt_col, gridg(g01, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g01, h->M, pc);
   // ---- update_state(tend1): rows jb..je+1 (the Lin97 PGF of half row je reads row je+1) ----
   LAUNCH(h, k_axpy2d, gridg(g01, 1), 128, 0, g01, old_.phs, h->dphs, nw.phs, dt);

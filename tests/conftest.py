@@ -5,6 +5,8 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the parity tests read the dpt tendency back (gmc_get_field); production runs do not store it
+os.environ.setdefault("GMCORE_DEBUG_FIELDS", "1")
 sys.path.insert(0, ROOT)
 
 

@@ -28,3 +28,17 @@ for r in data:
           f"{g(r, 'lts__throughput.avg.pct_of_peak_sustained_elapsed'):5.1f} {g(r, 'sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active'):5.1f} "
           f"{g(r, 'sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active'):5.1f} {g(r, 'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active'):5.1f} "
           f"{g(r, 'sm__warps_active.avg.pct_of_peak_sustained_active'):5.1f} {g(r, 'launch__registers_per_thread'):4.0f} {inst * 32 / thr:7.0f} {inst / (148 * 4) / cyc if cyc == cyc else float('nan'):5.2f}")
+
+if "--json" in sys.argv:
+    import json
+    out = {"workload": sys.argv[sys.argv.index("--json") + 1], "source": "ncu --set full --clock-control none, one launch per kernel (mean over the captured launches)", "kernels": {}}
+    acc = {}
+    for r in data:
+        name = r[ix['Kernel Name']].split('(')[0]
+        b = scaled(r, 'dram__bytes_read.sum', 1) + scaled(r, 'dram__bytes_write.sum', 1)
+        t = scaled(r, 'gpu__time_duration.sum', 1e-3)
+        acc.setdefault(name, []).append((b, t))
+    for k, v in acc.items():
+        big = [x for x in v if x[0] >= 0.5 * max(y[0] for y in v)]     # ignore the 2-D / few-row launches of the same kernel
+        out["kernels"][k] = {"dram_bytes_per_launch": sum(x[0] for x in big) / len(big), "ncu_ms_per_launch": sum(x[1] for x in big) / len(big), "launches": len(big)}
+    json.dump(out, open(sys.argv[sys.argv.index("--json") + 2], "w"), indent=1)
