@@ -247,7 +247,23 @@ class GmcoreBand(GmcoreGPU):
                                             abi.dptr(self._b(ic["pt_or_gz"], "cell")), abi.dptr(self._b(ic.get("phs"), "2d"))))
 
     def set_tracers(self, q):
-        self._chk(self.lib.gmc_set_tracers(self.h, abi.dptr(np.ascontiguousarray(np.stack([self._b(x, "cell") for x in q])))))
+        self.set_tracers_sliced(self.slice_tracers(q))
+
+    # band slicing of global arrays is host set-up; the *_sliced entry points take this rank's rows directly
+    # (what a banded Fortran host owns in the first place)
+    def slice_state(self, ic):
+        loc = {"gzs": "2d", "u_lon": "lon", "v_lat": "lat", "pt_or_gz": "cell", "phs": "2d"}
+        return {k: self._b(ic.get(k), loc[k]) for k in loc}
+
+    def slice_tracers(self, q):
+        return np.ascontiguousarray(np.stack([self._b(x, "cell") for x in q]))
+
+    def set_state_sliced(self, b, itime=1):
+        self._chk(self.lib.gmc_set_static(self.h, abi.dptr(b["gzs"])))
+        self._chk(self.lib.gmc_upload_state(self.h, itime, abi.dptr(b["u_lon"]), abi.dptr(b["v_lat"]), abi.dptr(b["pt_or_gz"]), abi.dptr(b["phs"])))
+
+    def set_tracers_sliced(self, qb):
+        self._chk(self.lib.gmc_set_tracers(self.h, abi.dptr(qb)))
 
     def band_shape(self, loc):
         s = list(self.host.shape(loc))
