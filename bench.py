@@ -312,6 +312,12 @@ def _main(out):
     if q0 is not None:
         q0p = pinned_like(gpu2.slice_tracers(q0) if banded else q0)[0]
     h2d = sum(v.nbytes for v in icp.values() if v is not None)
+    # untimed warm-up of this handle (first-use costs: NCCL connection set-up, pinned-page registration)
+    (gpu2.set_state_sliced if banded else gpu2.set_state)(icp)
+    if q0 is not None:
+        (gpu2.set_tracers_sliced if banded else gpu2.set_tracers)(q0p)
+    gpu2.prepare_run(); gpu2.time_integrate(); gpu2.diagnose(); gpu2.synchronize()
+    gpu2.reset_clock()
     barrier(world); torch.cuda.synchronize()
     t0 = time.perf_counter()
     (gpu2.set_state_sliced if banded else gpu2.set_state)(icp)

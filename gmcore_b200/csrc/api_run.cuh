@@ -131,6 +131,15 @@ int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int
   return bad;
 }
 
+// Back to the state right after gmc_create + set_*: step counter bookkeeping of the tracer batch and the
+// alert clock (time_init, time_mod.F90:61-98).  The host then uploads a state and calls gmc_prepare_run again.
+int gmc_reset_clock(gmc_handle* h) {
+  for_bands(h, [&](gmc_handle* b) {
+    b->uv_step = b->mf_step = b->we_step = 0; b->q_old = 0; b->q_new = 1;
+    b->alert_last = -b->cfg.dt_adv; b->alert_ring = false;
+  });
+  return 0;
+}
 int gmc_set_tracers(gmc_handle* h, const double* q) { return hydro_set_tracers(h, q); }
 int gmc_get_tracers(gmc_handle* h, double* q) { return hydro_get_tracers(h, q); }
 

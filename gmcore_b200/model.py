@@ -18,7 +18,7 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error",
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock",
                "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init"]
 
 
@@ -59,6 +59,7 @@ def load_library():
     lib.gmc_timer_elapsed_ms.argtypes = [V, P]
     lib.gmc_profile.argtypes = [V, C.c_int]
     lib.gmc_profile_report.argtypes = [V, C.c_char_p, C.c_int]
+    lib.gmc_reset_clock.argtypes = [V]
     lib.gmc_stream.restype = C.c_void_p
     lib.gmc_stream.argtypes = [V]
     _LIB = lib
@@ -110,6 +111,11 @@ class GmcoreGPU:
         q = np.zeros((self.host.cfg.ntracers,) + self.host.shape("cell"))
         self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
         return q
+
+    def reset_clock(self):
+        """time_init: step counter 0, old/new = 1/2, tracer-batch sample counters cleared (before a fresh upload)."""
+        self._chk(self.lib.gmc_reset_clock(self.h))
+        self.old.value, self.new.value, self.time_step.value = 1, 2, 0
 
     def prepare_run(self):
         self._chk(self.lib.gmc_prepare_run(self.h, self.old.value))

@@ -134,6 +134,9 @@ int gmc_group_link(gmc_handle** hs, int n);
 int gmc_nccl_unique_id(char id[128]);
 int gmc_nccl_init(gmc_handle* h, const char id[128]);
 
+/* time_init (time_mod.F90:61-98): clear the step / tracer-batch sample counters before a fresh upload. */
+int gmc_reset_clock(gmc_handle* h);
+
 int gmc_synchronize(gmc_handle* h);
 /* Device milliseconds spent in, and kernels launched by, calls on this handle
  * since the last reset (CUDA events on the handle's stream). */
