@@ -190,6 +190,8 @@ int gmc_set_filters(gmc_handle* h, int which, const int* ngrid_lon, const double
   F.max_hn = mx > 1 ? (mx - 1) / 2 : 0;
   if (F.max_hn > h->max_hn) h->max_hn = F.max_hn;
   if (F.max_hn >= c.nlon) { snprintf(h->err, sizeof(h->err), "filter wider than the zonal circle"); return 1; }
+  // the row filter stages two rows and two weight vectors in shared memory (up to 227 KB per block on sm_100a)
+  cudaFuncSetAttribute(k_filter_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   h->filters_set[which] = !rc;
   return rc;
 }

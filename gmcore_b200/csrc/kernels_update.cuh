@@ -21,7 +21,34 @@ struct FilterArgs {
   // chain: out2 = f2(in) then out1 = f1(out2) from a second staged row (small_filter2 -> big_filter on u, v,
   // time_schemes_mod.F90:216-236); f1 is skipped on rows skip_a / skip_b (the pole-adjacent v rows are blended first)
   int chain, row2_off, skip_a, skip_b;
+  int mh;                       // largest filter half-width (shared-memory layout)
 };
+// Row convolution, 4 outputs per thread a quarter row apart (i, i+S, i+2S, i+3S): one shared-memory read of
+// the weight serves four multiply-adds, the four x streams stay bank-conflict free and the stores coalesced.
+// Every output accumulates its taps left to right (sum(wgt(1:n) * x(i-hn:i+hn))) as before.
+__device__ __forceinline__ double conv1(const double* __restrict__ x, const double* __restrict__ w, int n) {
+  double s = 0;
+  for (int t = 0; t < n; ++t) s += w[t] * x[t];
+  return s;
+}
+// out[i] = post(f(x))[i] for the whole row; xs = staged row with halo hn_s, filter half-width hnf (<= hn_s)
+template <class Store> __device__ __forceinline__ void conv_row(const double* __restrict__ xs, int hn_s, const double* __restrict__ w, int n, int nlon, Store store) {
+  const int hnf = n > 1 ? (n - 1) / 2 : 0;
+  const double* __restrict__ x0 = xs + (hn_s - hnf);
+  if (n <= 1) { for (int i = threadIdx.x; i < nlon; i += blockDim.x) store(i, xs[i + hn_s]); return; }
+  const int S = (nlon + 3) >> 2;
+  for (int r = threadIdx.x; r < S; r += blockDim.x) {
+    if (r + 3 * S < nlon) {
+      const double* __restrict__ xa = x0 + r; const double* __restrict__ xb = xa + S; const double* __restrict__ xc = xb + S; const double* __restrict__ xd = xc + S;
+      double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+      for (int t = 0; t < n; ++t) { const double wt = w[t]; s0 += wt * xa[t]; s1 += wt * xb[t]; s2 += wt * xc[t]; s3 += wt * xd[t]; }
+      store(r, s0); store(r + S, s1); store(r + 2 * S, s2); store(r + 3 * S, s3);
+    } else {
+      for (int q = 0; q < 4; ++q) if (r + q * S < nlon) store(r + q * S, conv1(x0 + r + q * S, w, n));
+    }
+  }
+}
+// shared memory: [row: nlon+2*mh][row2: nlon+2*mh][w1: 2*mh+1][w2: 2*mh+1], mh = a.mh (largest half-width of any filter)
 __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   extern __shared__ double srow[];
   const int j = (a.half_lat ? g.hjb : g.jb) + blockIdx.x, k = blockIdx.y;
@@ -30,55 +57,38 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   const int n2 = a.use_f2 ? (a.half_lat ? a.f2.ngrid_lat[j + 1] : a.f2.ngrid_lon[j + 1]) : 0;
   const int hn1 = n1 > 1 ? (n1 - 1) / 2 : 0, hn2 = n2 > 1 ? (n2 - 1) / 2 : 0;
   const int hn = a.chain ? hn2 : (hn1 > hn2 ? hn1 : hn2);
+  const int nlon = g.nlon, rs = nlon + 2 * a.mh;
+  double* __restrict__ srow2 = srow + rs;
+  double* __restrict__ ws1 = srow + 2 * rs; double* __restrict__ ws2 = ws1 + (2 * a.mh + 1);
   const double* __restrict__ row = a.in + gidx(g, 0, j, k);
-  const int nlon = g.nlon;
   for (int x = threadIdx.x; x < nlon + 2 * hn; x += blockDim.x) {
     int i = x - hn; i = i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
     srow[x] = row[i];
   }
-  __syncthreads();
   const double* __restrict__ w1 = a.half_lat ? a.f1.wgt_lat + (size_t)(j + 1) * a.f1.ld_lat : a.f1.wgt_lon + (size_t)(j + 1) * a.f1.ld_lon;
   const double* __restrict__ w2 = a.half_lat ? a.f2.wgt_lat + (size_t)(j + 1) * a.f2.ld_lat : a.f2.wgt_lon + (size_t)(j + 1) * a.f2.ld_lon;
-  const long long base = gidx(g, 0, j, k);
+  for (int t = threadIdx.x; t < n1; t += blockDim.x) ws1[t] = __ldg(w1 + t);
+  for (int t = threadIdx.x; t < n2; t += blockDim.x) ws2[t] = __ldg(w2 + t);
+  __syncthreads();
+  const int base = gidx(g, 0, j, k);
   if (a.chain) {
-    double* __restrict__ srow2 = srow + a.row2_off;
-    for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
-      double s;
-      if (n2 > 1) { s = 0; const double* x = srow + i; for (int t = 0; t < n2; ++t) s += __ldg(w2 + t) * x[t]; }
-      else s = srow[i + hn];
-      a.out2[base + i] = s;
-      srow2[i + hn1] = s;
-    }
+    conv_row(srow, hn, ws2, n2, nlon, [&](int i, double s) { a.out2[base + i] = s; srow2[i + hn1] = s; });
     if (j == a.skip_a || j == a.skip_b) return;     // block-uniform
     __syncthreads();
     if (n1 > 1) {
       for (int x = threadIdx.x; x < hn1; x += blockDim.x) { srow2[x] = srow2[x + nlon]; srow2[hn1 + nlon + x] = srow2[hn1 + x]; }
       __syncthreads();
     }
-    for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
-      double s;
-      if (n1 > 1) { s = 0; const double* x = srow2 + i; for (int t = 0; t < n1; ++t) s += __ldg(w1 + t) * x[t]; }
-      else s = srow2[i + hn1];
-      a.out1[base + i] = s;
-    }
+    conv_row(srow2, hn1, ws1, n1, nlon, [&](int i, double s) { a.out1[base + i] = s; });
     return;
   }
-  for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
-    if (a.out1) {
-      double s;
-      if (n1 > 1) { s = 0; const double* x = srow + (i + hn - hn1); for (int t = 0; t < n1; ++t) s += __ldg(w1 + t) * x[t]; }
-      else s = srow[i + hn];
-      a.out1[base + i] = s;
-    }
-    if (a.out2 || a.out_m) {
-      double s;
-      if (n2 > 1) { s = 0; const double* x = srow + (i + hn - hn2); for (int t = 0; t < n2; ++t) s += __ldg(w2 + t) * x[t]; }
-      else s = srow[i + hn];
+  if (a.out1) conv_row(srow, hn, ws1, n1, nlon, [&](int i, double s) { a.out1[base + i] = s; });
+  if (a.out2 || a.out_m)
+    conv_row(srow, hn, ws2, n2, nlon, [&](int i, double s) {
       if (a.post == POST_DIV_M) s = s / __ldg(a.mdiv + base + i);
       if (a.out2) a.out2[base + i] = s;
       if (a.post == POST_SWM_M) a.out_m[base + i] = (s - __ldg(a.gzs + gidx(g, i, j, 0))) / a.grav;
-    }
-  }
+    });
 }
 
 // ---- backward pass: PGF + du,dv + u,v update (gmcore_mod.F90:529-571,

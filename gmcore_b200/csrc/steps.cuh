@@ -11,7 +11,7 @@
 static inline dim3 grid3(const gmc_handle* h, int nk) {
   return dim3((h->g.nlon + 127) / 128, h->g.je - h->g.jb + 1, nk);
 }
-static inline size_t filt_smem(const gmc_handle* h) { return (size_t)(h->g.nlon + 2 * h->max_hn) * sizeof(double); }
+static inline size_t filt_smem(const gmc_handle* h) { return (size_t)(2 * (h->g.nlon + 2 * h->max_hn) + 2 * (2 * h->max_hn + 1)) * sizeof(double); }
 
 // operators_prepare(forward_pass) for the horizontal part: calc_mf, calc_ke, calc_div,
 // calc_pv, interp_pv (operators_mod.F90:117-122)
@@ -33,7 +33,7 @@ static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, 
   a.f1 = h->filt[f1 >= 0 ? f1 : 0]; a.out1 = out1; a.use_f1 = f1 >= 0;
   a.f2 = h->filt[f2 >= 0 ? f2 : 0]; a.out2 = out2; a.use_f2 = f2 >= 0;
   a.post = post; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = mdiv; a.out_m = out_m;
-  a.chain = 0; a.row2_off = 0; a.skip_a = a.skip_b = -1000;
+  a.chain = 0; a.row2_off = 0; a.skip_a = a.skip_b = -1000; a.mh = h->max_hn;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
   LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
 }
@@ -47,9 +47,9 @@ static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int 
   a.f1 = h->filt[f1]; a.out1 = out1; a.use_f1 = 1;
   a.f2 = h->filt[f2]; a.out2 = out2; a.use_f2 = 1;
   a.post = POST_NONE; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = nullptr; a.out_m = nullptr;
-  a.chain = 1; a.row2_off = g.nlon + 2 * h->max_hn; a.skip_a = skip_a; a.skip_b = skip_b;
+  a.chain = 1; a.row2_off = g.nlon + 2 * h->max_hn; a.skip_a = skip_a; a.skip_b = skip_b; a.mh = h->max_hn;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
-  LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, 2 * filt_smem(h), g, a);
+  LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
 }
 
 #include "hydro.cuh"
