@@ -192,15 +192,13 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   u.u_old = old_.u; u.v_old = old_.v; u.u_new = nw.u; u.v_new = nw.v; u.dt = dt; u.swm = 0; u.blend = 0;
   LAUNCH(h, k_uv_update_h, tile_grid(g, g.nlev), tile_block(), 0, g, h->M, u);
   // small_filter2 in place, then big_filter -> u_f / v_f from the same staged row.  The two pole-adjacent
-  // v rows are blended with their neighbours first (time_schemes_mod.F90:225-233) and big-filtered after.
+  // v rows are blended with their small-filtered neighbours in between (time_schemes_mod.F90:225-233), inside
+  // the same kernel; a pole-adjacent block re-reads its neighbour's RAW row, so v is filtered out of place
+  // (into the free dv work array) and the two pointers are swapped.
   run_filter_chain(h, nw.u, 0, g.nlev, GMC_SMALL_FILTER2, nw.u, GMC_BIG_FILTER, nw.u_f);
   const int sa = g.has_south ? 1 : -1000, sb = g.has_north ? g.nhalf : -1000;
-  run_filter_chain(h, nw.v, 1, g.nlev, GMC_SMALL_FILTER2, nw.v, GMC_BIG_FILTER, nw.v_f, sa, sb);
-  if (g.has_south || g.has_north) {
-    LAUNCH(h, k_v_pole_blend, dim3((g.nlon + 127) / 128, g.nlev, 2), 128, 0, g, nw.v);
-    if (g.has_south) { Geo gr = g; gr.hjb = gr.hje = 1; run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr, POST_NONE, nullptr, nullptr, &gr); }
-    if (g.has_north) { Geo gr = g; gr.hjb = gr.hje = g.nhalf; run_filter(h, nw.v, 1, g.nlev, GMC_BIG_FILTER, nw.v_f, -1, nullptr, POST_NONE, nullptr, nullptr, &gr); }
-  }
+  run_filter_chain(h, nw.v, 1, g.nlev, GMC_SMALL_FILTER2, h->dv, GMC_BIG_FILTER, nw.v_f, sa, sb);
+  { double* t = nw.v; nw.v = h->dv; h->dv = t; nw.names["v_lat"] = {nw.v, 1}; }
 }
 // arrays of a state that travel at the per-stage exchange point
 static HaloSet stage_halo_set(gmc_handle* b, int it) {

@@ -73,8 +73,27 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   const int base = gidx(g, 0, j, k);
   if (a.chain) {
     conv_row(srow, hn, ws2, n2, nlon, [&](int i, double s) { a.out2[base + i] = s; srow2[i + hn1] = s; });
-    if (j == a.skip_a || j == a.skip_b) return;     // block-uniform
     __syncthreads();
+    if (j == a.skip_a || j == a.skip_b) {     // block-uniform
+      // pole-adjacent v row: blend with the small-filtered neighbour row first (time_schemes_mod.F90:225-233:
+      // v(j) = 0.4 v(j) + 0.6 v(jn)); the neighbour's filtered row is recomputed here from its raw row.
+      const int jn = j == a.skip_a ? j + 1 : j - 1;
+      const int n2n = a.f2.ngrid_lat[jn + 1], hn2n = n2n > 1 ? (n2n - 1) / 2 : 0;
+      const double* __restrict__ rown = a.in + gidx(g, 0, jn, k);
+      const double* __restrict__ w2n = a.f2.wgt_lat + (size_t)(jn + 1) * a.f2.ld_lat;
+      for (int x = threadIdx.x; x < nlon + 2 * hn2n; x += blockDim.x) {
+        int i = x - hn2n; i = i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
+        srow[x] = rown[i];
+      }
+      for (int t = threadIdx.x; t < n2n; t += blockDim.x) ws2[t] = __ldg(w2n + t);
+      __syncthreads();
+      const double wgt = 0.6;
+      conv_row(srow, hn2n, ws2, n2n, nlon, [&](int i, double sn) {
+        const double v = (1 - wgt) * srow2[i + hn1] + wgt * sn;
+        a.out2[base + i] = v; srow2[i + hn1] = v;
+      });
+      __syncthreads();
+    }
     if (n1 > 1) {
       for (int x = threadIdx.x; x < hn1; x += blockDim.x) { srow2[x] = srow2[x + nlon]; srow2[hn1 + nlon + x] = srow2[hn1 + x]; }
       __syncthreads();
