@@ -63,60 +63,71 @@ struct CflArgs {
   double dt, radius; int* flags;
   int jx0, jx1, jy0, jy1;              // rows of the x part (cflx, divx, divy) / the y part (cfly); band mode
 };
-__global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
-  if (i >= g.nlon || j > g.je) return;
-  const int c = gidx(g, i, j, k), rb = c - i;
+// One memory phase in the common case: a departure point less than one cell away (|CFL| < 1, everywhere
+// except the polar rows in x) interpolates between the edge's own value and one of its two neighbours, so
+// the three-point windows u(i-1..i+1), v(j-1..j+1) and the edge coordinates are loaded up front and the three
+// RK4 stages are register arithmetic; a lane whose point leaves the window gathers as the reference does
+// (adv_batch_mod.F90:256-288,290-335).  x and y chains are interleaved; divides by dx, dy, area_cell are
+// multiplies by host-formed reciprocals.
+template <bool EDGE> __device__ __forceinline__ void cfl_body(const Geo& g, const DMesh& M, const CflArgs& a, int i, int j, int k) {
+  const int n = g.nlon, c = gidx(g, i, j, k), rb = c - i;
   const int i1 = i + 1;                       // Fortran index
   const double* __restrict__ hl = M.half_lon + (M.hx - 1);   // hl[l] = half_lon(l), l Fortran index
   const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;   // warp-uniform
   const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
   const double* __restrict__ ur = a.u + rb;
-  // The x and y RK4 chains are independent: their three dependent gathers are interleaved stage
-  // by stage so that both are in flight together.  Divides by the row constants dx, dy,
-  // area_cell are multiplies by host-formed reciprocals.
-  const double rdx = MJ(M.r_de_lon, j), cl = MJ(M.full_cos_lat, j), rcl = a.radius * cl;
-  const double rdy = doy ? MJ(M.r_de_lat, j) : 0.0;
-  const double u1 = dox ? __ldg(ur + i) : 0.0;
-  const double v1 = doy ? __ldg(a.v + c) : 0.0;
-  const double x0 = rcl * hl[i1], y0 = doy ? a.radius * MJ(M.half_lat, j) : 0.0;
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double rdx = R->r_de_lon, rcl = a.radius * R->full_cos_lat, rdy = R->r_de_lat;
+  double u_m = 0, u1 = 0, u_p = 0, v_s = 0, v1 = 0, v_n = 0;
+  if (dox) { u_m = __ldg(ur + wrapE<EDGE>(i - 1, n)); u1 = __ldg(ur + i); u_p = __ldg(ur + wrapE<EDGE>(i + 1, n)); }
+  if (doy || dox) { v_s = __ldg(a.v + c - n); v1 = __ldg(a.v + c); }
+  if (doy) v_n = __ldg(a.v + c + n);
+  const double xm = rcl * hl[i1 - 1], x0 = rcl * hl[i1], xp = rcl * hl[i1 + 1];
+  const double ym = a.radius * R[-1].half_lat, y0 = a.radius * R->half_lat, yp = a.radius * R[1].half_lat;
   double x = x0 + a.dt / 2 * u1, y = y0 + a.dt / 2 * v1;
   double us[3], vs[3];
 #pragma unroll
   for (int s = 0; s < 3; ++s) {
     const double h = s == 1 ? a.dt : a.dt / 2;
-    double ua = 0, ub = 0, va = 0, vb = 0;
-    int lx = 0, ly = 0; bool inr = false;
     if (dox) {
-      lx = __double2int_rd(i1 + (x - x0) * rdx);
-      ua = __ldg(ur + wrapi(lx - 1, g.nlon)); ub = __ldg(ur + wrapi(lx, g.nlon));
+      const int lx = __double2int_rd(i1 + (x - x0) * rdx), d = lx - i1;
+      double ua, ub, xl, xr;
+      if (d == 0) { ua = u1; ub = u_p; xl = x0; xr = xp; }
+      else if (d == -1) { ua = u_m; ub = u1; xl = xm; xr = x0; }
+      else { ua = __ldg(ur + wrapi(lx - 1, n)); ub = __ldg(ur + wrapi(lx, n)); xl = rcl * hl[lx]; xr = rcl * hl[lx + 1]; }
+      us[s] = ((xr - x) * ua + (x - xl) * ub) * rdx; x = x0 + h * us[s];
     }
     if (doy) {
-      ly = __double2int_rd(j + (y - y0) * rdy);
-      inr = !(ly < 1 || ly > g.nhalf - 1);
-      if (inr) { va = ldW(a.v, g, i, ly, k); vb = ldW(a.v, g, i, ly + 1, k); }
-    }
-    if (dox) { us[s] = ((rcl * hl[lx + 1] - x) * ua + (x - rcl * hl[lx]) * ub) * rdx; x = x0 + h * us[s]; }
-    if (doy) {
-      vs[s] = inr ? ((a.radius * MJ(M.half_lat, ly + 1) - y) * va + (y - a.radius * MJ(M.half_lat, ly)) * vb) * rdy : v1;
+      const int ly = __double2int_rd(j + (y - y0) * rdy), d = ly - j;
+      const bool inr = !(ly < 1 || ly > g.nhalf - 1);
+      double va, vb, yl, yr;
+      if (d == 0) { va = v1; vb = v_n; yl = y0; yr = yp; }
+      else if (d == -1) { va = v_s; vb = v1; yl = ym; yr = y0; }
+      else if (inr) { va = ldW(a.v, g, i, ly, k); vb = ldW(a.v, g, i, ly + 1, k); yl = a.radius * MJ(M.half_lat, ly); yr = a.radius * MJ(M.half_lat, ly + 1); }
+      else { va = vb = yl = yr = 0; }
+      vs[s] = inr ? ((yr - y) * va + (y - yl) * vb) * rdy : v1;
       y = y0 + h * vs[s];
     }
   }
   if (dox) {
-    const double rac = MJ(M.r_area_cell, j);
+    const double rac = R->r_area_cell;
     const double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) * (1.0 / 6.0) * a.dt * rdx;
     a.cflx[c] = cf;
     if (fabs(cf) > M.hx) atomicOr(a.flags, 1);
-    const double um = __ldg(ur + wrapi(i - 1, g.nlon));
-    a.divx[c] = (u1 - um) * MJ(M.le_lon, j) * rac;
-    a.divy[c] = (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1)) * rac;
+    a.divx[c] = (u1 - u_m) * R->le_lon * rac;
+    a.divy[c] = (v1 * R->le_lat - v_s * R[-1].le_lat) * rac;
   }
   if (doy) {
     const double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) * (1.0 / 6.0) * a.dt * rdy;
     a.cfly[c] = cf;
     if (fabs(cf) > 1) atomicOr(a.flags, 2);
   }
+}
+__global__ void __launch_bounds__(128) k_cfl(Geo g, DMesh M, CflArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j > g.je) return;
+  if (edge_block(g.nlon, 1)) cfl_body<true>(g, M, a, i, j, k); else cfl_body<false>(g, M, a, i, j, k);
 }
 
 // ---- zonal sums on the pole-adjacent half rows (zonal_sum, parallel_mod.F90:741-764) ---
