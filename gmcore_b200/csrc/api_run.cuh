@@ -29,7 +29,7 @@ static void diag_to_abi(const double* s, double* out) {
 // time_integrate (gmcore_mod.F90:577-591) for every band driven by this handle
 static int time_integrate_impl(gmc_handle* h, int old_, int nw, double dt, int time_step) {
   if (time_integrator(h, old_, nw, dt)) return 1;
-  if (!h->cfg.baroclinic) return 0;
+  if (!h->cfg.baroclinic) { if (h->cfg.use_smag_damp) run_smag_damp(h, h->st[nw], dt); return 0; }
   bool adv = false;
   for_bands(h, [&](gmc_handle* b) { adv = hydro_post_compute(b, nw, dt, time_step); });
   const bool hs = h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ;

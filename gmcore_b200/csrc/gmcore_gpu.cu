@@ -36,7 +36,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
   if (cfg->coriolis_scheme != 1) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d not built (only 1)", cfg->coriolis_scheme); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order != 2) { snprintf(g_create_err, sizeof(g_create_err), "div_damp_order=%d not built (only 2)", cfg->div_damp_order); delete h; return 3; }
-  if (cfg->use_smag_damp) { snprintf(g_create_err, sizeof(g_create_err), "use_smag_damp not built"); delete h; return 3; }
+  if (cfg->use_smag_damp && cfg->nranks > 1) { snprintf(g_create_err, sizeof(g_create_err), "use_smag_damp is built for a single band only (u_lon / v_lat halo rows are not exchanged)"); delete h; return 3; }
   if (cfg->nranks > 1 && !cfg->baroclinic) { snprintf(g_create_err, sizeof(g_create_err), "latitude bands (nranks>1) are built for the hydrostatic core only"); delete h; return 3; }
   if (cfg->nranks > 1 && cfg->lat_iend - cfg->lat_ibeg + 1 < 6) { snprintf(g_create_err, sizeof(g_create_err), "a latitude band needs at least 6 rows"); delete h; return 3; }
   if ((cfg->rank == 0) != (cfg->lat_ibeg == 1) || (cfg->rank == cfg->nranks - 1) != (cfg->lat_iend == cfg->nlat)) {
@@ -75,6 +75,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (!rc) rc = dev_alloc(h, &h->pole_work, (size_t)16 * g.nlev);
   if (!rc) rc = dev_alloc(h, &h->diag_partial, (size_t)7 * (g.je - g.jb + 1) * g.nlev);
   if (!rc) rc = dev_alloc(h, &h->diag_out, 8);
+  if (!rc && cfg->use_smag_damp) { rc = dev_alloc(h, &h->smag_t, n3); if (!rc) rc = dev_alloc(h, &h->smag_s, n3); if (!rc) rc = dev_alloc(h, &h->smag_du, n3); if (!rc) rc = dev_alloc(h, &h->smag_dv, n3); }
   if (!rc && baro) rc = hydro_alloc(h);
   if (!rc) rc = halo_alloc(h);
   h->stage_bytes = (size_t)(g.nlon + 2 * cfg->hx) * ((g.je - g.jb + 1) + 2 * cfg->hy) * (g.nlev + 4) * sizeof(double);

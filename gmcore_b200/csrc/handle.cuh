@@ -60,6 +60,7 @@ struct gmc_handle {
   double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
   double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)
   double *pole_work = 0;
+  double *smag_t = 0, *smag_s = 0, *smag_du = 0, *smag_dv = 0;   // smag_damp work arrays (use_smag_damp)
   // tracer batch
   double *q[2] = {0, 0}, *old_m = 0, *bu = 0, *bv = 0, *bmfx = 0, *bmfy = 0, *bwe = 0, *bm_lev = 0;
   double *bcflx = 0, *bcfly = 0, *bcflz = 0, *bdivx = 0, *bdivy = 0, *lon_damp_wgt = 0;

@@ -311,6 +311,15 @@ static HaloSet tracer_halo_set(gmc_handle* b, int which /*0: q_old, 1: q_new*/, 
   return s;
 }
 
+// smag_damp_run (damp_mod.F90:60-62) on state(new)%u_lon, v_lat
+static void run_smag_damp(gmc_handle* h, DState& S, double dt) {
+  const Geo& g = h->g;
+  SmagArgs a{S.u, S.v, h->smag_t, h->smag_s, h->smag_du, h->smag_dv, h->cfg.smag_damp_coef, dt};
+  LAUNCH(h, k_smag_strain, gridg(g, g.nlev), 128, 0, g, h->M, a);
+  LAUNCH(h, k_smag_tend, gridg(g, g.nlev), 128, 0, g, h->M, a);
+  LAUNCH(h, k_smag_apply, gridg(g, g.nlev), 128, 0, g, a, S.u, S.v);
+}
+
 // time_integrate after the time integrator (gmcore_mod.F90:586-590): forcing, damping, tracers
 static bool hydro_post_compute(gmc_handle* h, int nw, double dt, int time_step) {
   const Geo& g = h->g; DState& S = h->st[nw];
@@ -326,6 +335,7 @@ static bool hydro_post_compute(gmc_handle* h, int nw, double dt, int time_step) 
     DivDampArgs dd{S.div, h->c_lon, h->c_lat, S.u, S.v};
     LAUNCH(h, k_div_damp, gridg(g, g.nlev), 128, 0, g, h->M, dd);
   }
+  if (h->cfg.use_smag_damp) run_smag_damp(h, S, dt);
   return hydro_adv_run(h, nw, time_step);
 }
 

@@ -533,6 +533,60 @@ __global__ void __launch_bounds__(128) k_div_damp(Geo g, DMesh M, DivDampArgs a)
     a.v[c] = a.v[c] + __ldg(a.c_lat + (size_t)k * g.nhalf + (j - 1)) * (ldW(a.div, g, i, j + 1, k) - d0) / MJ(M.de_lat, j);
 }
 
+// ---- smag_damp_run (smag_damp_mod.F90:45-205): tension / shear strain -> eddy viscosity on the
+// edges -> Laplacian damping of u, v.  kmh_lon / kmh_lat are formed on the fly (never stored); the
+// tendencies are formed from the un-updated winds and applied by a second pass, as in the reference.
+struct SmagArgs { const double *u, *v; double *st, *ss, *du, *dv; double coef, dt; };
+__global__ void __launch_bounds__(128) k_smag_strain(Geo g, DMesh M, SmagArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const int c = gidx(g, i, j, k);
+  if (j > 1 && j < g.nlat)
+    a.st[c] = (__ldg(a.u + c) - ldW(a.u, g, i - 1, j, k)) / MJ(M.de_lon, j) -
+              (__ldg(a.v + c) * MJ(M.half_cos_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.half_cos_lat, j - 1)) / MJ(M.le_lon, j) / MJ(M.full_cos_lat, j);
+  if (j <= g.nhalf)
+    a.ss[c] = (ldW(a.v, g, i + 1, j, k) - __ldg(a.v + c)) / MJ(M.le_lat, j) +
+              (ldW(a.u, g, i, j + 1, k) * MJ(M.full_cos_lat, j + 1) - __ldg(a.u + c) * MJ(M.full_cos_lat, j)) / MJ(M.de_lat, j) / MJ(M.half_cos_lat, j);
+}
+__global__ void __launch_bounds__(128) k_smag_tend(Geo g, DMesh M, SmagArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const int c = gidx(g, i, j, k);
+  const double t0 = __ldg(a.st + c), s0 = j <= g.nhalf ? __ldg(a.ss + c) : 0.0;
+  if (j > 1 && j < g.nlat) {
+    const double de = MJ(M.de_lon, j), le = MJ(M.le_lon, j);
+    const double ls2 = a.coef / (1 / (de * de) + 1 / (le * le)) * 1.0;      // decay_from_top == 1 (:35-36)
+    const double tp = ldW(a.st, g, i + 1, j, k), sm = ldW(a.ss, g, i, j - 1, k);
+    const double kmh = ls2 * sqrt(0.5 * (t0 * t0 + tp * tp) + 0.5 * (s0 * s0 + sm * sm));
+    const double u0 = __ldg(a.u + c);
+    a.du[c] = kmh * ((ldW(a.u, g, i - 1, j, k) - 2 * u0 + ldW(a.u, g, i + 1, j, k)) / (de * de) +
+                     ((ldW(a.u, g, i, j + 1, k) - u0) / MJ(M.de_lat, j) * MJ(M.half_cos_lat, j) -
+                      (u0 - ldW(a.u, g, i, j - 1, k)) / MJ(M.de_lat, j - 1) * MJ(M.half_cos_lat, j - 1)) / le / MJ(M.full_cos_lat, j));
+  }
+  if (j <= g.nhalf) {
+    const double le = MJ(M.le_lat, j), de = MJ(M.de_lat, j);
+    const double ls2 = a.coef / (1 / (le * le) + 1 / (de * de)) * 1.0;
+    const double tn = ldW(a.st, g, i, j + 1, k), sw = ldW(a.ss, g, i - 1, j, k);
+    const double kmh = ls2 * sqrt(0.5 * (t0 * t0 + tn * tn) + 0.5 * (s0 * s0 + sw * sw));
+    const double v0 = __ldg(a.v + c);
+    double lap = (ldW(a.v, g, i - 1, j, k) - 2 * v0 + ldW(a.v, g, i + 1, j, k)) / (le * le);
+    if (!(j == 1 || j == g.nhalf))
+      lap = lap + ((ldW(a.v, g, i, j + 1, k) - v0) / MJ(M.le_lon, j + 1) * MJ(M.full_cos_lat, j + 1) -
+                   (v0 - ldW(a.v, g, i, j - 1, k)) / MJ(M.le_lon, j) * MJ(M.full_cos_lat, j)) / de / MJ(M.half_cos_lat, j);
+    a.dv[c] = kmh * lap;
+  }
+}
+__global__ void __launch_bounds__(128) k_smag_apply(Geo g, SmagArgs a, double* u, double* v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const int c = gidx(g, i, j, k);
+  if (j > 1 && j < g.nlat) u[c] = u[c] + a.dt * a.du[c];
+  if (j <= g.nhalf) v[c] = v[c] + a.dt * a.dv[c];
+}
+
 // ---- tracer batch (adv_batch_mod.F90:207-252,379-403; adv_mod.F90:152-312) -----------
 // wind / mass-flux accumulation: mode 0 copy, 1 add, 2 add and divide by nstep+1
 struct AccumArgs { double* dst[2]; const double* src[2]; int nlev_[2]; int mode, nstep; };

@@ -258,6 +258,54 @@ struct Model {
     fill_halo(mesh, u, true); fill_halo(mesh, v, false);
   }
 
+  // ---- smag_damp_mod.F90:45-205 (decay_from_top == 1, :35-36) ---------------------------------
+  void smag_damp_run(State& s, double dt) {
+    const Mesh& mesh = b.mesh;
+    const double coef = b.cfg.smag_damp_coef;
+    A3 &u = s.u_lon, &v = s.v_lat, &st = s.smag_t, &ss = s.smag_s, &klon = s.kmh_lon, &klat = s.kmh_lat;
+    const int nlon = mesh.nlon, nlat = mesh.nlat, nhalf = mesh.nhalf, nlev = mesh.nlev;
+    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+      st(i, j, k) = (u(i, j, k) - u(i - 1, j, k)) / mesh.de_lon(j) -
+                    (v(i, j, k) * mesh.half_cos_lat(j) - v(i, j - 1, k) * mesh.half_cos_lat(j - 1)) / mesh.le_lon(j) / mesh.full_cos_lat(j);
+    fill_halo(mesh, st, true, false, true, false, true);
+    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
+      ss(i, j, k) = (v(i + 1, j, k) - v(i, j, k)) / mesh.le_lat(j) +
+                    (u(i, j + 1, k) * mesh.full_cos_lat(j + 1) - u(i, j, k) * mesh.full_cos_lat(j)) / mesh.de_lat(j) / mesh.half_cos_lat(j);
+    fill_halo(mesh, ss, false, true, false, true, false);
+    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) {
+      const double ls2 = coef / (1 / (mesh.de_lon(j) * mesh.de_lon(j)) + 1 / (mesh.le_lon(j) * mesh.le_lon(j))) * 1.0;
+      for (int i = 1; i <= nlon; ++i)
+        klon(i, j, k) = ls2 * std::sqrt(0.5 * (st(i, j, k) * st(i, j, k) + st(i + 1, j, k) * st(i + 1, j, k)) +
+                                        0.5 * (ss(i, j, k) * ss(i, j, k) + ss(i, j - 1, k) * ss(i, j - 1, k)));
+    }
+    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) {
+      const double ls2 = coef / (1 / (mesh.le_lat(j) * mesh.le_lat(j)) + 1 / (mesh.de_lat(j) * mesh.de_lat(j))) * 1.0;
+      for (int i = 1; i <= nlon; ++i)
+        klat(i, j, k) = ls2 * std::sqrt(0.5 * (st(i, j, k) * st(i, j, k) + st(i, j + 1, k) * st(i, j + 1, k)) +
+                                        0.5 * (ss(i, j, k) * ss(i, j, k) + ss(i - 1, j, k) * ss(i - 1, j, k)));
+    }
+    // tendencies from the un-updated winds, then the updates (smag_damp_mod.F90:131-176)
+    std::vector<double> tu((size_t)nlon * nlat * nlev), tv((size_t)nlon * nlat * nlev);
+    auto T = [&](int i, int j, int k) { return ((size_t)(k - 1) * nlat + (j - 1)) * nlon + (i - 1); };
+    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+      tu[T(i, j, k)] = klon(i, j, k) * ((u(i - 1, j, k) - 2 * u(i, j, k) + u(i + 1, j, k)) / (mesh.de_lon(j) * mesh.de_lon(j)) +
+                        ((u(i, j + 1, k) - u(i, j, k)) / mesh.de_lat(j) * mesh.half_cos_lat(j) -
+                         (u(i, j, k) - u(i, j - 1, k)) / mesh.de_lat(j - 1) * mesh.half_cos_lat(j - 1)) / mesh.le_lon(j) / mesh.full_cos_lat(j));
+    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+      u(i, j, k) = u(i, j, k) + dt * tu[T(i, j, k)];
+    fill_halo(mesh, u, true);
+    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i) {
+      double lap = (v(i - 1, j, k) - 2 * v(i, j, k) + v(i + 1, j, k)) / (mesh.le_lat(j) * mesh.le_lat(j));
+      if (!(j == 1 || j == nhalf))
+        lap = lap + ((v(i, j + 1, k) - v(i, j, k)) / mesh.le_lon(j + 1) * mesh.full_cos_lat(j + 1) -
+                     (v(i, j, k) - v(i, j - 1, k)) / mesh.le_lon(j) * mesh.full_cos_lat(j)) / mesh.de_lat(j) / mesh.half_cos_lat(j);
+      tv[T(i, j, k)] = klat(i, j, k) * lap;
+    }
+    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
+      v(i, j, k) = v(i, j, k) + dt * tv[T(i, j, k)];
+    fill_halo(mesh, v, false);
+  }
+
   // ---- lon_damp_mod.F90:43-68 -----------------------------------------------------
   void lon_damp_init(const double* full_lat_deg /* 1-hy : nlat+hy */) {
     const Mesh& mesh = b.mesh;
@@ -461,6 +509,7 @@ struct Model {
     time_integrator(old, nw, dt);
     if (b.cfg.test_forcing == GMC_FORCING_HELD_SUAREZ) held_suarez_forcing(b.state[nw], dt);
     if (b.cfg.use_div_damp) div_damp_run(b.state[nw]);
+    if (b.cfg.use_smag_damp) smag_damp_run(b.state[nw], dt);      // damp_run, damp_mod.F90:49-63
     adv_run(nw);
   }
   // time_advance (time_mod.F90:128-159)
