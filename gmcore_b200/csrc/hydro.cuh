@@ -332,7 +332,14 @@ static bool hydro_post_compute(gmc_handle* h, int nw, double dt, int time_step) 
     DivArgs d{S.u_f, S.v_f, S.div};
     LAUNCH(h, k_div, gridg(g01, g.nlev), 128, 0, g01, h->M, d);
     run_pole_sum(h, S.v_f, nullptr, S.div, 1);
-    DivDampArgs dd{S.div, h->c_lon, h->c_lat, S.u, S.v};
+    const double* dsrc = S.div; double sgn = 1.0;
+    if (h->cfg.div_damp_order == 4) {     // u -= c d(div2)/dx with div2 = lap(div) (div_damp_mod.F90:120-134)
+      Div2Args d2{S.div, h->qx};          // qx is free here; its pole rows hold FFSL data, so clear them first
+      cudaMemsetAsync(h->qx, 0, (size_t)g.plane * g.nlev * sizeof(double), h->stream);
+      LAUNCH(h, k_div2, gridg(g, g.nlev), 128, 0, g, h->M, d2);
+      dsrc = h->qx; sgn = -1.0;
+    }
+    DivDampArgs dd{dsrc, h->c_lon, h->c_lat, S.u, S.v, sgn};
     LAUNCH(h, k_div_damp, gridg(g, g.nlev), 128, 0, g, h->M, dd);
   }
   if (h->cfg.use_smag_damp) run_smag_damp(h, S, dt);

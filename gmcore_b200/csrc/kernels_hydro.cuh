@@ -520,7 +520,19 @@ __global__ void __launch_bounds__(128) k_div(Geo g, DMesh M, DivArgs a) {
   a.div[c] = ((__ldg(a.u + c) * MJ(M.le_lon, j) - ldW(a.u, g, i - 1, j, k) * MJ(M.le_lon, j)) +
               (__ldg(a.v + c) * MJ(M.le_lat, j) - ldW(a.v, g, i, j - 1, k) * MJ(M.le_lat, j - 1))) / MJ(M.area_cell, j);
 }
-struct DivDampArgs { const double *div, *c_lon, *c_lat; double *u, *v; };
+// div2 = Laplacian of div for 4th-order damping (calc_div, operators_mod.F90:414-428); pole rows stay 0
+struct Div2Args { const double* div; double* div2; };
+__global__ void __launch_bounds__(128) k_div2(Geo g, DMesh M, Div2Args a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon || j == 1 || j == g.nlat) return;
+  const int c = gidx(g, i, j, k);
+  const double d0 = __ldg(a.div + c), de = MJ(M.de_lon, j);
+  a.div2[c] = (ldW(a.div, g, i + 1, j, k) - 2 * d0 + ldW(a.div, g, i - 1, j, k)) / (de * de) +
+              ((ldW(a.div, g, i, j + 1, k) - d0) * MJ(M.half_cos_lat, j) / MJ(M.de_lat, j) -
+               (d0 - ldW(a.div, g, i, j - 1, k)) * MJ(M.half_cos_lat, j - 1) / MJ(M.de_lat, j - 1)) / MJ(M.le_lon, j) / MJ(M.full_cos_lat, j);
+}
+struct DivDampArgs { const double *div, *c_lon, *c_lat; double *u, *v; double sgn; };
 __global__ void __launch_bounds__(128) k_div_damp(Geo g, DMesh M, DivDampArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
@@ -528,9 +540,9 @@ __global__ void __launch_bounds__(128) k_div_damp(Geo g, DMesh M, DivDampArgs a)
   const long long c = gidx(g, i, j, k);
   const double d0 = __ldg(a.div + c);
   if (j > 1 && j < g.nlat)
-    a.u[c] = a.u[c] + __ldg(a.c_lon + (size_t)k * g.nlat + (j - 1)) * (ldW(a.div, g, i + 1, j, k) - d0) / MJ(M.de_lon, j);
+    a.u[c] = a.u[c] + a.sgn * (__ldg(a.c_lon + (size_t)k * g.nlat + (j - 1)) * (ldW(a.div, g, i + 1, j, k) - d0) / MJ(M.de_lon, j));
   if (j <= g.nhalf)
-    a.v[c] = a.v[c] + __ldg(a.c_lat + (size_t)k * g.nhalf + (j - 1)) * (ldW(a.div, g, i, j + 1, k) - d0) / MJ(M.de_lat, j);
+    a.v[c] = a.v[c] + a.sgn * (__ldg(a.c_lat + (size_t)k * g.nhalf + (j - 1)) * (ldW(a.div, g, i, j + 1, k) - d0) / MJ(M.de_lat, j));
 }
 
 // ---- smag_damp_run (smag_damp_mod.F90:45-205): tension / shear strain -> eddy viscosity on the
