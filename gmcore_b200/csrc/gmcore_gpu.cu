@@ -34,7 +34,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   h->cfg = *cfg;
   if (cudaSetDevice(cfg->device) != cudaSuccess) { snprintf(g_create_err, sizeof(g_create_err), "cudaSetDevice(%d) failed", cfg->device); delete h; return 2; }
   if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
-  if (cfg->coriolis_scheme != 1) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d not built (only 1)", cfg->coriolis_scheme); delete h; return 3; }
+  if (cfg->coriolis_scheme != 1 && cfg->coriolis_scheme != 2) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d is not a GMCORE scheme (1 or 2)", cfg->coriolis_scheme); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order != 2 && cfg->div_damp_order != 4) { snprintf(g_create_err, sizeof(g_create_err), "Unsupported div_damp_order %d!", cfg->div_damp_order); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order == 4 && cfg->nranks > 1) { snprintf(g_create_err, sizeof(g_create_err), "div_damp_order=4 is built for a single band only"); delete h; return 3; }
   if (cfg->use_div_damp && !cfg->baroclinic) { snprintf(g_create_err, sizeof(g_create_err), "use_div_damp is not built for the shallow-water core"); delete h; return 3; }

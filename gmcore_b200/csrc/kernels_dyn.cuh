@@ -323,8 +323,10 @@ template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, cons
     }
     // ---- du (lon edges of full-lat rows) -------------------------------------------------------
     if (full) {
-      const double qhv = (ftw1 * (fy_0s * (plo_0 + pla_0s) + fy_ps * (plo_0 + pla_ps)) +
-                          ftw2 * (fy_0 * (plo_0 + pla_0) + fy_p * (plo_0 + pla_p))) * 0.5;
+      // coriolis_scheme 1: energy-conserving 4-point form; 2: tangential mass flux (calc_mf :597-604) x edge pv
+      const double qhv = a.coriolis_scheme == 1
+          ? (ftw1 * (fy_0s * (plo_0 + pla_0s) + fy_ps * (plo_0 + pla_ps)) + ftw2 * (fy_0 * (plo_0 + pla_0) + fy_p * (plo_0 + pla_p))) * 0.5
+          : (ftw1 * (fy_0s + fy_ps) + ftw2 * (fy_0 + fy_p)) * plo_0;
       const double dkedlon = (ke_p - ke0) * rdl;
       double du = qhv - dkedlon;
       if (hyd) {
@@ -353,8 +355,9 @@ template <bool EDGE> __device__ __forceinline__ void tend_col(const Geo& g, cons
     if (half) {
       // mfx_lon / pv_lon terms on pole rows are 0 (never computed by the reference)
       const double pl_b = s0 ? plo_0 : 0.0;
-      const double qhu = (htw1 * (fx_m * (pla_0 + plo_m) + fx_0 * (pla_0 + pl_b)) +
-                          htw2 * (fx_mn * (pla_0 + plo_mn) + fx_0n * (pla_0 + plo_0n))) * 0.5;
+      const double qhu = a.coriolis_scheme == 1
+          ? (htw1 * (fx_m * (pla_0 + plo_m) + fx_0 * (pla_0 + pl_b)) + htw2 * (fx_mn * (pla_0 + plo_mn) + fx_0n * (pla_0 + plo_0n))) * 0.5
+          : (htw1 * (fx_m + fx_0) + htw2 * (fx_mn + fx_0n)) * pla_0;
       const double dkedlat = (ke_n - ke0) * rda;
       double dv = -qhu - dkedlat;
       if (hyd) {
