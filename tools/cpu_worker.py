@@ -11,7 +11,7 @@ from oracle.orc import Oracle
 name, budget = sys.argv[1], float(sys.argv[2])
 wl = WORKLOADS[name]
 host = Host(wl["nlon"], wl["nlat"], wl["nlev"], wl["dt"], wl["case"])
-orc = Oracle(host, fast=True)
+orc = Oracle(host, fast=os.environ.get("ORC_FAST", "1") == "1")   # ORC_FAST=0: the portable -O2 build
 orc.set_state(host.initial_condition())
 if host.cfg.ntracers:
     orc.set_tracers(np.zeros((host.cfg.ntracers,) + host.shape("cell")))
