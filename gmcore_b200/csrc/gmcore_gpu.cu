@@ -102,6 +102,7 @@ void gmc_destroy(gmc_handle* h) {
     bool any = false; for (auto m : *grp) any = any || m;
     if (!any) delete grp;
   }
+  if (h->comm_stream) { cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_edge); cudaEventDestroy(h->ev_xdone); }
   if (h->stream && h->owns_stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -304,6 +305,10 @@ int gmc_nccl_init(gmc_handle* h, const char id[128]) {
   gmc_ncclUniqueId u; memcpy(u.internal, id, 128);
   CUDA_CHECK(cudaSetDevice(h->cfg.device));
   int rc = n.CommInitRank(&h->nccl_comm, h->cfg.nranks, u, h->cfg.rank);
+  { const char* e = getenv("GMCORE_NO_OVERLAP"); if (!rc && !(e && e[0] == '1')) {
+    cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&h->ev_edge, cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_xdone, cudaEventDisableTiming);
+  } }
   if (rc) { snprintf(h->err, sizeof(h->err), "ncclCommInitRank: %s", n.GetErrorString ? n.GetErrorString(rc) : "error"); h->nccl_comm = nullptr; return 1; }
   return 0;
 }

@@ -72,6 +72,9 @@ struct gmc_handle {
   std::vector<gmc_handle*>* group = nullptr;   // single-process band group (all bands on this device/stream)
   bool owns_stream = true;
   void* nccl_comm = nullptr;          // one-process-per-GPU mode
+  // overlap of the per-stage exchange with interior work (one-process-per-GPU mode): edge rows are finished
+  // first, ev_edge releases pack + ncclSend/Recv + unpack on comm_stream while the interior rows are filtered
+  cudaStream_t comm_stream = 0; cudaEvent_t ev_edge = 0, ev_xdone = 0;
   bool mesh_set = false, filters_set[3] = {false, false, false};
   int max_hn = 0;
   bool keep_dpt = false;              // GMCORE_DEBUG_FIELDS=1: also store the dpt tendency (parity tests read it back)

@@ -195,9 +195,23 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   // v rows are blended with their small-filtered neighbours in between (time_schemes_mod.F90:225-233), inside
   // the same kernel; a pole-adjacent block re-reads its neighbour's RAW row, so v is filtered out of place
   // (into the free dv work array) and the two pointers are swapped.
-  run_filter_chain(h, nw.u, 0, g.nlev, GMC_SMALL_FILTER2, nw.u, GMC_BIG_FILTER, nw.u_f);
   const int sa = g.has_south ? 1 : -1000, sb = g.has_north ? g.nhalf : -1000;
-  run_filter_chain(h, nw.v, 1, g.nlev, GMC_SMALL_FILTER2, h->dv, GMC_BIG_FILTER, nw.v_f, sa, sb);
+  auto chain_rows = [&](int j0, int j1) {       // full rows j0..j1 of u, half rows j0..min(j1, hje) of v
+    if (j1 < j0) return;
+    Geo gr = g; gr.jb = j0; gr.je = j1; gr.hjb = j0; gr.hje = j1 < g.hje ? j1 : g.hje;
+    run_filter_chain(h, nw.u, 0, g.nlev, GMC_SMALL_FILTER2, nw.u, GMC_BIG_FILTER, nw.u_f, -1000, -1000, &gr);
+    run_filter_chain(h, nw.v, 1, g.nlev, GMC_SMALL_FILTER2, h->dv, GMC_BIG_FILTER, nw.v_f, sa, sb, &gr);
+  };
+  if (h->comm_stream && g.je - g.jb + 1 > 2 * h->H) {
+    // rows that travel in the stage exchange first, then the interior (overlapped with the exchange, do_step)
+    const int s1 = g.has_south ? g.jb - 1 : g.jb + h->H - 1, n0 = g.has_north ? g.je + 1 : g.je - h->H + 1;
+    chain_rows(g.jb, s1); chain_rows(n0, g.je);
+    cudaEventRecord(h->ev_edge, h->stream);
+    chain_rows(s1 + 1, n0 - 1);
+  } else {
+    chain_rows(g.jb, g.je);
+    if (h->comm_stream) cudaEventRecord(h->ev_edge, h->stream);
+  }
   { double* t = nw.v; nw.v = h->dv; h->dv = t; nw.names["v_lat"] = {nw.v, 1}; }
 }
 // arrays of a state that travel at the per-stage exchange point

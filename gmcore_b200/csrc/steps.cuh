@@ -40,8 +40,8 @@ static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, 
 
 // out2 = f2(in), out1 = f1(out2) in one launch (one read of the raw row instead of two passes)
 static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int nlev, int f2, double* out2, int f1, double* out1,
-                             int skip_a = -1000, int skip_b = -1000) {
-  const Geo& g = h->g;
+                             int skip_a = -1000, int skip_b = -1000, const Geo* gp = nullptr) {
+  const Geo& g = gp ? *gp : h->g;
   FilterArgs a;
   a.in = in; a.half_lat = half_lat; a.nlev = nlev;
   a.f1 = h->filt[f1]; a.out1 = out1; a.use_f1 = 1;
@@ -49,6 +49,7 @@ static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int 
   a.post = POST_NONE; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = nullptr; a.out_m = nullptr;
   a.chain = 1; a.row2_off = g.nlon + 2 * h->max_hn; a.skip_a = skip_a; a.skip_b = skip_b; a.mh = h->max_hn;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
+  if (nrows <= 0) return;
   LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
 }
 
@@ -79,7 +80,18 @@ static void swm_step(gmc_handle* h, DState& old_, DState& star, DState& nw, doub
 static int do_step(gmc_handle* h, int old_, int star, int nw, double dt) {
   if (!h->cfg.baroclinic) { swm_step(h, h->st[old_], h->st[star], h->st[nw], dt); return 0; }
   for_bands(h, [&](gmc_handle* b) { hydro_stage(b, b->st[old_], b->st[star], b->st[nw], dt); });
-  if (halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); })) return 1;
+  if (h->comm_stream) {
+    // the edge rows of new%{u_f, v_f, pt, phs_f} are final at ev_edge: the exchange runs on comm_stream next to
+    // the interior rows of the last filter launches; the compute stream rejoins before it touches halo rows
+    cudaStream_t s0 = h->stream;
+    cudaStreamWaitEvent(h->comm_stream, h->ev_edge, 0);
+    h->stream = h->comm_stream;
+    const int rc = halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); });
+    cudaEventRecord(h->ev_xdone, h->comm_stream);
+    h->stream = s0;
+    cudaStreamWaitEvent(s0, h->ev_xdone, 0);
+    if (rc) return 1;
+  } else if (halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); })) return 1;
   for_bands(h, [&](gmc_handle* b) { hydro_after_exchange(b, b->st[nw]); });
   return 0;
 }
