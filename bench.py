@@ -97,6 +97,15 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def mark(self):
+        """Samples before this point (warm-up, idle waiting) are dropped if later ones exist."""
+        self.n0 = len(self.rows)
+
+    def wait_first(self, timeout=5.0):
+        t0 = time.time()
+        while self.proc and not self.rows and time.time() - t0 < timeout:
+            time.sleep(0.02)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -105,6 +114,8 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
+        rows = self.rows[getattr(self, 'n0', 0):] or self.rows
+        self.rows = rows
         sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         reasons = set()
@@ -265,8 +276,12 @@ def _main(out):
         q0 = np.zeros((host.cfg.ntracers,) + host.shape("cell"))
         gpu.set_tracers(q0)
     gpu.prepare_run()
+    # nvidia-smi takes a while to deliver its first sample (longer with 8 ranks starting one each): start it before
+    # the warm-up steps (same load) and make sure it is delivering before the timed region begins
+    clocks = ClockSampler(local); clocks.start()
     gpu.run_steps(W, diag=True)
     gpu.synchronize()
+    clocks.wait_first()
 
     n3 = wl["nlon"] * wl["nlat"] * wl["nlev"]
     n3_k = n3 // world if banded else n3          # cells one GPU's kernels process
@@ -275,8 +290,8 @@ def _main(out):
     flush_buf = torch.empty(int(2 * L2_BYTES) // 8, dtype=torch.float64, device=f"cuda:{local}") if flush else None
 
     # ---- device-resident timed region: exactly K steps --------------------------------
-    clocks = ClockSampler(local); clocks.start()
     barrier(world); torch.cuda.synchronize()
+    clocks.mark()
     l0 = gpu.launches
     if flush:
         ms = 0.0
