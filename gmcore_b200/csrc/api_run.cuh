@@ -140,6 +140,36 @@ int gmc_reset_clock(gmc_handle* h) {
   });
   return 0;
 }
+// ---- advection-only driver (gmcore_adv_driver.F90:84-88) -------------------------------------------------
+// gmc_adv_prescribe = set_uv of src/tests/adv/*_test_mod.F90: state(itime)%m = 1, u_f / v_f given, mfx_lon = u_f,
+// mfy_lat = v_f (no vertical motion).  gmc_adv_step = adv_run(itime) for the tracer batch.
+__global__ void k_fill(double* p, size_t n, double v) {
+  for (size_t x = blockIdx.x * (size_t)blockDim.x + threadIdx.x; x < n; x += (size_t)gridDim.x * blockDim.x) p[x] = v;
+}
+int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double* v_f) {
+  if (!h->cfg.baroclinic || h->cfg.ntracers <= 0 || h->cfg.nranks > 1) {
+    snprintf(h->err, sizeof(h->err), "the advection-only driver needs the hydrostatic core with a tracer batch on one band"); return 1; }
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  const Geo& g = h->g; DState& S = h->st[itime];
+  const size_t n3 = (size_t)g.plane * g.nlev, n3h = (size_t)g.plane * (g.nlev + 1);
+  if (xfer(h, S.u_f, const_cast<double*>(u_f), 0, 0) || xfer(h, S.v_f, const_cast<double*>(v_f), 1, 0)) return 1;
+  LAUNCH(h, k_fill, 1184, 256, 0, S.m, n3, 1.0);
+  LAUNCH(h, k_fill, 1184, 256, 0, S.m_lev, n3h, 1.0);
+  CUDA_CHECK(cudaMemsetAsync(S.we_lev, 0, n3h * sizeof(double), h->stream));
+  CUDA_CHECK(cudaMemcpyAsync(S.mfx_lon, S.u_f, n3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  CUDA_CHECK(cudaMemcpyAsync(S.mfy_lat, S.v_f, n3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  return 0;
+}
+int gmc_adv_step(gmc_handle* h, int itime, int time_step) {
+  if (check_ready(h)) return 1;
+  if (!h->cfg.baroclinic || h->cfg.ntracers <= 0 || h->cfg.nranks > 1) {
+    snprintf(h->err, sizeof(h->err), "the advection-only driver needs the hydrostatic core with a tracer batch on one band"); return 1; }
+  alert_advance(h, time_step - 1);
+  const bool adv = hydro_adv_run(h, itime, time_step);
+  hydro_adv_finish(h, itime, adv);
+  CUDA_CHECK(cudaGetLastError());
+  return hydro_check_flags(h);
+}
 int gmc_set_tracers(gmc_handle* h, const double* q) { return hydro_set_tracers(h, q); }
 int gmc_get_tracers(gmc_handle* h, double* q) { return hydro_get_tracers(h, q); }
 

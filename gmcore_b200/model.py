@@ -18,7 +18,7 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock",
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_step",
                "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init"]
 
 
@@ -60,6 +60,8 @@ def load_library():
     lib.gmc_profile.argtypes = [V, C.c_int]
     lib.gmc_profile_report.argtypes = [V, C.c_char_p, C.c_int]
     lib.gmc_reset_clock.argtypes = [V]
+    lib.gmc_adv_prescribe.argtypes = [V, C.c_int, P, P]
+    lib.gmc_adv_step.argtypes = [V, C.c_int, C.c_int]
     lib.gmc_stream.restype = C.c_void_p
     lib.gmc_stream.argtypes = [V]
     _LIB = lib
@@ -111,6 +113,15 @@ class GmcoreGPU:
         q = np.zeros((self.host.cfg.ntracers,) + self.host.shape("cell"))
         self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
         return q
+
+    # advection-only driver (gmcore_adv_driver.F90:84-88): set_uv(new) -> adv_run(new) -> time_advance
+    def adv_prescribe(self, u_f, v_f, itime=None):
+        self._chk(self.lib.gmc_adv_prescribe(self.h, self.new.value if itime is None else itime, abi.dptr(u_f), abi.dptr(v_f)))
+
+    def adv_step(self):
+        self._chk(self.lib.gmc_adv_step(self.h, self.new.value, self.time_step.value))
+        self.old.value, self.new.value = self.new.value, self.old.value
+        self.time_step.value += 1
 
     def reset_clock(self):
         """time_init: step counter 0, old/new = 1/2, tracer-batch sample counters cleared (before a fresh upload)."""

@@ -134,6 +134,12 @@ int gmc_group_link(gmc_handle** hs, int n);
 int gmc_nccl_unique_id(char id[128]);
 int gmc_nccl_init(gmc_handle* h, const char id[128]);
 
+/* Advection-only driver (drivers/gmcore_adv_driver.F90:84-88): gmc_adv_prescribe is the set_uv of
+ * tests/adv/*_test_mod.F90 (state(itime)%m = 1, u_f / v_f given, mfx_lon = u_f, mfy_lat = v_f); gmc_adv_step is
+ * adv_run(itime) (adv_mod.F90:152-312).  time_step as in gmc_time_integrate. */
+int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double* v_f);
+int gmc_adv_step(gmc_handle* h, int itime, int time_step);
+
 /* time_init (time_mod.F90:61-98): clear the step / tracer-batch sample counters before a fresh upload. */
 int gmc_reset_clock(gmc_handle* h);
 

@@ -32,6 +32,8 @@ def _load(fast):
     lib.orc_upload_state.argtypes = [C.c_void_p, C.c_int, P, P, P, P]
     lib.orc_set_tracers.argtypes = [C.c_void_p, P]
     lib.orc_get_tracers.argtypes = [C.c_void_p, P]
+    lib.orc_adv_prescribe.argtypes = [C.c_void_p, C.c_int, P, P]
+    lib.orc_adv_step.argtypes = [C.c_void_p]
     lib.orc_prepare_run.argtypes = [C.c_void_p]
     lib.orc_run_steps.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_diagnose.argtypes = [C.c_void_p, C.c_int, P]
@@ -78,6 +80,13 @@ class Oracle:
         q = np.zeros((n,) + self.host.shape("cell"))
         self.lib.orc_get_tracers(self.h, _dp(q))
         return q
+
+    # advection-only driver (gmcore_adv_driver.F90:84-88)
+    def adv_prescribe(self, u_f, v_f, itime=None):
+        self.lib.orc_adv_prescribe(self.h, self.new_index if itime is None else itime, _dp(u_f), _dp(v_f))
+
+    def adv_step(self):
+        self._check(self.lib.orc_adv_step(self.h))
 
     def prepare_run(self):
         self._check(self.lib.orc_prepare_run(self.h))

@@ -96,6 +96,24 @@ int orc_set_tracers(void* h, const double* q) {
   }
   return 0;
 }
+// Advection-only driver (gmcore_adv_driver.F90:84-88): set_uv(state(new)) then adv_run(new), time_advance.
+// orc_adv_prescribe = the set_uv of tests/adv/*_test_mod.F90: m = 1, u_f/v_f given, mfx = u, mfy = v.
+int orc_adv_prescribe(void* h, int itime, const double* u_f, const double* v_f) {
+  Model* m = (Model*)h; State& s = m->b.state[itime]; const Mesh& mesh = m->b.mesh;
+  std::fill(s.m.d.begin(), s.m.d.end(), 1.0);
+  std::memcpy(s.u_f.d.data(), u_f, s.u_f.d.size() * sizeof(double)); fill_halo(mesh, s.u_f, true);
+  s.mfx_lon.d = s.u_f.d;
+  std::memcpy(s.v_f.d.data(), v_f, s.v_f.d.size() * sizeof(double)); fill_halo(mesh, s.v_f, false);
+  s.mfy_lat.d = s.v_f.d;
+  if (m->b.cfg.baroclinic) { std::fill(s.we_lev.d.begin(), s.we_lev.d.end(), 0.0); std::fill(s.m_lev.d.begin(), s.m_lev.d.end(), 1.0); }
+  return 0;
+}
+int orc_adv_step(void* h) {
+  Model* m = (Model*)h;
+  m->adv_run(m->new_idx);
+  m->time_advance();
+  return m->b.error.empty() ? 0 : 1;
+}
 int orc_get_tracers(void* h, double* q) {
   Model* m = (Model*)h; AdvBatch& B = m->b.adv_batch;
   for (int l = 0; l < B.ntracers; ++l) {
