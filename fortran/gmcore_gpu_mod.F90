@@ -51,6 +51,7 @@ module gmcore_gpu_mod
     integer(c_int) use_smag_damp
     integer(c_int) test_forcing
     integer(c_int) ntracers
+    integer(c_int) limiter_type
     real(c_double) ke_cell_wgt, upwind_wgt_pv
     real(c_double) div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0
     real(c_double) smag_damp_coef
@@ -187,6 +188,11 @@ contains
     cfg%use_smag_damp = merge(1, 0, use_smag_damp)
     cfg%test_forcing = merge(1, 0, test_case == 'held_suarez')
     cfg%ntracers = ntracers
+    select case (limiter_type)
+    case ('none'); cfg%limiter_type = 0
+    case ('mono'); cfg%limiter_type = 1
+    case ('pd');   cfg%limiter_type = 2
+    end select
     cfg%ke_cell_wgt = ke_cell_wgt; cfg%upwind_wgt_pv = upwind_wgt_pv
     cfg%div_damp_coef2 = div_damp_coef2; cfg%div_damp_coef4 = div_damp_coef4
     cfg%div_damp_top = div_damp_top; cfg%div_damp_pole = div_damp_pole; cfg%div_damp_lat0 = div_damp_lat0

@@ -33,6 +33,7 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   gmc_handle* h = new gmc_handle();
   h->cfg = *cfg;
   if (cudaSetDevice(cfg->device) != cudaSuccess) { snprintf(g_create_err, sizeof(g_create_err), "cudaSetDevice(%d) failed", cfg->device); delete h; return 2; }
+  if (cfg->limiter_type < 0 || cfg->limiter_type > 2) { snprintf(g_create_err, sizeof(g_create_err), "Invalid limiter_type %d!", cfg->limiter_type); delete h; return 3; }
   if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
   if (cfg->coriolis_scheme != 1 && cfg->coriolis_scheme != 2) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d is not a GMCORE scheme (1 or 2)", cfg->coriolis_scheme); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order != 2 && cfg->div_damp_order != 4) { snprintf(g_create_err, sizeof(g_create_err), "Unsupported div_damp_order %d!", cfg->div_damp_order); delete h; return 3; }
@@ -342,7 +343,8 @@ int gmc_profile_report(gmc_handle* h, char* buf, int len) {
   std::map<std::string, std::pair<long long, double>> agg;
   for (auto& e : h->prof.entries) {
     float ms = 0; cudaEventElapsedTime(&ms, e.e0, e.e1);
-    auto& a = agg[e.name]; a.first++; a.second += ms;
+    std::string nm(e.name); nm = nm.substr(0, nm.find('<'));     // k_hflx<1> -> k_hflx
+    auto& a = agg[nm]; a.first++; a.second += ms;
   }
   std::vector<std::pair<double, std::string>> order;
   for (auto& kv : agg) order.push_back({-kv.second.second, kv.first});

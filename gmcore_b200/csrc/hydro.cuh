@@ -129,12 +129,12 @@ struct BatchRef { const double *u, *v, *mfx, *mfy, *cflx, *cfly, *divx, *divy; }
 static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double* flx, double* fly, double dt) {
   const Geo gw = xg(h, 3, 4), gn = xg(h, 1, 1), g0 = h->g;
   HflxArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qmfx, h->qmfy, gw.jb, gw.je, gn.jb, gn.je};
-  LAUNCH(h, k_hflx, tile_grid(gw, gw.nlev), tile_block(), 0, gw, in);
+  LAUNCH_LIM(h, k_hflx, tile_grid(gw, gw.nlev), tile_block(), 0, gw, in);
   run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);
   FfslQArgs qa{q, h->qmfx, h->qmfy, B.divx, B.divy, h->pole_work, h->qx, h->qy, dt, xg(h, 0, 1).jb, xg(h, 0, 1).je};
   LAUNCH(h, k_ffsl_q, tile_grid(gw, gw.nlev), tile_block(), 0, gw, h->M, qa);
   HflxArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, g0.jb, xg(h, 0, 1).je, gn.jb, gn.je};
-  LAUNCH(h, k_hflx, tile_grid(gn, gn.nlev), tile_block(), 0, gn, out);
+  LAUNCH_LIM(h, k_hflx, tile_grid(gn, gn.nlev), tile_block(), 0, gn, out);
 }
 
 // RK4 CFL numbers + divx/divy of a batch: x part on rows jb-3..je+4, y part on half rows jb-1..je+1
@@ -179,7 +179,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   run_ffsl_h(h, B, star.pt, h->ptf_lon, h->ptf_lat, dt);
   run_pole_sum(h, h->ptf_lat, h->pole_work + 2 * g.nlev, nullptr, 1);
   PtColArgs pc{star.pt, h->ptf_lon, h->ptf_lat, h->pole_work + 2 * g.nlev, star.we_lev, h->cflz, old_.pt, old_.m, nw.pt, h->keep_dpt ? h->dpt : nullptr, dt};
-  LAUNCH(h, k_pt_col, gridg(g01, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g01, h->M, pc);
+  LAUNCH_LIM(h, k_pt_col, gridg(g01, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g01, h->M, pc);
   // ---- update_state(tend1): rows jb..je+1 (the Lin97 PGF of half row je reads row je+1) ----
   LAUNCH(h, k_axpy2d, gridg(g01, 1), 128, 0, g01, old_.phs, h->dphs, nw.phs, dt);
   run_filter(h, nw.phs, 0, 1, GMC_BIG_FILTER, nw.phs_f, -1, nullptr, POST_NONE, nullptr, nullptr, &g01);
@@ -303,7 +303,7 @@ static bool hydro_adv_run(gmc_handle* h, int itime, int time_step) {
       NegXArgs nx{qn, S.m, h->dflags};
       LAUNCH(h, k_negfill_x, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, nx);
       TrVArgs tv{qn, S.m, h->bwe, h->bcflz, dt_adv, h->dflags};
-      LAUNCH(h, k_tracer_v, gridg(g, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g, tv);
+      LAUNCH_LIM(h, k_tracer_v, gridg(g, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g, tv);
       LonDampArgs ld{qn, h->lon_damp_wgt, 3};
       LAUNCH(h, k_lon_damp, dim3(g.je - g.jb + 1, g.nlev), 256, (size_t)2 * g.nlon * sizeof(double), g, ld);
     }

@@ -30,19 +30,19 @@ __device__ __forceinline__ double max3(double a, double b, double c) { return dm
 // With da = f - fm1, db = fp1 - f:  f - min3 = max(da, 0, -db) and max3 - f = max(-da, 0, db) exactly,
 // so the limiter is min(|df|, 2|da|, 2|db|) when da, db have the same sign and 0 at a local extremum --
 // two min-selects instead of six min/max-selects, identical values (up to the sign of a zero).
-__device__ __forceinline__ double slope_mono_d(double da, double db, double df) {
+// LIM = limiter_type (ffsl_mod.F90:131-140): 0 'none' (slope_simple :1175), 1 'mono', 2 'pd' (slope_pd :1196, f = centre value)
+template <int LIM> __device__ __forceinline__ double slope_mono_d(double da, double db, double df, double f) {
+  if (LIM == 0) return df;
+  if (LIM == 2) return copysign(dmin(fabs(df), 2 * f), df);
   const double lim = dmin(fabs(df), 2 * dmin(fabs(da), fabs(db)));
   return da * db > 0 ? copysign(lim, df) : 0.0;
 }
-__device__ __forceinline__ double slope_mono(double fm1, double f, double fp1) {
-  return slope_mono_d(f - fm1, fp1 - f, (fp1 - fm1) * 0.5);
-}
 // ffsl_mod.F90:1147-1173; the four first differences are shared by the three slopes
-__device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
+template <int LIM> __device__ __forceinline__ void ppm(double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
   const double d1 = fm1 - fm2, d2 = f - fm1, d3 = fp1 - f, d4 = fp2 - fp1;
-  const double dfl = slope_mono_d(d1, d2, (f - fm2) * 0.5);
-  df = slope_mono_d(d2, d3, (fp1 - fm1) * 0.5);
-  const double dfr = slope_mono_d(d3, d4, (fp2 - f) * 0.5);
+  const double dfl = slope_mono_d<LIM>(d1, d2, (f - fm2) * 0.5, fm1);
+  df = slope_mono_d<LIM>(d2, d3, (fp1 - fm1) * 0.5, f);
+  const double dfr = slope_mono_d<LIM>(d3, d4, (fp2 - f) * 0.5, fp1);
   fl = 0.5 * (fm1 + f) + (dfl - df) * (1.0 / 6.0);
   double fr = 0.5 * (fp1 + f) + (df - dfr) * (1.0 / 6.0);
   fl = f - fsign(dmin(fabs(df), fabs(fl - f)), df);
@@ -289,7 +289,7 @@ struct HflxArgs {
 // 6-point window i-2..i+3 (j-2..j+3), whose addresses do not depend on the CFL numbers -- the window
 // loads go out together with the CFL / velocity loads.  Lanes with |cflx| >= 1 (polar rows) re-gather
 // around their own upwind cell and add the whole-cell segment sum (ffsl_mod.F90:831-848).
-template <bool EDGE> __device__ __forceinline__ void hflx_body(const Geo& g, const HflxArgs& a, int i, int j, int k) {
+template <bool EDGE, int LIM> __device__ __forceinline__ void hflx_body(const Geo& g, const HflxArgs& a, int i, int j, int k) {
   const int n = g.nlon, c = gidx(g, i, j, k), rb = c - i;
   const bool dox = j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;     // warp-uniform
   const bool doy = j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
@@ -329,7 +329,7 @@ template <bool EDGE> __device__ __forceinline__ void hflx_body(const Geo& g, con
       }
       const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
       double ml, dm, m6;
-      ppm(x0, x1, x2, x3, x4, ml, dm, m6);
+      ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
       flux = qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
     }
     a.mfx[c] = flux;
@@ -341,17 +341,17 @@ template <bool EDGE> __device__ __forceinline__ void hflx_body(const Geo& g, con
       const double y0 = pos ? yw0 : yw1, y1 = pos ? yw1 : yw2, y2 = pos ? yw2 : yw3, y3 = pos ? yw3 : yw4, y4 = pos ? yw4 : yw5;
       const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
       double ml, dm, m6;
-      ppm(y0, y1, y2, y3, y4, ml, dm, m6);
+      ppm<LIM>(y0, y1, y2, y3, y4, ml, dm, m6);
       flux = qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
     }
     a.mfy[c] = flux;
   }
 }
-__global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
+template <int LIM> __global__ void __launch_bounds__(128) k_hflx(Geo g, HflxArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
   if (i >= g.nlon || j > g.je) return;
-  if (edge_block(g.nlon, 3) || blockIdx.x * blockDim.x < 2) hflx_body<true>(g, a, i, j, k); else hflx_body<false>(g, a, i, j, k);
+  if (edge_block(g.nlon, 3) || blockIdx.x * blockDim.x < 2) hflx_body<true, LIM>(g, a, i, j, k); else hflx_body<false, LIM>(g, a, i, j, k);
 }
 
 // Intermediate fields of the inner advective step (ffsl_mod.F90:354-406)
@@ -400,7 +400,7 @@ struct ColQ {
   }
 };
 // flux through half level k1 (2..nlev)
-__device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, double w) {
+template <int LIM> __device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, double w) {
   if (cz == 0) return 0.0;
   const int ci = (int)cz;
   const double cf = cz - ci;
@@ -408,7 +408,7 @@ __device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, dou
   if (cz > 0) { ku = k1 - ci - 1; s1 = 1 - cf; s2 = 1; for (int l = k1 - ci; l <= k1 - 1; ++l) sm += q(l); }
   else { ku = k1 - ci; s1 = 0; s2 = -cf; for (int l = k1; l <= k1 - ci - 1; ++l) sm += q(l); }
   double ml = 0, dm = 0, m6 = 0;
-  if (ku >= 1 && ku <= q.nlev) ppm(q(ku - 2), q(ku - 1), q(ku), q(ku + 1), q(ku + 2), ml, dm, m6);
+  if (ku >= 1 && ku <= q.nlev) ppm<LIM>(q(ku - 2), q(ku - 1), q(ku), q(ku + 1), q(ku + 2), ml, dm, m6);
   const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);
   return qdiv((cz > 0 ? w : -w) * integ, cz);
 }
@@ -422,7 +422,7 @@ struct PtColArgs {
   double *dpt;          // optional (parity tests), may be NULL
   double dt;
 };
-__global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
+template <int LIM> __global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
   extern __shared__ double pt_s[];       // [nlev][blockDim.x]: the pt column, loaded once
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh M, PtColArgs a) {
     const double po = __ldg(a.pt_old + c), mo = __ldg(a.m_old + c);
     const double dlon = pole ? 0.0 : (fx0 - fxm) * lel * rac;
     const double dlat = pole ? pdm : (fy0 * lea - fys * leas) * rac;
-    const double f_dn = k1 <= g.nlev ? vflx_one(q, k1, cz, w) : 0.0;
+    const double f_dn = k1 <= g.nlev ? vflx_one<LIM>(q, k1, cz, w) : 0.0;
     const double dlev = f_dn - f_up;
     f_up = f_dn;
     const double dpt = -dlon - dlat - dlev;
@@ -663,7 +663,7 @@ __global__ void __launch_bounds__(128) k_negfill_x(Geo g, NegXArgs a) {
 // vertical flux + update + negative filling in z (:259-297), one thread per column,
 // the column staged in shared memory (the update is in place).
 struct TrVArgs { double* q; const double *m, *we, *cflz; double dt; int* flags; };
-__global__ void __launch_bounds__(128) k_tracer_v(Geo g, TrVArgs a) {
+template <int LIM> __global__ void __launch_bounds__(128) k_tracer_v(Geo g, TrVArgs a) {
   extern __shared__ double col[];     // [nlev][blockDim.x]: the old q column
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y;
@@ -681,7 +681,7 @@ __global__ void __launch_bounds__(128) k_tracer_v(Geo g, TrVArgs a) {
     double cz = 0, w = 0;
     if (k1 <= nlev) { cz = __ldg(a.cflz + c + st); w = __ldg(a.we + c + st); }
     const double m = __ldg(a.m + c);
-    const double f_dn = k1 <= nlev ? vflx_one(q, k1, cz, w) : 0.0;
+    const double f_dn = k1 <= nlev ? vflx_one<LIM>(q, k1, cz, w) : 0.0;
     const double qn = qs[k * B] - qdiv((f_dn - f_up) * a.dt, m);
     a.q[c] = qn;                       // the update is in place: the stencil reads the staged column
     neg = neg || qn < 0;

@@ -27,6 +27,7 @@ enum { GMC_EULER = 0, GMC_PC2 = 1, GMC_WRFRK3 = 2 };           /* time_schemes_m
 enum { GMC_PV_MIDPOINT = 0, GMC_PV_UPWIND = 1 };               /* operators_mod.F90:58-69   */
 enum { GMC_BIG_FILTER = 0, GMC_SMALL_FILTER1 = 1, GMC_SMALL_FILTER2 = 2 }; /* block_mod.F90:62-64 */
 enum { GMC_FORCING_NONE = 0, GMC_FORCING_HELD_SUAREZ = 1 };    /* test_forcing_mod.F90:14-28 */
+enum { GMC_LIMITER_NONE = 0, GMC_LIMITER_MONO = 1, GMC_LIMITER_PD = 2 }; /* limiter_type, ffsl_mod.F90:131-140 */
 
 /* The namelist keys and constants the hot path reads
  * (namelist_mod.F90:10-122, const_mod.F90:19-33). */
@@ -47,6 +48,7 @@ typedef struct gmc_config {
   int use_smag_damp;
   int test_forcing;              /* GMC_FORCING_*                                       */
   int ntracers;                  /* tracers in the single 'moist'-like batch (0 = none) */
+  int limiter_type;              /* GMC_LIMITER_* : slope of the PPM sub-grid profile   */
   double ke_cell_wgt, upwind_wgt_pv;
   double div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0;
   double smag_damp_coef;

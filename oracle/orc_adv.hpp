@@ -192,11 +192,21 @@ inline double slope_mono(double fm1, double f, double fp1) {
   return fsign(min3(std::fabs(df), df_min, df_max), df);
 }
 
+// ffsl_mod.F90:1175-1181, 1196-1205 (limiter_type = 'none' | 'pd'); selection :131-140
+inline double slope_simple(double fm1, double, double fp1) { return (fp1 - fm1) * 0.5; }
+inline double slope_pd(double fm1, double f, double fp1) {
+  double df = (fp1 - fm1) * 0.5;
+  return fsign(std::fmin(std::fabs(df), 2 * f), df);
+}
+inline double slope(int lim, double fm1, double f, double fp1) {
+  return lim == GMC_LIMITER_NONE ? slope_simple(fm1, f, fp1) : lim == GMC_LIMITER_PD ? slope_pd(fm1, f, fp1) : slope_mono(fm1, f, fp1);
+}
+
 // ffsl_mod.F90:1147-1173
-inline void ppm(double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
-  double dfl = slope_mono(fm2, fm1, f);
-  df = slope_mono(fm1, f, fp1);
-  double dfr = slope_mono(f, fp1, fp2);
+inline void ppm(int lim, double fm2, double fm1, double f, double fp1, double fp2, double& fl, double& df, double& f6) {
+  double dfl = slope(lim, fm2, fm1, f);
+  df = slope(lim, fm1, f, fp1);
+  double dfr = slope(lim, f, fp1, fp2);
   fl = 0.5 * (fm1 + f) + (dfl - df) / 6.0;
   double fr = 0.5 * (fp1 + f) + (df - dfr) / 6.0;
   fl = f - fsign(std::fmin(std::fabs(df), std::fabs(fl - f)), df);
@@ -212,8 +222,8 @@ inline void hflx_ppm_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const
   const A3 &cflx = B.cflx, &cfly = B.cfly;
   for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
-      ppm(mx(i - 2, j, k), mx(i - 1, j, k), mx(i, j, k), mx(i + 1, j, k), mx(i + 2, j, k), mlx(i, j, k), dmx(i, j, k), m6x(i, j, k));
-      ppm(my(i, j - 2, k), my(i, j - 1, k), my(i, j, k), my(i, j + 1, k), my(i, j + 2, k), mly(i, j, k), dmy(i, j, k), m6y(i, j, k));
+      ppm(b.cfg.limiter_type, mx(i - 2, j, k), mx(i - 1, j, k), mx(i, j, k), mx(i + 1, j, k), mx(i + 2, j, k), mlx(i, j, k), dmx(i, j, k), m6x(i, j, k));
+      ppm(b.cfg.limiter_type, my(i, j - 2, k), my(i, j - 1, k), my(i, j, k), my(i, j + 1, k), my(i, j + 2, k), mly(i, j, k), dmy(i, j, k), m6y(i, j, k));
     }
   fill_halo(mesh, mlx, true, true, true, false, false);
   fill_halo(mesh, dmx, true, true, true, false, false);
@@ -265,7 +275,7 @@ inline void vflx_ppm_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, A3& m
   A3 &mlz = B.qlx, &dmz = B.dqx, &m6z = B.q6x; const A3& cflz = B.cflz;
   for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
-      ppm(m(i, j, k - 2), m(i, j, k - 1), m(i, j, k), m(i, j, k + 1), m(i, j, k + 2), mlz(i, j, k), dmz(i, j, k), m6z(i, j, k));
+      ppm(b.cfg.limiter_type, m(i, j, k - 2), m(i, j, k - 1), m(i, j, k), m(i, j, k + 1), m(i, j, k + 2), mlz(i, j, k), dmz(i, j, k), m6z(i, j, k));
   for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       int ci = (int)cflz(i, j, k);
