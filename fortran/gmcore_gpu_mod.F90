@@ -52,6 +52,8 @@ module gmcore_gpu_mod
     integer(c_int) test_forcing
     integer(c_int) ntracers
     integer(c_int) limiter_type
+    integer(c_int) ffsl_flux_type
+    integer(c_int) reserved_
     real(c_double) ke_cell_wgt, upwind_wgt_pv
     real(c_double) div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0
     real(c_double) smag_damp_coef
@@ -193,6 +195,8 @@ contains
     case ('mono'); cfg%limiter_type = 1
     case ('pd');   cfg%limiter_type = 2
     end select
+    cfg%ffsl_flux_type = merge(1, 0, ffsl_flux_type == 'van_leer')
+    cfg%reserved_ = 0
     cfg%ke_cell_wgt = ke_cell_wgt; cfg%upwind_wgt_pv = upwind_wgt_pv
     cfg%div_damp_coef2 = div_damp_coef2; cfg%div_damp_coef4 = div_damp_coef4
     cfg%div_damp_top = div_damp_top; cfg%div_damp_pole = div_damp_pole; cfg%div_damp_lat0 = div_damp_lat0

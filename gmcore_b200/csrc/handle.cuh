@@ -37,9 +37,11 @@ struct Profiler {
   if ((h)->prof.on) { pe_.e1 = (h)->prof.get(); cudaEventRecord(pe_.e1, (h)->stream); (h)->prof.entries.push_back(pe_); } \
 } while (0)
 
-// kernels templated on the PPM slope limiter (cfg.limiter_type, ffsl_mod.F90:131-140)
-#define LAUNCH_LIM(h, kern, ...) do { switch ((h)->cfg.limiter_type) { \
+// kernels templated on MODE = limiter_type + 4 * ffsl_flux_type (ffsl_mod.F90:116-140)
+#define LAUNCH_LIM(h, kern, ...) do { switch ((h)->cfg.limiter_type + 4 * (h)->cfg.ffsl_flux_type) { \
   case 0: LAUNCH(h, kern<0>, __VA_ARGS__); break; case 2: LAUNCH(h, kern<2>, __VA_ARGS__); break; \
+  case 4: LAUNCH(h, kern<4>, __VA_ARGS__); break; case 5: LAUNCH(h, kern<5>, __VA_ARGS__); break; \
+  case 6: LAUNCH(h, kern<6>, __VA_ARGS__); break; \
   default: LAUNCH(h, kern<1>, __VA_ARGS__); } } while (0)
 
 struct gmc_handle {

@@ -31,7 +31,9 @@ __device__ __forceinline__ double max3(double a, double b, double c) { return dm
 // so the limiter is min(|df|, 2|da|, 2|db|) when da, db have the same sign and 0 at a local extremum --
 // two min-selects instead of six min/max-selects, identical values (up to the sign of a zero).
 // LIM = limiter_type (ffsl_mod.F90:131-140): 0 'none' (slope_simple :1175), 1 'mono', 2 'pd' (slope_pd :1196, f = centre value)
-template <int LIM> __device__ __forceinline__ double slope_mono_d(double da, double db, double df, double f) {
+// Kernels carry MODE = limiter_type + 4 * ffsl_flux_type; only the two low bits matter here.
+template <int MODE> __device__ __forceinline__ double slope_mono_d(double da, double db, double df, double f) {
+  constexpr int LIM = MODE & 3;
   if (LIM == 0) return df;
   if (LIM == 2) return copysign(dmin(fabs(df), 2 * f), df);
   const double lim = dmin(fabs(df), 2 * dmin(fabs(da), fabs(db)));
@@ -49,6 +51,16 @@ template <int LIM> __device__ __forceinline__ void ppm(double fm2, double fm1, d
   fr = f + fsign(dmin(fabs(df), fabs(fr - f)), df);
   f6 = 6 * f - 3 * (fl + fr);
   df = fr - fl;
+}
+// ffsl_flux_type = 'van_leer' (ffsl_mod.F90:556-658): piecewise-linear profile, slope of the upwind cell
+template <int MODE> __device__ __forceinline__ double vl_slope(double fm1, double f, double fp1) {
+  return slope_mono_d<MODE>(f - fm1, fp1 - f, (fp1 - fm1) * 0.5, f);
+}
+// fractional-cell part + whole-cell sum along x / z (ffsl_mod.F90:589-601, 640-652); vel = u | w, c = CFL != 0
+template <int MODE> __device__ __forceinline__ double vl_flux(double fm1, double f, double fp1, double sm, double cf, double c, double vel) {
+  const double dm = vl_slope<MODE>(fm1, f, fp1);
+  const double t = c > 0 ? cf * (f + dm * 0.5 * (1 - cf)) + sm : cf * (f - dm * 0.5 * (1 + cf)) - sm;
+  return qdiv(vel * t, c);
 }
 // The PPM flux integral shared by the three directions (ffsl_mod.F90:831-851).
 __device__ __forceinline__ double ppm_integral(double sm, double ml, double dm, double m6, double s1, double s2) {
@@ -327,16 +339,24 @@ template <bool EDGE, int LIM> __device__ __forceinline__ void hflx_body(const Ge
         if (pos) { for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
         else { for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
       }
-      const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
-      double ml, dm, m6;
-      ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
-      flux = qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
+      if (LIM >= 4) {
+        flux = vl_flux<LIM>(x1, x2, x3, sm, cf, cx, uu);
+      } else {
+        const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+        double ml, dm, m6;
+        ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
+        flux = qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
+      }
     }
     a.mfx[c] = flux;
   }
   if (doy) {
     double flux = 0;
-    if (cy != 0) {
+    if (LIM >= 4) {                       // ffsl_mod.F90:605-611: no zero-CFL branch, ju = j + 1 unless cfly > 0
+      const bool pos = cy > 0;
+      const double y1 = pos ? yw1 : yw2, y2 = pos ? yw2 : yw3, y3 = pos ? yw3 : yw4;
+      flux = vv * (y2 + vl_slope<LIM>(y1, y2, y3) * 0.5 * (copysign(1.0, cy) - cy));
+    } else if (cy != 0) {
       const bool pos = cy > 0;
       const double y0 = pos ? yw0 : yw1, y1 = pos ? yw1 : yw2, y2 = pos ? yw2 : yw3, y3 = pos ? yw3 : yw4, y4 = pos ? yw4 : yw5;
       const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
@@ -407,6 +427,7 @@ template <int LIM> __device__ __forceinline__ double vflx_one(const ColQ& q, int
   int ku; double s1, s2, sm = 0;
   if (cz > 0) { ku = k1 - ci - 1; s1 = 1 - cf; s2 = 1; for (int l = k1 - ci; l <= k1 - 1; ++l) sm += q(l); }
   else { ku = k1 - ci; s1 = 0; s2 = -cf; for (int l = k1; l <= k1 - ci - 1; ++l) sm += q(l); }
+  if (LIM >= 4) return vl_flux<LIM>(q(ku - 1), q(ku), q(ku + 1), sm, cf, cz, w);
   double ml = 0, dm = 0, m6 = 0;
   if (ku >= 1 && ku <= q.nlev) ppm<LIM>(q(ku - 2), q(ku - 1), q(ku), q(ku + 1), q(ku + 2), ml, dm, m6);
   const double integ = ppm_integral(sm, ml, dm, m6, s1, s2);

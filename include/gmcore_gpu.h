@@ -28,6 +28,7 @@ enum { GMC_PV_MIDPOINT = 0, GMC_PV_UPWIND = 1 };               /* operators_mod.
 enum { GMC_BIG_FILTER = 0, GMC_SMALL_FILTER1 = 1, GMC_SMALL_FILTER2 = 2 }; /* block_mod.F90:62-64 */
 enum { GMC_FORCING_NONE = 0, GMC_FORCING_HELD_SUAREZ = 1 };    /* test_forcing_mod.F90:14-28 */
 enum { GMC_LIMITER_NONE = 0, GMC_LIMITER_MONO = 1, GMC_LIMITER_PD = 2 }; /* limiter_type, ffsl_mod.F90:131-140 */
+enum { GMC_FLUX_PPM = 0, GMC_FLUX_VAN_LEER = 1 };              /* ffsl_flux_type, ffsl_mod.F90:116-129 */
 
 /* The namelist keys and constants the hot path reads
  * (namelist_mod.F90:10-122, const_mod.F90:19-33). */
@@ -48,7 +49,9 @@ typedef struct gmc_config {
   int use_smag_damp;
   int test_forcing;              /* GMC_FORCING_*                                       */
   int ntracers;                  /* tracers in the single 'moist'-like batch (0 = none) */
-  int limiter_type;              /* GMC_LIMITER_* : slope of the PPM sub-grid profile   */
+  int limiter_type;              /* GMC_LIMITER_* : slope of the sub-grid profile       */
+  int ffsl_flux_type;            /* GMC_FLUX_* : sub-grid profile of the FFSL fluxes    */
+  int reserved_;                 /* keeps the doubles 8-byte aligned; must be 0         */
   double ke_cell_wgt, upwind_wgt_pv;
   double div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0;
   double smag_damp_coef;

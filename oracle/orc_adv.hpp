@@ -298,12 +298,79 @@ inline void vflx_ppm_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, A3& m
     }
 }
 
+// ffsl_mod.F90:556-616 (ffsl_flux_type = 'van_leer')
+inline void hflx_van_leer_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const A3& mx, const A3& my, A3& mfx, A3& mfy) {
+  const Mesh& mesh = b.mesh;
+  const int lim = b.cfg.limiter_type;
+  const A3 &cflx = B.cflx, &cfly = B.cfly;
+  for (int k = 1; k <= mesh.nlev; ++k) {
+    for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+      int ci = (int)cflx(i, j, k);
+      double cf = cflx(i, j, k) - ci;
+      if (cflx(i, j, k) > 0) {
+        int iu = i - ci;
+        double dm = slope(lim, mx(iu - 1, j, k), mx(iu, j, k), mx(iu + 1, j, k));
+        double sm = 0; for (int l = i + 1 - ci; l <= i; ++l) sm += mx(l, j, k);
+        mfx(i, j, k) = u(i, j, k) * (cf * (mx(iu, j, k) + dm * 0.5 * (1 - cf)) + sm) / cflx(i, j, k);
+      } else if (cflx(i, j, k) < 0) {
+        int iu = i - ci + 1;
+        double dm = slope(lim, mx(iu - 1, j, k), mx(iu, j, k), mx(iu + 1, j, k));
+        double sm = 0; for (int l = i + 1; l <= i - ci; ++l) sm += mx(l, j, k);
+        mfx(i, j, k) = u(i, j, k) * (cf * (mx(iu, j, k) - dm * 0.5 * (1 + cf)) - sm) / cflx(i, j, k);
+      } else {
+        mfx(i, j, k) = 0;
+      }
+    }
+    for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+      double cf = cfly(i, j, k);
+      int ju = cf > 0 ? j : j + 1;
+      double dm = slope(lim, my(i, ju - 1, k), my(i, ju, k), my(i, ju + 1, k));
+      mfy(i, j, k) = v(i, j, k) * (my(i, ju, k) + dm * 0.5 * (std::copysign(1.0, cf) - cf));
+    }
+  }
+}
+
+// ffsl_mod.F90:618-658
+inline void vflx_van_leer_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, A3& mfz) {
+  const Mesh& mesh = b.mesh;
+  const int lim = b.cfg.limiter_type;
+  const A3& cflz = B.cflz;
+  for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+    for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+      int ci = (int)cflz(i, j, k);
+      double cf = cflz(i, j, k) - ci;
+      if (cflz(i, j, k) > 0) {
+        int ku = k - ci - 1;
+        double dm = slope(lim, m(i, j, ku - 1), m(i, j, ku), m(i, j, ku + 1));
+        double sm = 0; for (int l = k - ci; l <= k - 1; ++l) sm += m(i, j, l);
+        mfz(i, j, k) = w(i, j, k) * (cf * (m(i, j, ku) + dm * 0.5 * (1 - cf)) + sm) / cflz(i, j, k);
+      } else if (cflz(i, j, k) < 0) {
+        int ku = k - ci;
+        double dm = slope(lim, m(i, j, ku - 1), m(i, j, ku), m(i, j, ku + 1));
+        double sm = 0; for (int l = k; l <= k - ci - 1; ++l) sm += m(i, j, l);
+        mfz(i, j, k) = w(i, j, k) * (cf * (m(i, j, ku) - dm * 0.5 * (1 + cf)) - sm) / cflz(i, j, k);
+      } else {
+        mfz(i, j, k) = 0;
+      }
+    }
+}
+
+// the hflx / vflx procedure pointers bound by ffsl_init (ffsl_mod.F90:116-129)
+inline void hflx_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const A3& mx, const A3& my, A3& mfx, A3& mfy) {
+  if (b.cfg.ffsl_flux_type == GMC_FLUX_VAN_LEER) hflx_van_leer_cell(b, B, u, v, mx, my, mfx, mfy);
+  else hflx_ppm_cell(b, B, u, v, mx, my, mfx, mfy);
+}
+inline void vflx_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, A3& mfz) {
+  if (b.cfg.ffsl_flux_type == GMC_FLUX_VAN_LEER) vflx_van_leer_cell(b, B, w, m, mfz);
+  else vflx_ppm_cell(b, B, w, m, mfz);
+}
+
 // ffsl_mod.F90:318-413
 inline void ffsl_calc_tracer_hflx_cell(Block& b, AdvBatch& B, const A3& q, A3& qmfx, A3& qmfy, double dt, bool has_dt) {
   const Mesh& mesh = b.mesh;
   double dt_ = has_dt ? dt : B.dt;
   A3 &qx = B.qx, &qy = B.qy; const A3 &divx = B.divx, &divy = B.divy;
-  hflx_ppm_cell(b, B, B.u, B.v, q, q, qmfx, qmfy);
+  hflx_cell(b, B, B.u, B.v, q, q, qmfx, qmfy);
   fill_halo(mesh, qmfx, true, true, true, false, false);
   fill_halo(mesh, qmfy, false, false, false, true, true);
   for (int k = 1; k <= mesh.nlev; ++k)
@@ -336,12 +403,12 @@ inline void ffsl_calc_tracer_hflx_cell(Block& b, AdvBatch& B, const A3& q, A3& q
   }
   fill_halo(mesh, qx, true, false, false, true, true);
   fill_halo(mesh, qy, true, true, true, false, false);
-  hflx_ppm_cell(b, B, B.mfx, B.mfy, qy, qx, qmfx, qmfy);
+  hflx_cell(b, B, B.mfx, B.mfy, qy, qx, qmfx, qmfy);
 }
 
 // ffsl_mod.F90:415-432
 inline void ffsl_calc_tracer_vflx_cell(Block& b, AdvBatch& B, const A3& q, A3& qmfz) {
-  vflx_ppm_cell(b, B, B.we, q, qmfz);
+  vflx_cell(b, B, B.we, q, qmfz);
 }
 
 }  // namespace orc
