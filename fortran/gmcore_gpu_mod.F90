@@ -53,7 +53,7 @@ module gmcore_gpu_mod
     integer(c_int) ntracers
     integer(c_int) limiter_type
     integer(c_int) ffsl_flux_type
-    integer(c_int) reserved_
+    integer(c_int) tvd_limiter_type
     real(c_double) ke_cell_wgt, upwind_wgt_pv
     real(c_double) div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0
     real(c_double) smag_damp_coef
@@ -182,7 +182,12 @@ contains
     case ('wrfrk3'); cfg%time_scheme = 2
     end select
     cfg%ke_scheme = ke_scheme
-    cfg%pv_scheme = merge(0, 1, pv_scheme == 'midpoint')
+    select case (pv_scheme)
+    case ('midpoint'); cfg%pv_scheme = 0
+    case ('upwind');   cfg%pv_scheme = 1
+    case ('tvd');      cfg%pv_scheme = 2
+    case default;      cfg%pv_scheme = -1          ! 'ffsl': rejected by gmc_create
+    end select
     cfg%upwind_order_pv = upwind_order_pv
     cfg%pv_pole_stokes = merge(1, 0, pv_pole_stokes)
     cfg%coriolis_scheme = coriolis_scheme
@@ -196,7 +201,11 @@ contains
     case ('pd');   cfg%limiter_type = 2
     end select
     cfg%ffsl_flux_type = merge(1, 0, ffsl_flux_type == 'van_leer')
-    cfg%reserved_ = 0
+    select case (tvd_limiter_type)
+    case ('none');     cfg%tvd_limiter_type = 0
+    case ('van_leer'); cfg%tvd_limiter_type = 1
+    case ('mc');       cfg%tvd_limiter_type = 2
+    end select
     cfg%ke_cell_wgt = ke_cell_wgt; cfg%upwind_wgt_pv = upwind_wgt_pv
     cfg%div_damp_coef2 = div_damp_coef2; cfg%div_damp_coef4 = div_damp_coef4
     cfg%div_damp_top = div_damp_top; cfg%div_damp_pole = div_damp_pole; cfg%div_damp_lat0 = div_damp_lat0

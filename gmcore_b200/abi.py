@@ -6,7 +6,8 @@ the struct sizes against the compiled library.
 import ctypes as C
 
 GMC_EULER, GMC_PC2, GMC_WRFRK3 = 0, 1, 2
-GMC_PV_MIDPOINT, GMC_PV_UPWIND = 0, 1
+GMC_PV_MIDPOINT, GMC_PV_UPWIND, GMC_PV_TVD = 0, 1, 2
+GMC_TVD_NONE, GMC_TVD_VAN_LEER, GMC_TVD_MC = 0, 1, 2
 GMC_BIG_FILTER, GMC_SMALL_FILTER1, GMC_SMALL_FILTER2 = 0, 1, 2
 GMC_FORCING_NONE, GMC_FORCING_HELD_SUAREZ = 0, 1
 GMC_LIMITER_NONE, GMC_LIMITER_MONO, GMC_LIMITER_PD = 0, 1, 2
@@ -15,7 +16,7 @@ GMC_FLUX_PPM, GMC_FLUX_VAN_LEER = 0, 1
 _INT_FIELDS = ["nlon", "nlat", "nlev", "hx", "hy", "lat_ibeg", "lat_iend", "device", "rank", "nranks",
                "baroclinic", "time_scheme", "ke_scheme", "pv_scheme", "upwind_order_pv", "pv_pole_stokes",
                "coriolis_scheme", "use_div_damp", "div_damp_order", "div_damp_k0", "use_smag_damp",
-               "test_forcing", "ntracers", "limiter_type", "ffsl_flux_type", "reserved_"]
+               "test_forcing", "ntracers", "limiter_type", "ffsl_flux_type", "tvd_limiter_type"]
 _DBL_FIELDS = ["ke_cell_wgt", "upwind_wgt_pv", "div_damp_coef2", "div_damp_coef4", "div_damp_top",
                "div_damp_pole", "div_damp_lat0", "smag_damp_coef", "dt_dyn", "dt_adv",
                "omega", "radius", "g", "Rd", "cpd", "p0", "Rd_o_cpd", "ptop", "hybrid_p0"]

@@ -56,7 +56,7 @@ int gmc_prepare_run(gmc_handle* h, int old_) {
     run_filter(h, S.v, 1, g.nlev, GMC_BIG_FILTER, S.v_f, -1, nullptr);
     // gz_f = big(gz); calc_m: m = (gz - gzs) / g
     run_filter(h, S.gz, 0, g.nlev, GMC_BIG_FILTER, S.gz_f, -1, nullptr, POST_SWM_M, nullptr, S.m);
-    run_forward_prepare(h, S);
+    run_forward_prepare(h, S, h->cfg.dt_dyn);
   } else {
     for_bands(h, [&](gmc_handle* b) {
       DState& S = b->st[old_];

@@ -34,6 +34,8 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   h->cfg = *cfg;
   if (cudaSetDevice(cfg->device) != cudaSuccess) { snprintf(g_create_err, sizeof(g_create_err), "cudaSetDevice(%d) failed", cfg->device); delete h; return 2; }
   if (cfg->limiter_type < 0 || cfg->limiter_type > 2) { snprintf(g_create_err, sizeof(g_create_err), "Invalid limiter_type %d!", cfg->limiter_type); delete h; return 3; }
+  if (cfg->pv_scheme < 0 || cfg->pv_scheme > 2) { snprintf(g_create_err, sizeof(g_create_err), "Invalid pv_scheme %d! (midpoint, upwind, tvd; 'ffsl' is not functional in the reference either)", cfg->pv_scheme); delete h; return 3; }
+  if (cfg->tvd_limiter_type < 0 || cfg->tvd_limiter_type > 2) { snprintf(g_create_err, sizeof(g_create_err), "Invalid tvd_limiter_type %d!", cfg->tvd_limiter_type); delete h; return 3; }
   if (cfg->ffsl_flux_type < 0 || cfg->ffsl_flux_type > 1) { snprintf(g_create_err, sizeof(g_create_err), "Invalid ffsl_flux_type %d!", cfg->ffsl_flux_type); delete h; return 3; }
   if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
   if (cfg->coriolis_scheme != 1 && cfg->coriolis_scheme != 2) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d is not a GMCORE scheme (1 or 2)", cfg->coriolis_scheme); delete h; return 3; }

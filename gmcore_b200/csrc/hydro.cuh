@@ -149,7 +149,7 @@ static void hydro_accum_wind(gmc_handle* h, int itime);
 extern "C" { static int xfer(gmc_handle* h, double* dev, double* host, int kind, int dir); }
 
 // forward-pass diagnostics of a state on rows jb-2..je+2 (pv needs two rows either side)
-static void run_forward_prepare_x(gmc_handle* h, DState& S) {
+static void run_forward_prepare_x(gmc_handle* h, DState& S, double dt /* interp_pv_tvd only */) {
   const Geo g2 = xg(h, 2, 2), g1 = xg(h, 1, 1);
   Fwd1Args f{S.u_f, S.v_f, S.m, S.mfx_lon, S.mfy_lat, S.u_lat, S.v_lon, S.ke, S.pv, S.div, h->cfg.ke_scheme, h->cfg.ke_cell_wgt};
   LAUNCH(h, k_fwd1, tile_grid(g2, 1), tile_block(), 0, g2, h->M, f);
@@ -157,7 +157,7 @@ static void run_forward_prepare_x(gmc_handle* h, DState& S) {
     Pole1Args p{S.v_f, S.m, S.u_lat, S.mfy_lat, S.ke, S.div, S.pv, h->pole_dmf, h->cfg.pv_pole_stokes};
     LAUNCH(h, k_pole1, dim3(h->g.nlev, 2), 256, 0, h->g, h->M, p);
   }
-  PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv};
+  PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv, h->M.rows, dt, h->cfg.tvd_limiter_type};
   LAUNCH(h, k_pv_edge, tile_grid(g1, g1.nlev), tile_block(), 0, g1, e);
 }
 
@@ -166,7 +166,7 @@ static void run_forward_prepare_x(gmc_handle* h, DState& S) {
 static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, double dt) {
   const Geo g = h->g, g01 = xg(h, 0, 1);
   // ---- forward pass on star -------------------------------------------------------
-  run_forward_prepare_x(h, star);
+  run_forward_prepare_x(h, star, dt);
   run_cfl(h, star.u_f, star.v_f, h->cflx, h->cfly, h->divx, h->divy, dt);
   WeArgs w{star.mfx_lon, star.mfy_lat, h->pole_dmf, star.m_lev, star.we_lev, h->dphs, h->cflz, dt, h->dflags};
   LAUNCH(h, k_we_col, gridg(g01, 1), 128, (size_t)(g.nlev + 1) * 128 * sizeof(double), g01, h->M, w);
@@ -240,7 +240,7 @@ static void hydro_prepare_run_2(gmc_handle* h, int old_) {
   const Geo g44 = xg(h, 4, 4), g01 = xg(h, 0, 1);
   run_ph(h, S, g44);
   run_gz(h, S, g01);
-  run_forward_prepare_x(h, S);
+  run_forward_prepare_x(h, S, h->cfg.dt_dyn);
   run_cfl(h, S.u_f, S.v_f, h->cflx, h->cfly, h->divx, h->divy, h->cfg.dt_dyn);
 }
 // extra arrays of the start-up exchange: phs (old%phs is read on row je+1) and the tracers

@@ -201,17 +201,28 @@ __device__ __forceinline__ double upwind3(double dir, double wgt, double f1, dou
   return c31 * (f3 + f2) + c32 * (f4 + f1) + c33 * (f4 - f1 - 3 * (f3 - f2)) * wgt * dir;
 }
 
-// K2: interp_pv_upwind / interp_pv_midpoint (:705-795)
+// adv/tvd_mod.F90:42-85 (eps = default-real 1.0e-6 widened, :50); lim = tvd_limiter_type
+__device__ __forceinline__ double tvd(int lim, double cfl, double fm1, double f, double fp1, double fp2) {
+  const double eps = (double)1.0e-6f;
+  const double r = qdiv((cfl > 0 ? f - fm1 : fp2 - fp1) + eps, fp1 - f + eps);
+  double C = 1.0;
+  if (lim == GMC_TVD_MC) C = fmax(0.0, fmin(fmin(2.0 * r, 0.5 * (1 + r)), 2.0));
+  else if (lim == GMC_TVD_VAN_LEER) C = qdiv(r + fabs(r), 1 + fabs(r));
+  return 0.5 * (fp1 + f - ((1 - C) * sign1(cfl) + cfl * C) * (fp1 - f));
+}
+
+// K2: interp_pv_upwind / interp_pv_midpoint / interp_pv_tvd (:705-832)
 struct PvEdgeArgs {
   const double *pv, *u, *v, *u_lat, *v_lon;
   double *pv_lon, *pv_lat;
   int scheme, order; double wgt;
+  const RowCoef* rows; double dt; int tvd_lim;     // pv_scheme = tvd only
 };
 template <bool EDGE> __device__ __forceinline__ void pv_edge_body(const Geo& g, const PvEdgeArgs& a, int i, int j, int k) {
   const int n = g.nlon, c = gidx(g, i, j, k);
   const double eps = 2.220446049250313e-16;
   const bool full = j > 1 && j < g.nlat, half = j <= g.nhalf;      // warp-uniform
-  const bool up = a.scheme != 0, o3 = a.order != 1;
+  const bool tv = a.scheme == GMC_PV_TVD, up = a.scheme != 0, o3 = a.order != 1 || tv;
   const double* __restrict__ pv = a.pv + c;
   // one memory phase: the pv cross (4 rows x 4 columns of it) and the four wind components
   double pm1 = 0, p0 = 0, pm2 = 0, pp1 = 0, vt = 0, un = 0;
@@ -228,6 +239,7 @@ template <bool EDGE> __device__ __forceinline__ void pv_edge_body(const Geo& g, 
   }
   if (full) {
     if (!up) a.pv_lon[c] = 0.5 * (p0 + pm1);
+    else if (tv) a.pv_lon[c] = tvd(a.tvd_lim, qdiv(vt * a.dt, a.rows[j + 1].le_lon), pm2, pm1, p0, pp1);
     else {
       const double b = qdiv(fabs(vt), sqrt(un * un + vt * vt) + eps);
       const double upw = o3 ? upwind3(sign1(vt), a.wgt, pm2, pm1, p0, pp1) : upwind1(sign1(vt), a.wgt, pm1, p0);
@@ -236,6 +248,7 @@ template <bool EDGE> __device__ __forceinline__ void pv_edge_body(const Geo& g, 
   }
   if (half) {
     if (!up) a.pv_lat[c] = 0.5 * (qm1 + q0);
+    else if (tv) a.pv_lat[c] = tvd(a.tvd_lim, qdiv(ut * a.dt, a.rows[j + 1].le_lat), qm2, qm1, q0, qp1);
     else {
       const double b = qdiv(fabs(ut), sqrt(ut * ut + vn * vn) + eps);
       const double upw = o3 ? upwind3(sign1(ut), a.wgt, qm2, qm1, q0, qp1) : upwind1(sign1(ut), a.wgt, qm1, q0);

@@ -15,13 +15,13 @@ static inline size_t filt_smem(const gmc_handle* h) { return (size_t)(2 * (h->g.
 
 // operators_prepare(forward_pass) for the horizontal part: calc_mf, calc_ke, calc_div,
 // calc_pv, interp_pv (operators_mod.F90:117-122)
-static void run_forward_prepare(gmc_handle* h, DState& S) {
+static void run_forward_prepare(gmc_handle* h, DState& S, double dt /* interp_pv_tvd only */) {
   const Geo& g = h->g;
   Fwd1Args f{S.u_f, S.v_f, S.m, S.mfx_lon, S.mfy_lat, S.u_lat, S.v_lon, S.ke, S.pv, S.div, h->cfg.ke_scheme, h->cfg.ke_cell_wgt};
   LAUNCH(h, k_fwd1, tile_grid(g, 1), tile_block(), 0, g, h->M, f);
   Pole1Args p{S.v_f, S.m, S.u_lat, S.mfy_lat, S.ke, S.div, S.pv, h->pole_dmf, h->cfg.pv_pole_stokes};
   LAUNCH(h, k_pole1, dim3(g.nlev, 2), 256, 0, g, h->M, p);
-  PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv};
+  PvEdgeArgs e{S.pv, S.u_f, S.v_f, S.u_lat, S.v_lon, S.pv_lon, S.pv_lat, h->cfg.pv_scheme, h->cfg.upwind_order_pv, h->cfg.upwind_wgt_pv, h->M.rows, dt, h->cfg.tvd_limiter_type};
   LAUNCH(h, k_pv_edge, tile_grid(g, g.nlev), tile_block(), 0, g, e);
 }
 
@@ -58,7 +58,7 @@ static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int 
 // One shallow-water step(old, star, new, dt) (time_schemes_mod.F90:102-118).
 static void swm_step(gmc_handle* h, DState& old_, DState& star, DState& nw, double dt) {
   const Geo& g = h->g;
-  run_forward_prepare(h, star);
+  run_forward_prepare(h, star, dt);
   TendArgs t{};
   t.mfx_lon = star.mfx_lon; t.mfy_lat = star.mfy_lat; t.pv_lon = star.pv_lon; t.pv_lat = star.pv_lat; t.ke = star.ke;
   t.we_lev = nullptr; t.du = h->du; t.dv = h->dv;

@@ -66,6 +66,7 @@ class Host:
         cfg.test_forcing = abi.GMC_FORCING_HELD_SUAREZ if test_case == "held_suarez" else abi.GMC_FORCING_NONE
         cfg.ntracers = (1 if baroclinic else 0) if ntracers is None else ntracers   # moist_mod.F90:18 'qv'
         cfg.limiter_type = abi.GMC_LIMITER_MONO           # namelist_mod.F90 default 'mono'
+        cfg.tvd_limiter_type = abi.GMC_TVD_VAN_LEER        # namelist_mod.F90:70 default 'van_leer'
         cfg.ffsl_flux_type = abi.GMC_FLUX_PPM              # namelist_mod.F90:69 default 'ppm'
         cfg.ke_cell_wgt, cfg.upwind_wgt_pv = 0.5, 1.0
         cfg.div_damp_coef2, cfg.div_damp_coef4 = 1.0 / 128.0, 0.01

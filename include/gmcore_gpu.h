@@ -24,7 +24,8 @@ extern "C" {
 typedef struct gmc_handle gmc_handle;
 
 enum { GMC_EULER = 0, GMC_PC2 = 1, GMC_WRFRK3 = 2 };           /* time_schemes_mod.F90:67-76 */
-enum { GMC_PV_MIDPOINT = 0, GMC_PV_UPWIND = 1 };               /* operators_mod.F90:58-69   */
+enum { GMC_PV_MIDPOINT = 0, GMC_PV_UPWIND = 1, GMC_PV_TVD = 2 }; /* operators_mod.F90:58-69 ('ffsl' is not functional upstream) */
+enum { GMC_TVD_NONE = 0, GMC_TVD_VAN_LEER = 1, GMC_TVD_MC = 2 }; /* tvd_limiter_type, adv/tvd_mod.F90:27-40 */
 enum { GMC_BIG_FILTER = 0, GMC_SMALL_FILTER1 = 1, GMC_SMALL_FILTER2 = 2 }; /* block_mod.F90:62-64 */
 enum { GMC_FORCING_NONE = 0, GMC_FORCING_HELD_SUAREZ = 1 };    /* test_forcing_mod.F90:14-28 */
 enum { GMC_LIMITER_NONE = 0, GMC_LIMITER_MONO = 1, GMC_LIMITER_PD = 2 }; /* limiter_type, ffsl_mod.F90:131-140 */
@@ -51,7 +52,7 @@ typedef struct gmc_config {
   int ntracers;                  /* tracers in the single 'moist'-like batch (0 = none) */
   int limiter_type;              /* GMC_LIMITER_* : slope of the sub-grid profile       */
   int ffsl_flux_type;            /* GMC_FLUX_* : sub-grid profile of the FFSL fluxes    */
-  int reserved_;                 /* keeps the doubles 8-byte aligned; must be 0         */
+  int tvd_limiter_type;          /* GMC_TVD_* : flux limiter of pv_scheme = GMC_PV_TVD  */
   double ke_cell_wgt, upwind_wgt_pv;
   double div_damp_coef2, div_damp_coef4, div_damp_top, div_damp_pole, div_damp_lat0;
   double smag_damp_coef;

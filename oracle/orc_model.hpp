@@ -54,10 +54,10 @@ struct Model {
       if (baro) calc_ph(b, s);
       calc_m(b, s);
       if (baro) calc_t(b, s);
-      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s);
+      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s, dt);
       if (baro) calc_gz_lev(b, s);
     } else if (pass == 1) {    // forward_pass
-      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s);
+      calc_mf(b, s, dt); calc_ke(b, s); calc_div(b, s); calc_pv(b, s); interp_pv(b, s, dt);
     } else {                   // backward_pass
       if (baro) { calc_ph(b, s); calc_t(b, s); calc_gz_lev(b, s); }
       calc_m(b, s);
@@ -69,7 +69,7 @@ struct Model {
     if (baro) calc_ph(b, s);
     calc_m(b, s);
     if (baro) calc_t(b, s);
-    calc_mf(b, s, dt); calc_ke(b, s); calc_pv(b, s); interp_pv(b, s); calc_div(b, s);
+    calc_mf(b, s, dt); calc_ke(b, s); calc_pv(b, s); interp_pv(b, s, dt); calc_div(b, s);
     if (baro) calc_gz_lev(b, s);
   }
 

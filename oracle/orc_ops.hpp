@@ -266,8 +266,43 @@ inline void interp_pv_upwind(Block& b, State& s) {
   fill_halo(mesh, s.pv_lat, false, true, true, true, false);
 }
 
-inline void interp_pv(Block& b, State& s) {
-  if (b.cfg.pv_scheme == GMC_PV_MIDPOINT) interp_pv_midpoint(b, s); else interp_pv_upwind(b, s);
+// adv/tvd_mod.F90:42-85.  eps is the default-real literal 1.0e-6 widened to r8 (tvd_mod.F90:50).
+inline double tvd_flux_limiter(int type, double r) {
+  if (type == GMC_TVD_NONE) return 1.0;
+  if (type == GMC_TVD_MC) return std::fmax(0.0, std::fmin(std::fmin(2.0 * r, 0.5 * (1 + r)), 2.0));
+  return (r + std::fabs(r)) / (1 + std::fabs(r));
+}
+inline double tvd(int type, double cfl, double fm1, double f, double fp1, double fp2) {
+  const double eps = (double)1.0e-6f;
+  double r = cfl > 0 ? (f - fm1 + eps) / (fp1 - f + eps) : (fp2 - fp1 + eps) / (fp1 - f + eps);
+  double C = tvd_flux_limiter(type, r);
+  return 0.5 * (fp1 + f - ((1 - C) * sign1(cfl) + cfl * C) * (fp1 - f));
+}
+
+// operators_mod.F90:797-832
+inline void interp_pv_tvd(Block& b, State& s, double dt) {
+  const Mesh& mesh = b.mesh;
+  const A3 &ut = s.u_lat, &vt = s.v_lon, &pv = s.pv;
+  const int type = b.cfg.tvd_limiter_type;
+  for (int k = 1; k <= mesh.nlev; ++k) {
+    for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+      double cfl = vt(i, j, k) * dt / mesh.le_lon(j);
+      s.pv_lon(i, j, k) = tvd(type, cfl, pv(i, j - 2, k), pv(i, j - 1, k), pv(i, j, k), pv(i, j + 1, k));
+    }
+    for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+      double cfl = ut(i, j, k) * dt / mesh.le_lat(j);
+      s.pv_lat(i, j, k) = tvd(type, cfl, pv(i - 2, j, k), pv(i - 1, j, k), pv(i, j, k), pv(i + 1, j, k));
+    }
+  }
+  fill_halo(mesh, s.pv_lon, true, true, true, false, true);
+  fill_halo(mesh, s.pv_lat, false, true, true, true, false);
+}
+
+// procedure pointer bound by operators_init (operators_mod.F90:56-70)
+inline void interp_pv(Block& b, State& s, double dt) {
+  if (b.cfg.pv_scheme == GMC_PV_MIDPOINT) interp_pv_midpoint(b, s);
+  else if (b.cfg.pv_scheme == GMC_PV_TVD) interp_pv_tvd(b, s, dt);
+  else interp_pv_upwind(b, s);
 }
 
 // operators_mod.F90:846-906

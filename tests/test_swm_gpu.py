@@ -104,3 +104,16 @@ def test_coriolis_scheme2_parity(gpu_required, nlev):
             assert np.linalg.norm((a - b).ravel()) / scale <= TOL_STEP, (step, name)
         # tm, te; tpe is built from pv_lon whose upwind side is arbitrary while v_lon is round-off noise
         np.testing.assert_allclose(dg[:, [0, 1]], do[:, [0, 1]], rtol=1e-12)
+
+
+def test_pv_tvd_swm_parity(gpu_required):
+    """pv_scheme = 'tvd' on the shallow-water core (operators_mod.F90:797-832), stage dt = dt/3, dt/2, dt under wrfrk3."""
+    host, ic, orc, gpu = make_pair(64, 33, 1, 600.0, "rossby_haurwitz_wave", pv_scheme=2)
+    orc.prepare_run(); gpu.prepare_run()
+    for step in range(3):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        for name, loc in PROGNOSTIC_SWM:
+            a = host.interior(gpu.field(name), loc); b = host.interior(orc.field(name), loc)
+            scale = np.linalg.norm(host.interior(orc.field("u_lon"), "lon")) if name in ("u_lon", "v_lat") else np.linalg.norm(b)
+            assert np.linalg.norm((a - b).ravel()) / scale <= TOL_STEP, (step, name)
+        np.testing.assert_allclose(dg[:, [0, 1]], do[:, [0, 1]], rtol=1e-12)
