@@ -64,6 +64,11 @@ struct DMesh {
   // the 1e-12 parity bar) -- FP64 divides are ~30 issue slots each and dominated several kernels.
   const double *r_area_cell, *r_area_vtx, *r_de_lon, *r_de_lat, *r_area_lon, *r_area_lat;
   const double *r_full_dlev;   // 1 / full_dlev, same bounds (-1 : nlev+2)
+  // Pure-pressure levels: the leading nconst interfaces have hybi == 0, so ph_lev there is the same
+  // number in every column and its pow / log are formed once per level ON THE DEVICE (k_lev_tab, the
+  // same expressions as k_ph / k_gz_col, hence the same bits) instead of once per grid point:
+  // lev_tab[k] = ph_lev(k+1)^kappa, lev_tab[nlev+1+k] = (ph(k+1)/p0)^kappa, lev_tab[2(nlev+1)+k] = log(ph_lev(k+2)/ph_lev(k+1)).
+  const double *lev_tab; int nconst;
   int hx;
 };
 #define MJ(v, j) (v[(j) + 1])                  // vector entry at latitude index j

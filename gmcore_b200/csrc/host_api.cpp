@@ -21,7 +21,13 @@ struct gmh_host {
 extern "C" {
 
 gmh_host* gmh_create(int nlon, int nlat, int nlev, double dt_dyn, double ptop) {
+  return gmh_create_opts(nlon, nlat, nlev, dt_dyn, ptop, 0.0, 100.0, 0);
+}
+gmh_host* gmh_create_opts(int nlon, int nlat, int nlev, double dt_dyn, double ptop,
+                          double coarse_pole_mul, double coarse_pole_decay, int tangent_wgt_thuburn09) {
   gmh_host* h = new gmh_host();
+  h->mesh.coarse_pole_mul = coarse_pole_mul; h->mesh.coarse_pole_decay = coarse_pole_decay;
+  h->mesh.thuburn09 = tangent_wgt_thuburn09;
   h->ptop = ptop;
   h->fcfg.dt_dyn = dt_dyn;
   // gmcore_init: mesh with the namelist halo (2); block stage 1 builds the filters;

@@ -140,6 +140,9 @@ struct Mesh {
   Vec2 full_tangent_wgt, half_tangent_wgt;
   // vertical (filled by vert coord set-up; bounds full -1:nlev+2, half 1:nlev+1)
   Vec full_lev, half_lev, full_dlev, half_dlev;
+  // namelist_mod.F90:85-86 and tangent_wgt_scheme ('classic' | 'thuburn09'); set before init()
+  double coarse_pole_mul = 0, coarse_pole_decay = 100.0;
+  int thuburn09 = 0;
 
   void init(const Consts& c, int nlon_, int nlat_, int nlev_, int hx_, int hy_ = 2) {
     const double inf = 1.79769313486231570815e+308;  // huge(1.0_r8)
@@ -180,7 +183,18 @@ struct Mesh {
       half_lat(j) = start_lat + (j - 0.5) * dlat0;
       if (std::fabs(half_lat(j)) < (double)1.0e-12f) half_lat(j) = 0.0;
     }
-    for (int j = 1; j <= num_half_lat; ++j) dlat(j) = dlat0;   // coarse_pole_mul == 0
+    if (coarse_pole_mul != 0) {          // mesh_mod.F90:195-202: dlat stretched towards the poles, renormalised to pi
+      dlat0 = dlon;
+      double sum = 0;
+      for (int j = 1; j <= num_half_lat; ++j) {
+        const double d = std::fabs(half_lat(j)) - c.pi05;
+        dlat(j) = dlat0 * (1 + (coarse_pole_mul - 1) * std::exp(-coarse_pole_decay * (d * d)));
+        sum += dlat(j);
+      }
+      for (int j = 1; j <= num_half_lat; ++j) dlat(j) = dlat(j) / sum * c.pi;
+    } else {
+      for (int j = 1; j <= num_half_lat; ++j) dlat(j) = dlat0;
+    }
     full_lat(1) = start_lat; full_lat_deg(1) = start_lat * c.deg;
     for (int j = 2; j <= nlat - 1; ++j) {
       full_lat(j) = full_lat(j - 1) + dlat(j - 1);
@@ -275,14 +289,14 @@ struct Mesh {
       le_lat(j) = radius * half_cos_lat(j) * dlon;
       de_lat(j) = 2.0 * area_lat(j) / le_lat(j);
     }
-    // tangent_wgt_scheme = 'classic' (mesh_mod.F90:417-427)
+    // tangent_wgt_scheme = 'classic' | 'thuburn09' (mesh_mod.F90:417-438)
     for (int j = 2; j <= nlat - 1; ++j) {
-      full_tangent_wgt(1, j) = le_lat(j - 1) / de_lon(j) * 0.25;
-      full_tangent_wgt(2, j) = le_lat(j) / de_lon(j) * 0.25;
+      full_tangent_wgt(1, j) = le_lat(j - 1) / de_lon(j) * (thuburn09 ? area_subcell(2, j) / area_cell(j) : 0.25);
+      full_tangent_wgt(2, j) = le_lat(j) / de_lon(j) * (thuburn09 ? area_subcell(1, j) / area_cell(j) : 0.25);
     }
     for (int j = 1; j <= num_half_lat; ++j) {
-      half_tangent_wgt(1, j) = le_lon(j) / de_lat(j) * 0.25;
-      half_tangent_wgt(2, j) = le_lon(j + 1) / de_lat(j) * 0.25;
+      half_tangent_wgt(1, j) = le_lon(j) / de_lat(j) * (thuburn09 ? area_subcell(1, j) / area_cell(j) : 0.25);
+      half_tangent_wgt(2, j) = le_lon(j + 1) / de_lat(j) * (thuburn09 ? area_subcell(2, j + 1) / area_cell(j + 1) : 0.25);
     }
     for (int j = 1; j <= nlat; ++j) full_f(j) = 2.0 * c.omega * full_sin_lat(j);
     for (int j = 1; j <= num_half_lat; ++j) half_f(j) = 2.0 * c.omega * half_sin_lat(j);

@@ -33,6 +33,18 @@ static int hydro_alloc(gmc_handle* h) {
 // (div_damp_mod.F90:27-87) and the lon_damp latitude profile (lon_damp_mod.F90:43-68).
 static int hydro_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
   const gmc_config& c = h->cfg;
+  {  // pure-pressure levels (hybi == 0 from the top down): per-level pow / log table, see DMesh.lev_tab
+    int nconst = 0;
+    while (nconst <= c.nlev && mv->hybi[nconst] == 0.0) ++nconst;
+    if (getenv("GMCORE_NO_LEVTAB")) nconst = 0;
+    double* tab = nullptr;
+    if (dev_alloc(h, &tab, (size_t)3 * (c.nlev + 1))) return 1;
+    cudaMemset(tab, 0, (size_t)3 * (c.nlev + 1) * sizeof(double));
+    h->M.lev_tab = tab; h->M.nconst = 0;
+    k_lev_tab<<<(c.nlev + 128) / 128, 128, 0, h->stream>>>(h->M, make_vc(h), c.nlev, tab);
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) { snprintf(h->err, sizeof(h->err), "k_lev_tab failed"); return 1; }
+    h->M.nconst = nconst;
+  }
   const int nlat = c.nlat, nhalf = c.nlat - 1, nlev = c.nlev, hy = c.hy;
   auto F = [&](const double* v, int j) { return v[j - (1 - hy)]; };
   std::vector<double> cl((size_t)nlat * nlev, 0.0), ca((size_t)nhalf * nlev, 0.0);

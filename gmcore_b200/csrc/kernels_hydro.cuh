@@ -494,12 +494,27 @@ __global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
   const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
   const long long c = gidx(g, i, j, k);
   const double pl = ph_lev_at(M, a.vc, k + 1, phs);
-  a.ph_exn_lev[c] = pow(pl, a.vc.kappa);
+  a.ph_exn_lev[c] = k + 1 <= M.nconst ? __ldg(M.lev_tab + k) : pow(pl, a.vc.kappa);
   a.m_lev[c] = m_lev_at(M, a.vc, g.nlev, k + 1, phs);
   if (k < g.nlev) {
     const double m = ph_lev_at(M, a.vc, k + 2, phs) - pl;
     a.m[c] = m;
     if (m <= 0) atomicOr(a.flags, 8);
+  }
+}
+
+// Per-level table of the pure-pressure levels (DMesh.lev_tab); phs is irrelevant there (hybi == 0).
+__global__ void k_lev_tab(DMesh M, VC vc, int nlev, double* tab) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > nlev) return;
+  const double rp0 = 1.0 / vc.p0;
+  const double pl0 = ph_lev_at(M, vc, k + 1, vc.p0);
+  tab[k] = pow(pl0, vc.kappa);
+  if (k < nlev) {
+    const double pl1 = ph_lev_at(M, vc, k + 2, vc.p0);
+    const double ph = 0.5 * (pl0 + pl1);
+    tab[nlev + 1 + k] = pow(ph * rp0, vc.kappa);
+    tab[2 * (nlev + 1) + k] = log(qdiv(pl1, pl0));
   }
 }
 
@@ -522,9 +537,10 @@ __global__ void __launch_bounds__(128) k_gz_col(Geo g, DMesh M, GzArgs a) {
   for (int k = g.nlev - 1; k >= 0; --k) {
     const double pl0 = ph_lev_at(M, a.vc, k + 1, phs);
     const double ph = 0.5 * (pl0 + pl1);
-    const double t = __ldg(a.pt + c0 + k * st) * pow(ph * rp0, a.vc.kappa);
+    const bool cst = k + 2 <= M.nconst;       // both interfaces of this layer are pure-pressure levels
+    const double t = __ldg(a.pt + c0 + k * st) * (cst ? __ldg(M.lev_tab + (g.nlev + 1) + k) : pow(ph * rp0, a.vc.kappa));
     a.t[c0 + k * st] = t;
-    dgz = dgz + a.vc.Rd * t * log(qdiv(pl1, pl0));
+    dgz = dgz + a.vc.Rd * t * (cst ? __ldg(M.lev_tab + 2 * (g.nlev + 1) + k) : log(qdiv(pl1, pl0)));
     a.gz_lev[c0 + k * st] = gzs + dgz;
     pl1 = pl0;
   }

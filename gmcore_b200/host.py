@@ -28,6 +28,8 @@ def _load():
     lib = C.CDLL(path)
     lib.gmh_create.restype = C.c_void_p
     lib.gmh_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]
+    lib.gmh_create_opts.restype = C.c_void_p
+    lib.gmh_create_opts.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int]
     lib.gmh_destroy.argtypes = [C.c_void_p]
     lib.gmh_hx.argtypes = [C.c_void_p]
     lib.gmh_get_vector.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]
@@ -42,12 +44,16 @@ class Host:
     """Mesh + filters + namelist defaults for one run (single block owning the sphere)."""
 
     def __init__(self, nlon, nlat, nlev=1, dt_dyn=300.0, test_case="rossby_haurwitz_wave",
-                 time_scheme="wrfrk3", ntracers=None, **overrides):
+                 time_scheme="wrfrk3", ntracers=None, coarse_pole_mul=0.0, coarse_pole_decay=100.0,
+                 tangent_wgt_scheme="classic", **overrides):
         self.lib = _load()
         self.nlon, self.nlat, self.nlev = nlon, nlat, nlev
         self.test_case = test_case
         ptop = 2.194e2
-        self.h = self.lib.gmh_create(nlon, nlat, nlev, float(dt_dyn), ptop)
+        if tangent_wgt_scheme not in ("classic", "thuburn09"):
+            raise ValueError(f"Invalid tangent_wgt_scheme {tangent_wgt_scheme}!")
+        self.h = self.lib.gmh_create_opts(nlon, nlat, nlev, float(dt_dyn), ptop, float(coarse_pole_mul),
+                                          float(coarse_pole_decay), int(tangent_wgt_scheme == "thuburn09"))
         self.hx = self.lib.gmh_hx(self.h)
         self.hy = 2
         baroclinic = nlev > 1

@@ -22,6 +22,10 @@ enum { GMH_IC_ROSSBY_HAURWITZ = 0, GMH_IC_MOUNTAIN_ZONAL_FLOW = 1, GMH_IC_BAROCL
  * big_filter%ngrid_lat, and re-initialises the mesh with it.  nlev==1 -> SWM;
  * nlev==32 uses template 'wrf_l32', otherwise 'equal_eta'. */
 gmh_host* gmh_create(int nlon, int nlat, int nlev, double dt_dyn, double ptop);
+/* + the mesh switches of namelist_mod.F90:85-86 (coarse_pole_mul /= 0: latitude spacing stretched towards the
+ * poles, mesh_mod.F90:195-202) and tangent_wgt_scheme = 'thuburn09' (mesh_mod.F90:428-437). */
+gmh_host* gmh_create_opts(int nlon, int nlat, int nlev, double dt_dyn, double ptop,
+                          double coarse_pole_mul, double coarse_pole_decay, int tangent_wgt_thuburn09);
 void gmh_destroy(gmh_host* h);
 int gmh_hx(const gmh_host* h);
 

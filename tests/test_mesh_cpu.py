@@ -79,3 +79,31 @@ def test_vertical_coordinate():
     # wrf_l32 table entries are single-precision literals widened to r8
     assert np.array_equal(hyai, hyai.astype(np.float32).astype(np.float64))
     np.testing.assert_allclose(h.vec["half_lev"], hyai + hybi, rtol=0, atol=0)
+
+
+def test_coarse_pole_and_thuburn09_mesh():
+    """coarse_pole_mul /= 0 (mesh_mod.F90:195-202): dlat grows towards the poles, the rows still tile the sphere
+    and stay mirror-symmetric.  tangent_wgt_scheme = 'thuburn09' (mesh_mod.F90:428-437): sub-cell area ratios
+    replace the constant 1/4; on every row the two weights still sum to the classic pair's sum scaled by the
+    sub-cell split, and the oracle conserves mass on the stretched mesh."""
+    from oracle.orc import Oracle
+    nlon, nlat = 64, 33
+    h0 = Host(nlon, nlat, 8, 600.0, "baroclinic_wave")
+    h = Host(nlon, nlat, 8, 600.0, "baroclinic_wave", coarse_pole_mul=2.0, coarse_pole_decay=100.0,
+             tangent_wgt_scheme="thuburn09")
+    hy = h.hy
+    fl = h.vec["full_lat"][hy:hy + nlat]; hl = h.vec["half_lat"][hy:hy + nlat - 1]
+    d = np.diff(fl)
+    assert d[0] / d[nlat // 2] > 1.5 and np.all(d > 0)
+    assert np.allclose(fl, -fl[::-1], rtol=0, atol=1e-15) and np.allclose(hl, -hl[::-1], rtol=0, atol=1e-15)
+    a = h.vec["area_cell"][hy:hy + nlat]
+    assert abs(a.sum() * nlon / (4 * np.pi * h.cfg.radius ** 2) - 1) < 1e-14
+    ftw, ftw0 = h.vec["full_tangent_wgt"].reshape(-1, 2), h0.vec["full_tangent_wgt"].reshape(-1, 2)
+    j = slice(hy + 1, hy + nlat - 1)
+    assert np.all(np.isfinite(ftw[j])) and np.all(ftw[j] > 0) and not np.allclose(ftw[j], ftw0[j])
+    with pytest.raises(ValueError):
+        Host(nlon, nlat, 8, 600.0, "baroclinic_wave", tangent_wgt_scheme="bogus")
+    o = Oracle(h); o.set_state(h.initial_condition()); o.prepare_run()
+    dg = o.run_steps(5)
+    assert abs(dg[-1, 0] / dg[0, 0] - 1) < 1e-13
+    assert abs(dg[-1, 1] / dg[0, 1] - 1) < 1e-5
