@@ -33,6 +33,20 @@ static int hydro_alloc(gmc_handle* h) {
 // (div_damp_mod.F90:27-87) and the lon_damp latitude profile (lon_damp_mod.F90:43-68).
 static int hydro_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
   const gmc_config& c = h->cfg;
+  {  // column kernels stage whole columns in dynamic shared memory: opt in above 48 KB (deep level counts)
+    const int big = 200 * 1024;
+    if (we_col_smem(c.nlev) > (size_t)big || (size_t)c.nlev * 128 * sizeof(double) > (size_t)big) {
+      snprintf(h->err, sizeof(h->err), "num_lev %d: a column does not fit the 200 KB shared-memory staging", c.nlev); return 1;
+    }
+    cudaFuncSetAttribute(k_we_col, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+    cudaFuncSetAttribute(k_cflz, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+#define SMEM_OPT_IN(kern) cudaFuncSetAttribute(kern<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big); \
+  cudaFuncSetAttribute(kern<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big); cudaFuncSetAttribute(kern<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big); \
+  cudaFuncSetAttribute(kern<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big); cudaFuncSetAttribute(kern<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, big); \
+  cudaFuncSetAttribute(kern<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+    SMEM_OPT_IN(k_pt_col) SMEM_OPT_IN(k_tracer_v)
+#undef SMEM_OPT_IN
+  }
   {  // pure-pressure levels (hybi == 0 from the top down): per-level pow / log table, see DMesh.lev_tab
     int nconst = 0;
     while (nconst <= c.nlev && mv->hybi[nconst] == 0.0) ++nconst;
@@ -181,7 +195,7 @@ static void hydro_stage(gmc_handle* h, DState& old_, DState& star, DState& nw, d
   run_forward_prepare_x(h, star, dt);
   run_cfl(h, star.u_f, star.v_f, h->cflx, h->cfly, h->divx, h->divy, dt);
   WeArgs w{star.mfx_lon, star.mfy_lat, h->pole_dmf, star.m_lev, star.we_lev, h->dphs, h->cflz, dt, h->dflags};
-  LAUNCH(h, k_we_col, gridg(g01, 1), 128, (size_t)(g.nlev + 1) * 128 * sizeof(double), g01, h->M, w);
+  LAUNCH(h, k_we_col, gridg(g01, 1, WE_TX), dim3(WE_TX, WE_TY), we_col_smem(g.nlev), g01, h->M, w);
   TendArgs t{};
   t.mfx_lon = star.mfx_lon; t.mfy_lat = star.mfy_lat; t.pv_lon = star.pv_lon; t.pv_lat = star.pv_lat; t.ke = star.ke;
   t.we_lev = star.we_lev; t.u_f = star.u_f; t.v_f = star.v_f; t.m = star.m; t.du = h->du; t.dv = h->dv;
@@ -289,7 +303,7 @@ static void hydro_accum_wind(gmc_handle* h, int itime) {
   accum_pair(h, g, h->bwe, S.we_lev, g.nlev + 1, h->bm_lev, S.m_lev, g.nlev + 1, mode);
   if (h->we_step == 0) {
     CflzArgs c{h->bwe, h->bm_lev, h->bcflz, h->cfg.dt_adv, h->dflags};
-    LAUNCH(h, k_cflz, gridg(g, 1), 128, (size_t)(g.nlev + 1) * 128 * sizeof(double), g, h->M, c);
+    LAUNCH(h, k_cflz, gridg(g, 1, WE_TX), dim3(WE_TX, WE_TY), cflz_smem(g.nlev), g, h->M, c);
   }
 }
 

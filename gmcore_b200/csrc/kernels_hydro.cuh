@@ -216,74 +216,104 @@ __device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const
   return false;
 }
 
-__global__ void __launch_bounds__(128) k_we_col(Geo g, DMesh M, WeArgs a) {
-  extern __shared__ double wm_s[];       // [nlev+1][blockDim.x]
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// Column kernels with a serial part (running sums in k) and a parallel part (one RK4 departure search per
+// half level): a block is WE_TX columns x WE_TY level groups, so the loads, the eta-velocity divides and the
+// RK4 searches of one column are spread over WE_TY threads (levels interleaved, a warp = 32 adjacent columns
+// at one level -> coalesced), and only the two running sums are walked by one thread per column, in the
+// reference's k order.  4x the threads in flight of the one-thread-per-column version for the same shared memory.
+#ifndef WE_TX
+#define WE_TX 32
+#endif
+#ifndef WE_TY
+#define WE_TY 8
+#endif
+static inline size_t we_col_smem(int nlev) { return (size_t)((nlev + 1) + 2 * nlev + 1) * WE_TX * sizeof(double); }
+static inline size_t cflz_smem(int nlev) { return (size_t)(nlev + 1) * WE_TX * sizeof(double); }
+__global__ void __launch_bounds__(WE_TX * WE_TY) k_we_col(Geo g, DMesh M, WeArgs a) {
+  extern __shared__ double wm_s[];       // wm[nlev+1][TX] | dlon[nlev][TX] | dlat[nlev][TX] | dphs[TX]
+  const int tx = threadIdx.x, ty = threadIdx.y, nlev = g.nlev;
+  const int i = blockIdx.x * WE_TX + tx;
   const int j = g.jb + blockIdx.y;
-  if (i >= g.nlon) return;
+  const bool act = i < g.nlon;
   const bool pole = (j == 1 || j == g.nlat);
-  const int st = (int)g.plane, B = blockDim.x, n = g.nlon;
-  const int c0 = gidx(g, i, j, 0), im = wrapi(i - 1, n) - i;
+  const int st = (int)g.plane, n = g.nlon;
+  const int c0 = act ? gidx(g, i, j, 0) : 0, im = act ? wrapi(i - 1, n) - i : 0;
   const RowCoef* __restrict__ R = M.rows + (j + 1);
   const double rac = R->r_area_cell, lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
-  double* wm = wm_s + threadIdx.x;
-  double dphs = 0, mf = 0;
-  // calc_grad_mf + calc_dphsdt: running sums in the reference's k order; prefix parked in shared memory
-#ifndef WECOL_PF
-#define WECOL_PF 4
-#endif
-  const bool pfl = (i & 15) == 0;      // one prefetch per 128-byte line
+  double* wm = wm_s + tx;
+  double* dl = wm_s + (nlev + 1) * WE_TX + tx;
+  double* da = dl + nlev * WE_TX;
+  double* dps = wm_s + ((nlev + 1) + 2 * nlev) * WE_TX;
+  // calc_grad_mf (operators_mod.F90:1114-1166): the two divergence parts of every level
+  if (act) {
 #pragma unroll 4
-  for (int k = 0; k < g.nlev; ++k) {
-    double dlon, dlat;
-    if (WECOL_PF && pfl) {
-      pf_l2(a.m_lev + c0 + (k + 1) * st);
-      if (k + WECOL_PF < g.nlev) { pf_l2(a.mfx_lon + c0 + (k + WECOL_PF) * st); pf_l2(a.mfy_lat + c0 + (k + WECOL_PF) * st); }
+    for (int k = ty; k < nlev; k += WE_TY) {
+      double dlon, dlat;
+      if (pole) { dlon = 0.0; dlat = __ldg(a.pole_dmf + (j == 1 ? 0 : nlev) + k); }
+      else {
+        const double* fx = a.mfx_lon + c0 + k * st; const double* fy = a.mfy_lat + c0 + k * st;
+        dlon = (__ldg(fx) - __ldg(fx + im)) * lel * rac;
+        dlat = (__ldg(fy) * lea - __ldg(fy - n) * leas) * rac;
+      }
+      dl[k * WE_TX] = dlon; da[k * WE_TX] = dlat;
     }
-    if (pole) { dlon = 0.0; dlat = __ldg(a.pole_dmf + (j == 1 ? 0 : g.nlev) + k); }
-    else {
-      const double* fx = a.mfx_lon + c0 + k * st; const double* fy = a.mfy_lat + c0 + k * st;
-      dlon = (__ldg(fx) - __ldg(fx + im)) * lel * rac;
-      dlat = (__ldg(fy) * lea - __ldg(fy - n) * leas) * rac;
-    }
-    dphs = dphs - dlon - dlat;
-    mf = mf + dlon + dlat;
-    wm[(k + 1) * B] = mf;
   }
-  a.dphs[c0] = dphs;
+  __syncthreads();
+  // calc_dphsdt + the column prefix of calc_we_lev: running sums in the reference's k order
+  if (act && ty == 0) {
+    double dphs = 0, mf = 0;
+    for (int k = 0; k < nlev; ++k) {
+      const double dlon = dl[k * WE_TX], dlat = da[k * WE_TX];
+      dphs = dphs - dlon - dlat;
+      mf = mf + dlon + dlat;
+      wm[(k + 1) * WE_TX] = mf;
+    }
+    a.dphs[c0] = dphs; dps[tx] = dphs;
+  }
+  __syncthreads();
   // calc_we_lev, and the eta velocity of accum_we_lev
-  double* we = a.we_lev + c0;
-  const double* ml = a.m_lev + c0;
-  const double* hd = M.half_dlev - 1;
-  we[0] = 0.0; wm[0] = 0.0;
-  for (int k1 = 2; k1 <= g.nlev; ++k1) {
-    const double w = -(M.hybi[k1 - 1] * dphs) - wm[(k1 - 1) * B];
-    we[(k1 - 1) * st] = w;
-    wm[(k1 - 1) * B] = qdiv(w, __ldg(ml + (k1 - 1) * st)) * hd[k1];
+  if (act) {
+    const double dphs = dps[tx];
+    double* we = a.we_lev + c0;
+    const double* ml = a.m_lev + c0;
+    const double* hd = M.half_dlev - 1;
+    for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
+      const double w = -(M.hybi[k1 - 1] * dphs) - wm[(k1 - 1) * WE_TX];
+      we[(k1 - 1) * st] = w;
+      wm[(k1 - 1) * WE_TX] = qdiv(w, __ldg(ml + (k1 - 1) * st)) * hd[k1];
+    }
+    if (ty == 0) { we[0] = 0.0; wm[0] = 0.0; }
+    if (ty == 1) { we[nlev * st] = 0.0; wm[nlev * WE_TX] = 0.0; }
   }
-  we[g.nlev * st] = 0.0; wm[g.nlev * B] = 0.0;
-  for (int k1 = 2; k1 <= g.nlev; ++k1) {
-    double cz;
-    if (cflz_one(M, g.nlev, k1, wm, B, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+  __syncthreads();
+  if (act) {
+    for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
+      double cz;
+      if (cflz_one(M, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+    }
   }
 }
 
 // cflz for a tracer batch from its accumulated we / m_lev (adv_batch_mod.F90:526-627)
 struct CflzArgs { const double *we, *m_lev; double* cflz; double dt; int* flags; };
-__global__ void __launch_bounds__(128) k_cflz(Geo g, DMesh M, CflzArgs a) {
+__global__ void __launch_bounds__(WE_TX * WE_TY) k_cflz(Geo g, DMesh M, CflzArgs a) {
   extern __shared__ double wm_s[];
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int tx = threadIdx.x, ty = threadIdx.y, nlev = g.nlev;
+  const int i = blockIdx.x * WE_TX + tx;
   const int j = g.jb + blockIdx.y;
-  if (i >= g.nlon) return;
-  const int st = (int)g.plane, B = blockDim.x, c0 = gidx(g, i, j, 0);
-  double* wm = wm_s + threadIdx.x;
+  const bool act = i < g.nlon;
+  const int st = (int)g.plane, c0 = act ? gidx(g, i, j, 0) : 0;
+  double* wm = wm_s + tx;
   const double* hd = M.half_dlev - 1;
-  for (int k1 = 1; k1 <= g.nlev + 1; ++k1)
-    wm[(k1 - 1) * B] = qdiv(__ldg(a.we + c0 + (k1 - 1) * st), __ldg(a.m_lev + c0 + (k1 - 1) * st)) * hd[k1];
-  for (int k1 = 2; k1 <= g.nlev; ++k1) {
-    double cz;
-    if (cflz_one(M, g.nlev, k1, wm, B, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
-  }
+  if (act)
+    for (int k1 = 1 + ty; k1 <= nlev + 1; k1 += WE_TY)
+      wm[(k1 - 1) * WE_TX] = qdiv(__ldg(a.we + c0 + (k1 - 1) * st), __ldg(a.m_lev + c0 + (k1 - 1) * st)) * hd[k1];
+  __syncthreads();
+  if (act)
+    for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
+      double cz;
+      if (cflz_one(M, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+    }
 }
 
 // ---- FFSL horizontal PPM flux (hflx_ppm_cell, ffsl_mod.F90:778-881) ----------------
