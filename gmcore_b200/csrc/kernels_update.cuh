@@ -51,13 +51,30 @@ template <class Store> __device__ __forceinline__ void conv_row(const double* __
 // shared memory: [row: nlon+2*mh][row2: nlon+2*mh][w1: 2*mh+1][w2: 2*mh+1], mh = a.mh (largest half-width of any filter)
 __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   extern __shared__ double srow[];
-  const int j = (a.half_lat ? g.hjb : g.jb) + blockIdx.x, k = blockIdx.y;
+  // grid = (level, row rank): rows are issued from the two ends of the band inwards, i.e. widest filters (most
+  // taps, longest blocks) first and all levels of a row together, so the launch does not end on a polar tail
+  const int rr = blockIdx.y, nr = gridDim.y, k = blockIdx.x;
+  const int j = (a.half_lat ? g.hjb : g.jb) + ((rr & 1) ? nr - 1 - (rr >> 1) : (rr >> 1));
   if (a.half_lat ? (j > g.hje) : (j > g.je)) return;
   const int n1 = a.use_f1 ? (a.half_lat ? a.f1.ngrid_lat[j + 1] : a.f1.ngrid_lon[j + 1]) : 0;
   const int n2 = a.use_f2 ? (a.half_lat ? a.f2.ngrid_lat[j + 1] : a.f2.ngrid_lon[j + 1]) : 0;
   const int hn1 = n1 > 1 ? (n1 - 1) / 2 : 0, hn2 = n2 > 1 ? (n2 - 1) / 2 : 0;
-  const int hn = a.chain ? hn2 : (hn1 > hn2 ? hn1 : hn2);
+  // chain rows the first filter leaves alone (most rows: small_filter2 is polar only) stage the raw row once,
+  // with the second filter's halo, and skip the intermediate row
+  const bool chain1 = a.chain && n2 <= 1 && j != a.skip_a && j != a.skip_b;
+  const int hn = a.chain ? (chain1 ? hn1 : hn2) : (hn1 > hn2 ? hn1 : hn2);
   const int nlon = g.nlon, rs = nlon + 2 * a.mh;
+  if (!a.chain && n1 <= 1 && n2 <= 1) {      // unfiltered row (block-uniform): straight from global memory
+    const int base = gidx(g, 0, j, k);
+    for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
+      double s = __ldg(a.in + base + i);
+      if (a.out1) a.out1[base + i] = s;
+      if (a.post == POST_DIV_M) s = s / __ldg(a.mdiv + base + i);
+      if (a.out2) a.out2[base + i] = s;
+      if (a.post == POST_SWM_M) a.out_m[base + i] = (s - __ldg(a.gzs + gidx(g, i, j, 0))) / a.grav;
+    }
+    return;
+  }
   double* __restrict__ srow2 = srow + rs;
   double* __restrict__ ws1 = srow + 2 * rs; double* __restrict__ ws2 = ws1 + (2 * a.mh + 1);
   const double* __restrict__ row = a.in + gidx(g, 0, j, k);
@@ -71,6 +88,11 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   for (int t = threadIdx.x; t < n2; t += blockDim.x) ws2[t] = __ldg(w2 + t);
   __syncthreads();
   const int base = gidx(g, 0, j, k);
+  if (chain1) {
+    if (a.out2 != a.in) for (int i = threadIdx.x; i < nlon; i += blockDim.x) a.out2[base + i] = srow[i + hn];
+    conv_row(srow, hn, ws1, n1, nlon, [&](int i, double s) { a.out1[base + i] = s; });
+    return;
+  }
   if (a.chain) {
     conv_row(srow, hn, ws2, n2, nlon, [&](int i, double s) { a.out2[base + i] = s; srow2[i + hn1] = s; });
     __syncthreads();

@@ -35,7 +35,7 @@ static void run_filter(gmc_handle* h, const double* in, int half_lat, int nlev, 
   a.post = post; a.gzs = h->gzs; a.grav = h->cfg.g; a.mdiv = mdiv; a.out_m = out_m;
   a.chain = 0; a.row2_off = 0; a.skip_a = a.skip_b = -1000; a.mh = h->max_hn;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
-  LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
+  LAUNCH(h, k_filter_rows, dim3(nlev, nrows), 256, filt_smem(h), g, a);
 }
 
 // out2 = f2(in), out1 = f1(out2) in one launch (one read of the raw row instead of two passes)
@@ -50,7 +50,7 @@ static void run_filter_chain(gmc_handle* h, const double* in, int half_lat, int 
   a.chain = 1; a.row2_off = g.nlon + 2 * h->max_hn; a.skip_a = skip_a; a.skip_b = skip_b; a.mh = h->max_hn;
   const int nrows = half_lat ? (g.hje - g.hjb + 1) : (g.je - g.jb + 1);
   if (nrows <= 0) return;
-  LAUNCH(h, k_filter_rows, dim3(nrows, nlev), 256, filt_smem(h), g, a);
+  LAUNCH(h, k_filter_rows, dim3(nlev, nrows), 256, filt_smem(h), g, a);
 }
 
 #include "hydro.cuh"
