@@ -17,7 +17,7 @@ static int launch_diag(gmc_handle* h, int itime, double* dev_out) {
              h->diag_partial, h->cfg.g, h->cfg.cpd, h->cfg.baroclinic};
   const int nrows = g.je - g.jb + 1;
   LAUNCH(h, k_diag_partial, dim3(nrows, g.nlev), 256, 0, g, h->M, a);
-  LAUNCH(h, k_diag_final, 1, 1024, 0, h->diag_partial, nrows * g.nlev, dev_out);
+  LAUNCH(h, k_diag_final, 7, 1024, 0, h->diag_partial, nrows * g.nlev, dev_out);
   return 0;
 }
 // device sums (tm, te_ke, te_ie, te_pe, tav, tpe, tpt) -> ABI order

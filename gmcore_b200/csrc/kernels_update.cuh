@@ -231,7 +231,7 @@ struct DiagArgs {
   double grav, cpd; int baroclinic;
 };
 __global__ void __launch_bounds__(256) k_diag_partial(Geo g, DMesh M, DiagArgs a) {
-  __shared__ double sm[32];
+  __shared__ double sm7[7][32];
   const int j = g.jb + blockIdx.x, k = blockIdx.y;
   const int nrows = g.je - g.jb + 1;
   double tm = 0, ke = 0, ie = 0, pe = 0, av = 0, tpe = 0, tpt = 0;
@@ -260,20 +260,30 @@ __global__ void __launch_bounds__(256) k_diag_partial(Geo g, DMesh M, DiagArgs a
     }
   }
   const int slot = blockIdx.y * nrows + blockIdx.x, ns = nrows * g.nlev;
+  // seven block sums with the summation tree of block_sum (warp shuffles, then one warp per diagnostic folds the
+  // per-warp values) behind one barrier instead of 21
   double v[7] = {tm, ke, ie, pe, av, tpe, tpt};
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
   for (int q = 0; q < 7; ++q) {
-    const double s = block_sum(v[q], sm);
-    if (threadIdx.x == 0) a.partial[(size_t)q * ns + slot] = s;
+    double x = v[q];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0) sm7[q][w] = x;
+  }
+  __syncthreads();
+  if (w < 7) {
+    double r = lane < nw ? sm7[w][lane] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_down_sync(0xffffffffu, r, o);
+    if (lane == 0) a.partial[(size_t)w * ns + slot] = r;
   }
 }
 __global__ void __launch_bounds__(1024) k_diag_final(const double* partial, int ns, double* out /*[7]*/) {
   __shared__ double sm[32];
-  for (int q = 0; q < 7; ++q) {
-    double s = 0;
-    for (int x = threadIdx.x; x < ns; x += blockDim.x) s += partial[(size_t)q * ns + x];
-    s = block_sum(s, sm);
-    if (threadIdx.x == 0) out[q] = s;
-  }
+  const int q = blockIdx.x;            // one block per diagnostic; the summation order within one is fixed
+  double s = 0;
+  for (int x = threadIdx.x; x < ns; x += blockDim.x) s += partial[(size_t)q * ns + x];
+  s = block_sum(s, sm);
+  if (threadIdx.x == 0) out[q] = s;
 }
 
 // ---- host (halo'd Fortran storage) <-> device (compact) layout conversion --------------

@@ -185,11 +185,19 @@ class GmcoreGPU:
         return self.lib.gmc_stream(self.h)
 
     # read-back --------------------------------------------------------------------------
-    def download_state(self, itime=None):
+    def download_state(self, itime=None, out=None):
+        """out: optional dict of preallocated halo'd host arrays (u_lon, v_lat, pt_or_gz, phs) -- e.g. the host
+        model's own page-locked state arrays -- written in place instead of fresh pageable ones."""
         itime = self.old.value if itime is None else itime
         hst = self.host
-        u = np.zeros(hst.shape("lon")); v = np.zeros(hst.shape("lat")); s = np.zeros(hst.shape("cell"))
-        phs = np.zeros(hst.shape("2d")) if hst.nlev > 1 else None
+        if out is not None:
+            u, v, s, phs = out["u_lon"], out["v_lat"], out["pt_or_gz"], out.get("phs")
+            for a, loc in ((u, "lon"), (v, "lat"), (s, "cell")) + (((phs, "2d"),) if phs is not None else ()):
+                if a.shape != tuple(hst.shape(loc)) or a.dtype != np.float64 or not a.flags.c_contiguous:
+                    raise ValueError(f"download_state: out array for '{loc}' must be C-contiguous float64 of shape {tuple(hst.shape(loc))}")
+        else:
+            u = np.zeros(hst.shape("lon")); v = np.zeros(hst.shape("lat")); s = np.zeros(hst.shape("cell"))
+            phs = np.zeros(hst.shape("2d")) if hst.nlev > 1 else None
         self._chk(self.lib.gmc_download_state(self.h, itime, abi.dptr(u), abi.dptr(v), abi.dptr(s), abi.dptr(phs)))
         return {"u_lon": u, "v_lat": v, "pt_or_gz": s, "phs": phs}
 
@@ -301,10 +309,16 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
         return q
 
-    def download_state(self, itime=None):
+    def download_state(self, itime=None, out=None):
         itime = self.old.value if itime is None else itime
-        u = np.zeros(self.band_shape("lon")); v = np.zeros(self.band_shape("lat")); s = np.zeros(self.band_shape("cell"))
-        phs = np.zeros(self.band_shape("2d"))
+        if out is not None:
+            u, v, s, phs = out["u_lon"], out["v_lat"], out["pt_or_gz"], out["phs"]
+            for a, loc in ((u, "lon"), (v, "lat"), (s, "cell"), (phs, "2d")):
+                if a.shape != tuple(self.band_shape(loc)) or a.dtype != np.float64 or not a.flags.c_contiguous:
+                    raise ValueError(f"download_state: out array for '{loc}' must be C-contiguous float64 of shape {tuple(self.band_shape(loc))}")
+        else:
+            u = np.zeros(self.band_shape("lon")); v = np.zeros(self.band_shape("lat")); s = np.zeros(self.band_shape("cell"))
+            phs = np.zeros(self.band_shape("2d"))
         self._chk(self.lib.gmc_download_state(self.h, itime, abi.dptr(u), abi.dptr(v), abi.dptr(s), abi.dptr(phs)))
         return {"u_lon": u, "v_lat": v, "pt_or_gz": s, "phs": phs}
 

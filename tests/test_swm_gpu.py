@@ -81,6 +81,13 @@ def test_upload_download_roundtrip(gpu_required):
     assert np.array_equal(host.interior(st["u_lon"], "lon"), host.interior(ic["u_lon"], "lon"))
     assert np.array_equal(host.interior(st["v_lat"], "lat"), host.interior(ic["v_lat"], "lat"))
     assert np.array_equal(host.interior(st["pt_or_gz"], "cell"), host.interior(ic["pt_or_gz"], "cell"))
+    # in-place download into caller-owned arrays (the host model's state arrays): same image, stale contents overwritten
+    out = {k: np.full_like(v, 7.0) for k, v in st.items() if v is not None}
+    st2 = gpu.download_state(1, out=out)
+    for k in out:
+        assert st2[k] is out[k] and np.array_equal(out[k], st[k]), k
+    with pytest.raises(ValueError):
+        gpu.download_state(1, out={"u_lon": out["u_lon"][:, :, :-1], "v_lat": out["v_lat"], "pt_or_gz": out["pt_or_gz"]})
 
 
 @pytest.mark.parametrize("nlev", [1, 8])
