@@ -322,6 +322,17 @@ int gmc_synchronize(gmc_handle* h) {
   CUDA_CHECK(cudaGetLastError());
   return 0;
 }
+int gmc_pin_host(gmc_handle* h, void* ptr, size_t bytes) {
+  if (!ptr || !bytes) { snprintf(h->err, sizeof(h->err), "gmc_pin_host: empty range"); return 1; }
+  const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) { cudaGetLastError(); snprintf(h->err, sizeof(h->err), "gmc_pin_host: %s", cudaGetErrorString(e)); return 1; }
+  return 0;
+}
+int gmc_unpin_host(gmc_handle* h, void* ptr) {
+  const cudaError_t e = cudaHostUnregister(ptr);   // a failure here must not poison later cudaGetLastError checks
+  if (e != cudaSuccess) { cudaGetLastError(); snprintf(h->err, sizeof(h->err), "gmc_unpin_host: %s", cudaGetErrorString(e)); return 1; }
+  return 0;
+}
 int gmc_launch_count(gmc_handle* h, long long* launches) { *launches = h->launches; return 0; }
 // Timing helpers (CUDA events on the handle's stream; torch.cuda.Event only sees
 // torch's current stream).  slot 0 = start, 1 = stop.

@@ -19,7 +19,7 @@ ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
                "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_step",
-               "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init"]
+               "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host"]
 
 
 def load_library():
@@ -60,6 +60,8 @@ def load_library():
     lib.gmc_profile.argtypes = [V, C.c_int]
     lib.gmc_profile_report.argtypes = [V, C.c_char_p, C.c_int]
     lib.gmc_reset_clock.argtypes = [V]
+    lib.gmc_pin_host.argtypes = [V, C.c_void_p, C.c_size_t]
+    lib.gmc_unpin_host.argtypes = [V, C.c_void_p]
     lib.gmc_adv_prescribe.argtypes = [V, C.c_int, P, P]
     lib.gmc_adv_step.argtypes = [V, C.c_int, C.c_int]
     lib.gmc_stream.restype = C.c_void_p
@@ -185,6 +187,13 @@ class GmcoreGPU:
         return self.lib.gmc_stream(self.h)
 
     # read-back --------------------------------------------------------------------------
+    def pin_host(self, a):
+        """Page-lock a host array used for repeated uploads / downloads (gmc_pin_host)."""
+        self._chk(self.lib.gmc_pin_host(self.h, a.ctypes.data, a.nbytes))
+
+    def unpin_host(self, a):
+        self._chk(self.lib.gmc_unpin_host(self.h, a.ctypes.data))
+
     def download_state(self, itime=None, out=None):
         """out: optional dict of preallocated halo'd host arrays (u_lon, v_lat, pt_or_gz, phs) -- e.g. the host
         model's own page-locked state arrays -- written in place instead of fresh pageable ones."""

@@ -17,6 +17,7 @@
 #ifndef GMCORE_GPU_H
 #define GMCORE_GPU_H
 
+#include <stddef.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -150,6 +151,12 @@ int gmc_adv_step(gmc_handle* h, int itime, int time_step);
 int gmc_reset_clock(gmc_handle* h);
 
 int gmc_synchronize(gmc_handle* h);
+
+/* Page-lock (cudaHostRegister) / release a host array that is uploaded or downloaded repeatedly -- the arrays of
+ * state_type allocated once in state_mod.F90:103-199.  Optional: pageable arrays work, at a fraction of the PCIe
+ * rate (the transfers of gmc_upload_state / gmc_download_state then go through the driver's bounce buffer). */
+int gmc_pin_host(gmc_handle* h, void* ptr, size_t bytes);
+int gmc_unpin_host(gmc_handle* h, void* ptr);
 /* Device milliseconds spent in, and kernels launched by, calls on this handle
  * since the last reset (CUDA events on the handle's stream). */
 int gmc_launch_count(gmc_handle* h, long long* launches);

@@ -86,6 +86,14 @@ def test_upload_download_roundtrip(gpu_required):
     st2 = gpu.download_state(1, out=out)
     for k in out:
         assert st2[k] is out[k] and np.array_equal(out[k], st[k]), k
+    # the same through page-locked arrays (gmc_pin_host / gmc_unpin_host)
+    for k in out:
+        out[k][...] = -3.0; gpu.pin_host(out[k])
+    gpu.download_state(1, out=out)
+    for k in out:
+        gpu.unpin_host(out[k]); assert np.array_equal(out[k], st[k]), k
+    with pytest.raises(RuntimeError):
+        gpu.unpin_host(out["u_lon"])          # not registered any more: the CUDA error text comes back through the ABI
     with pytest.raises(ValueError):
         gpu.download_state(1, out={"u_lon": out["u_lon"][:, :, :-1], "v_lat": out["v_lat"], "pt_or_gz": out["pt_or_gz"]})
 

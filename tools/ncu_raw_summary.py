@@ -10,10 +10,13 @@ def scaled(r, k, to):
     v = g(r, k); u = units[ix[k]]
     f = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9, 'ns': 1e-9, 'us': 1e-6, 'ms': 1e-3, 's': 1}.get(u, 1)
     return v * f / to
+def kname(s):          # "void k_hflx<1>(Geo, HflxArgs)" -> "k_hflx" (the name gmc_profile reports)
+    s = s.split('(')[0].split('<')[0]
+    return s[5:] if s.startswith('void ') else s
 seen = set()
 print(f"{'kernel':16s} {'grid':>14s} {'ms':>7s} {'rdGB':>6s} {'wrGB':>6s} {'GB/s':>6s} {'sm%':>5s} {'l1%':>5s} {'l2%':>5s} {'fp64%':>5s} {'alu%':>5s} {'lsu%':>5s} {'occ%':>5s} {'regs':>4s} {'inst/pt':>7s} {'ipc':>5s}")
 for r in data:
-    name = r[ix['Kernel Name']].split('(')[0]
+    name = kname(r[ix['Kernel Name']])
     key = (name, r[ix['Grid Size']])
     if key in seen: continue
     seen.add(key)
@@ -34,7 +37,7 @@ if "--json" in sys.argv:
     out = {"workload": sys.argv[sys.argv.index("--json") + 1], "source": "ncu --set full --clock-control none, one launch per kernel (mean over the captured launches)", "kernels": {}}
     acc = {}
     for r in data:
-        name = r[ix['Kernel Name']].split('(')[0]
+        name = kname(r[ix['Kernel Name']])
         b = scaled(r, 'dram__bytes_read.sum', 1) + scaled(r, 'dram__bytes_write.sum', 1)
         t = scaled(r, 'gpu__time_duration.sum', 1e-3)
         acc.setdefault(name, []).append((b, t))
