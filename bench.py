@@ -284,7 +284,8 @@ def _main(out):
     clocks.wait_first()
 
     n3 = wl["nlon"] * wl["nlat"] * wl["nlev"]
-    n3_k = n3 // world if banded else n3          # cells one GPU's kernels process
+    # cells this rank's kernels process (its own rows; the redundant halo rows are not counted)
+    n3_k = wl["nlon"] * (gpu.cfg.lat_iend - gpu.cfg.lat_ibeg + 1) * wl["nlev"] if banded else n3
     working_set = 40 * n3_k * 8
     flush = working_set < 2 * L2_BYTES
     flush_buf = torch.empty(int(2 * L2_BYTES) // 8, dtype=torch.float64, device=f"cuda:{local}") if flush else None
@@ -360,6 +361,11 @@ def _main(out):
            "region": "upload_state(pinned)+prepare_run+K*(time_integrate+diagnose D2H)+download_state"}
     gpu2.close()
 
+    if banded:
+        from gmcore_b200.model import balanced_rows, round_robin
+        band_rows = os.environ.get("GMCORE_BAND_ROWS", "balanced")
+        parts = balanced_rows(host, world) if band_rows == "balanced" else round_robin(host.nlat, world)
+        band_sizes = "/".join(str(e - b + 1) for b, e in parts)
     if rank == 0:
         cb = None
         if not args.no_cpu_baseline:
@@ -372,7 +378,7 @@ def _main(out):
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
                 "scaling": "strong" if banded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")},
-                           "time_scheme": "wrfrk3", "hx": host.hx, "parallelism": (f"{world} latitude bands, NCCL halo exchange" if banded else f"replicas x{world}") if world > 1 else "1 GPU",
+                           "time_scheme": "wrfrk3", "hx": host.hx, "parallelism": (f"{world} latitude bands ({band_rows} rows: {band_sizes}), NCCL halo exchange" if banded else f"replicas x{world}") if world > 1 else "1 GPU",
                            "l2": "flushed between timed steps (256 MB write)" if flush else "working set >> L2 (no flush)"},
                 "gpu_launches": launches, "clocks": clk, "e2e": e2e, "roofline": roofline, "cpu_baseline": cb}
         print(json.dumps(line), file=out, flush=True)

@@ -240,9 +240,59 @@ def round_robin(n, nparts):
     return out
 
 
-def band_config(host, rank, nranks, device):
+# Cost model of one latitude row for the balanced split: 1 (everything uniform in latitude) + ROW_TAP_COST per zonal
+# filter tap above the equatorial count (big_filter on u, v; small_filter2 on u, v; small_filter1 on pt) + POLE_ROW_COST
+# for a pole row (zonal sums, k_pole1 / k_pole_sum launches).  Calibrated on the 8-band 0.25 deg x L32 run: the two
+# polar bands spent 0.36 ms more in k_filter_rows and 0.17 ms in pole kernels than the 0.034 ms per row of an
+# interior band (profiles/r01_bench_bw_1440x720x32_8gpu_v5.json vs the balanced run).
+ROW_TAP_COST = 0.00486
+POLE_ROW_COST = 5.0
+BOUNDARY_COST = 4.0      # row-equivalents of redundant halo-row compute per interior band boundary (6 rows, not every kernel)
+
+
+def row_weights(host):
+    big_l, _, _, big_a, _, _ = host.filters[0]
+    s1_l = host.filters[1][0]
+    s2_l, _, _, s2_a, _, _ = host.filters[2]
+    hy = host.hy
+    T = np.zeros(host.nlat)
+    for j in range(1, host.nlat + 1):
+        t = int(big_l[j - 1 + hy]) + int(s1_l[j - 1 + hy]) + int(s2_l[j - 1 + hy])
+        if j <= host.nlat - 1:
+            t += int(big_a[j - 1 + hy]) + int(s2_a[j - 1 + hy])
+        T[j - 1] = t
+    w = 1.0 + ROW_TAP_COST * np.maximum(T - np.median(T), 0.0)
+    w[0] += POLE_ROW_COST; w[-1] += POLE_ROW_COST
+    return w
+
+
+def balanced_rows(host, nparts, min_rows=6):
+    """Contiguous latitude bands of equal modelled cost (the polar bands get fewer rows: their rows carry the wide
+    zonal filters).  The reference's rule is round_robin (equal row counts); the band boundaries are the host's
+    choice -- gmc_create takes lat_ibeg / lat_iend -- and results do not depend on them (tools/band_check.py).
+    Returns [(ibeg, iend)] 1-based inclusive."""
+    n = host.nlat
+    if nparts == 1:
+        return [(1, n)]
+    cw = np.concatenate([[0.0], np.cumsum(row_weights(host))])
+    target = (cw[-1] + BOUNDARY_COST * 2 * (nparts - 1)) / nparts
+    cuts = [0]
+    for k in range(1, nparts):
+        want = k * target - BOUNDARY_COST * (2 * k - 1)          # rows of bands 0..k-1 (which have 2k-1 boundaries)
+        j = int(np.searchsorted(cw, want))                       # first prefix >= want
+        if j > 0 and want - cw[j - 1] < cw[j] - want:
+            j -= 1                                               # nearest prefix
+        j = max(j, cuts[-1] + min_rows)
+        j = min(j, n - min_rows * (nparts - k))
+        cuts.append(j)
+    cuts.append(n)
+    return [(cuts[k] + 1, cuts[k + 1]) for k in range(nparts)]
+
+
+def band_config(host, rank, nranks, device, rows="round_robin"):
     cfg = abi.GmcConfig.from_buffer_copy(host.cfg)
-    cfg.lat_ibeg, cfg.lat_iend = round_robin(host.nlat, nranks)[rank]
+    parts = balanced_rows(host, nranks) if rows == "balanced" else round_robin(host.nlat, nranks)
+    cfg.lat_ibeg, cfg.lat_iend = parts[rank]
     cfg.rank, cfg.nranks, cfg.device = rank, nranks, device
     return cfg
 
@@ -259,10 +309,10 @@ def band_slice(host, cfg, a, loc):
 class GmcoreBand(GmcoreGPU):
     """One latitude band = one handle (what one MPI rank of GMCORE owns)."""
 
-    def __init__(self, host, rank, nranks, device=0):
+    def __init__(self, host, rank, nranks, device=0, rows="round_robin"):
         self.lib = load_library()
         self.host = host
-        self.cfg = band_config(host, rank, nranks, device)
+        self.cfg = band_config(host, rank, nranks, device, rows)
         self.h = C.c_void_p()
         rc = self.lib.gmc_create(C.byref(self.cfg), C.byref(self.h))
         if rc != 0:
@@ -342,11 +392,13 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_nccl_init(self.h, uid))
 
 
-def make_band_nccl(host, rank, world, device):
-    """torch.distributed-launched rank -> its latitude band with the NCCL transport set up."""
+def make_band_nccl(host, rank, world, device, rows=None):
+    """torch.distributed-launched rank -> its latitude band with the NCCL transport set up.
+    rows: "balanced" (default; GMCORE_BAND_ROWS overrides) or "round_robin" (the reference's equal row counts)."""
     import torch
     import torch.distributed as dist
-    band = GmcoreBand(host, rank, world, device)
+    rows = rows or os.environ.get("GMCORE_BAND_ROWS", "balanced")
+    band = GmcoreBand(host, rank, world, device, rows)
     t = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{device}")
     if rank == 0:
         t = torch.frombuffer(bytearray(band.nccl_unique_id()), dtype=torch.uint8).to(f"cuda:{device}")
@@ -371,9 +423,9 @@ class GmcoreBandGroup:
     """All latitude bands in ONE process on ONE device (gmc_group_link): the single-GPU stand-in for
     the N-rank run, used to check that results do not depend on the band count."""
 
-    def __init__(self, host, nbands, device=0):
+    def __init__(self, host, nbands, device=0, rows="round_robin"):
         self.host = host
-        self.bands = [GmcoreBand(host, r, nbands, device) for r in range(nbands)]
+        self.bands = [GmcoreBand(host, r, nbands, device, rows) for r in range(nbands)]
         self.lib = self.bands[0].lib
         arr = (C.c_void_p * nbands)(*[b.h for b in self.bands])
         if self.lib.gmc_group_link(arr, nbands) != 0:

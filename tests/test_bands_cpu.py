@@ -24,6 +24,28 @@ def test_round_robin_matches_reference_rule():
         assert all(parts[r + 1][0] == parts[r][1] + 1 for r in range(p - 1))
 
 
+def test_balanced_rows_cover_the_sphere_and_relieve_the_polar_bands():
+    from gmcore_b200.model import balanced_rows, row_weights
+    for (nlon, nlat, nlev, dt), ps in (((1440, 720, 32, 30.0), (1, 2, 4, 8)), ((120, 61, 8, 300.0), (2, 3, 5, 8)), ((48, 25, 4, 600.0), (2, 3, 4))):
+        host = Host(nlon, nlat, nlev, dt, "baroclinic_wave")
+        w = row_weights(host)
+        # half row j is owned with full row j, so the two hemispheres mirror each other up to that one-row shift
+        assert w.shape == (nlat,) and w.min() >= 1.0 and abs(w[:nlat // 2].sum() / w[(nlat + 1) // 2:].sum() - 1) < 0.02
+        assert w[1] > w[nlat // 2]                                                    # polar rows carry the wide filters
+        for p in ps:
+            parts = balanced_rows(host, p)
+            assert len(parts) == p and parts[0][0] == 1 and parts[-1][1] == nlat
+            assert all(parts[r + 1][0] == parts[r][1] + 1 for r in range(p - 1))
+            sizes = [e - b + 1 for b, e in parts]
+            assert min(sizes) >= (6 if p > 1 else nlat)                               # gmc_create's minimum band
+            if p >= 3:
+                assert sizes[0] <= min(sizes[1:-1]) and sizes[-1] <= min(sizes[1:-1])
+    host = Host(1440, 720, 32, 30.0, "baroclinic_wave")
+    cost = lambda parts: max(row_weights(host)[b - 1:e].sum() for b, e in parts)
+    assert cost(balanced_rows(host, 8)) < cost(round_robin(720, 8))
+    assert band_config(host, 0, 8, 0, rows="balanced").lat_iend == balanced_rows(host, 8)[0][1]
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 

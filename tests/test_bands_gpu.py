@@ -15,18 +15,20 @@ def glob_field(x, name):
     return a
 
 
-@pytest.mark.parametrize("case,nlon,nlat,nlev,dt,nbands", [
-    ("baroclinic_wave", 64, 33, 8, 600.0, 2),
-    ("baroclinic_wave", 64, 33, 8, 600.0, 4),
-    ("held_suarez", 48, 25, 8, 600.0, 3),
-    ("baroclinic_wave", 120, 61, 32, 300.0, 8),
+@pytest.mark.parametrize("case,nlon,nlat,nlev,dt,nbands,rows", [
+    ("baroclinic_wave", 64, 33, 8, 600.0, 2, "round_robin"),
+    ("baroclinic_wave", 64, 33, 8, 600.0, 4, "round_robin"),
+    ("held_suarez", 48, 25, 8, 600.0, 3, "round_robin"),
+    ("baroclinic_wave", 120, 61, 32, 300.0, 8, "round_robin"),
+    ("baroclinic_wave", 120, 61, 32, 300.0, 5, "balanced"),      # unequal bands: polar bands own fewer rows
+    ("held_suarez", 48, 25, 8, 600.0, 3, "balanced"),
 ])
-def test_bands_match_single_band(gpu_required, case, nlon, nlat, nlev, dt, nbands):
+def test_bands_match_single_band(gpu_required, case, nlon, nlat, nlev, dt, nbands, rows):
     from gmcore_b200.model import GmcoreBandGroup
     host, ic, orc, one = make_pair(nlon, nlat, nlev, dt, case)
     q = smooth_tracer(host, host.cfg.ntracers)
     one.set_tracers(q)
-    grp = GmcoreBandGroup(host, nbands)
+    grp = GmcoreBandGroup(host, nbands, rows=rows)
     grp.set_state(ic); grp.set_tracers(q)
     one.prepare_run(); grp.prepare_run()
     np.testing.assert_allclose(grp.diagnose()[[0, 1, 7]], one.diagnose()[[0, 1, 7]], rtol=1e-13)
