@@ -363,7 +363,7 @@ def _main(out):
 
     if banded:
         from gmcore_b200.model import balanced_rows, round_robin
-        band_rows = os.environ.get("GMCORE_BAND_ROWS", "balanced")
+        band_rows = os.environ.get("GMCORE_BAND_ROWS", "round_robin")
         parts = balanced_rows(host, world) if band_rows == "balanced" else round_robin(host.nlat, world)
         band_sizes = "/".join(str(e - b + 1) for b, e in parts)
     if rank == 0:

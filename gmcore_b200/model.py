@@ -240,11 +240,14 @@ def round_robin(n, nparts):
     return out
 
 
-# Cost model of one latitude row for the balanced split: 1 (everything uniform in latitude) + ROW_TAP_COST per zonal
-# filter tap above the equatorial count (big_filter on u, v; small_filter2 on u, v; small_filter1 on pt) + POLE_ROW_COST
-# for a pole row (zonal sums, k_pole1 / k_pole_sum launches).  Calibrated on the 8-band 0.25 deg x L32 run: the two
-# polar bands spent 0.36 ms more in k_filter_rows and 0.17 ms in pole kernels than the 0.034 ms per row of an
-# interior band (profiles/r01_bench_bw_1440x720x32_8gpu_v5.json vs the balanced run).
+# Cost model of one latitude row for the optional balanced split: 1 (everything uniform in latitude) + ROW_TAP_COST
+# per zonal filter tap above the equatorial count (big_filter on u, v; small_filter2 on u, v; small_filter1 on pt) +
+# POLE_ROW_COST for a pole row (zonal sums, k_pole1 / k_pole_sum launches).  The weights came from rank 0's kernel
+# times of the 8-band 0.25 deg x L32 run (+0.36 ms in k_filter_rows, +0.17 ms in pole kernels).  MEASURED: the split
+# they give (82/92/93/93/93/93/92/82) ran at 7497 SDPD against 7565 for 8 x 90 rows -- rank 0 got 6 % faster but the
+# interior bands, now 105 rows with their halo, became the critical path: at ~100 rows per GPU the kernels no longer
+# fill the device and the cost per row is far from uniform, so the modelled polar surplus was ~5x too large.
+# Equal rows stay the default; the option is kept for hosts with much wider polar filters (finer grids).
 ROW_TAP_COST = 0.00486
 POLE_ROW_COST = 5.0
 BOUNDARY_COST = 4.0      # row-equivalents of redundant halo-row compute per interior band boundary (6 rows, not every kernel)
@@ -394,10 +397,10 @@ class GmcoreBand(GmcoreGPU):
 
 def make_band_nccl(host, rank, world, device, rows=None):
     """torch.distributed-launched rank -> its latitude band with the NCCL transport set up.
-    rows: "balanced" (default; GMCORE_BAND_ROWS overrides) or "round_robin" (the reference's equal row counts)."""
+    rows: "round_robin" (default: the reference's equal row counts; GMCORE_BAND_ROWS overrides) or "balanced"."""
     import torch
     import torch.distributed as dist
-    rows = rows or os.environ.get("GMCORE_BAND_ROWS", "balanced")
+    rows = rows or os.environ.get("GMCORE_BAND_ROWS", "round_robin")
     band = GmcoreBand(host, rank, world, device, rows)
     t = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{device}")
     if rank == 0:
