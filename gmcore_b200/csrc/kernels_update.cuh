@@ -236,6 +236,32 @@ __global__ void __launch_bounds__(256) k_diag_partial(Geo g, DMesh M, DiagArgs a
   const int nrows = g.je - g.jb + 1;
   double tm = 0, ke = 0, ie = 0, pe = 0, av = 0, tpe = 0, tpt = 0;
   const bool nopole = j > 1 && j < g.nlat, half = j <= g.nhalf;
+  // Interior rows of the hydrostatic core (all but the two pole rows): one straight-line body, so that the twelve
+  // loads of a point are issued together; the general loop below has one basic block (= one memory round trip)
+  // per term.  Same terms in the same order.
+  const bool common = nopole && half && a.baroclinic && j + 1 <= g.nlat;
+  if (common) {
+    const double ac = MJ(M.area_cell, j), alon = MJ(M.area_lon, j), alat = MJ(M.area_lat, j), avtx = MJ(M.area_vtx, j);
+    const int n = g.nlon;
+    const long long rb = gidx(g, 0, j, k);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const long long c = rb + i;
+      const int ip = i + 1 < n ? i + 1 : 0;
+      const double m = __ldg(a.m + c), me = __ldg(a.m + rb + ip), mn = __ldg(a.m + c + n);
+      const double fx = __ldg(a.mfx_lon + c), ul = __ldg(a.u_lon + c), pl = __ldg(a.pv_lon + c);
+      const double fy = __ldg(a.mfy_lat + c), vl = __ldg(a.v_lat + c), pv = __ldg(a.pv + c), pa = __ldg(a.pv_lat + c);
+      const double t = __ldg(a.t + c), pt = __ldg(a.pt + c);
+      tm += m * ac;
+      ke += fx * 0.5 * ul * alon * 2;
+      tpe += (m + me) * 0.5 * (pl * pl) * 0.5 * alon;
+      ke += fy * 0.5 * vl * alat * 2;
+      av += pv * avtx;
+      tpe += (m + mn) * 0.5 * (pa * pa) * 0.5 * alat;
+      ie += m * a.cpd * t * ac;
+      tpt += m * pt * ac;
+      if (k == 0) pe += __ldg(a.gzs + gidx(g, i, j, 0)) * __ldg(a.phs + gidx(g, i, j, 0)) * ac;
+    }
+  } else
   for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) {
     const long long c = gidx(g, i, j, k);
     const double m = __ldg(a.m + c);
