@@ -611,6 +611,13 @@ __global__ void __launch_bounds__(128) k_div_damp(Geo g, DMesh M, DivDampArgs a)
   if (i >= g.nlon) return;
   const long long c = gidx(g, i, j, k);
   const double d0 = __ldg(a.div + c);
+  if (j > 1 && j < g.nhalf) {      // interior rows: every load before the first store (one memory round trip, same arithmetic)
+    const double de = ldW(a.div, g, i + 1, j, k), dn = __ldg(a.div + c + g.nlon), uo = a.u[c], vo = a.v[c];
+    const double cl = __ldg(a.c_lon + (size_t)k * g.nlat + (j - 1)), ca = __ldg(a.c_lat + (size_t)k * g.nhalf + (j - 1));
+    a.u[c] = uo + a.sgn * (cl * (de - d0) / MJ(M.de_lon, j));
+    a.v[c] = vo + a.sgn * (ca * (dn - d0) / MJ(M.de_lat, j));
+    return;
+  }
   if (j > 1 && j < g.nlat)
     a.u[c] = a.u[c] + a.sgn * (__ldg(a.c_lon + (size_t)k * g.nlat + (j - 1)) * (ldW(a.div, g, i + 1, j, k) - d0) / MJ(M.de_lon, j));
   if (j <= g.nhalf)
