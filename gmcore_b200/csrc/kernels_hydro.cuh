@@ -703,6 +703,7 @@ __global__ void __launch_bounds__(128) k_tracer_h(Geo g, DMesh M, TrHArgs a) {
   if (i >= g.nlon) return;
   const long long c = gidx(g, i, j, k);
   const double mq = __ldg(a.old_m + c) * __ldg(a.qo + c);
+  const double mnew = __ldg(a.m + c);       // loaded with the others, not after the flux divergence
   double r;
   if (j > 1 && j < g.nlat)
     r = mq - ((__ldg(a.qmf_lon + c) - ldW(a.qmf_lon, g, i - 1, j, k)) * MJ(M.le_lon, j) +
@@ -711,7 +712,7 @@ __global__ void __launch_bounds__(128) k_tracer_h(Geo g, DMesh M, TrHArgs a) {
     const double pole = __ldg(a.pole + (j == 1 ? 0 : g.nlev) + k) * a.dt;
     r = j == 1 ? mq - pole : mq + pole;
   }
-  a.qn[c] = r / __ldg(a.m + c);
+  a.qn[c] = r / mnew;
 }
 
 // sequential negative filling along x (:236-258); one block per (row, level), the sweep
@@ -758,6 +759,10 @@ template <int LIM> __global__ void __launch_bounds__(128) k_tracer_v(Geo g, TrVA
   for (int k = 0; k < nlev; ++k) {
     const int k1 = k + 2, c = c0 + k * st;
     double cz = 0, w = 0;
+    if ((i & 15) == 0 && k + 3 < nlev) {     // one lane per 128-byte line: level k+3 into L2 (as k_pt_col)
+      const int cp = c + 3 * st;
+      pf_l2(a.cflz + cp + st); pf_l2(a.we + cp + st); pf_l2(a.m + cp);
+    }
     if (k1 <= nlev) { cz = __ldg(a.cflz + c + st); w = __ldg(a.we + c + st); }
     const double m = __ldg(a.m + c);
     const double f_dn = k1 <= nlev ? vflx_one<LIM>(q, k1, cz, w) : 0.0;
