@@ -282,6 +282,7 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_we_col(Geo g, DMesh M, WeArgs
     double* we = a.we_lev + c0;
     const double* ml = a.m_lev + c0;
     const double* hd = M.half_dlev - 1;
+#pragma unroll 4
     for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
       const double w = -(M.hybi[k1 - 1] * dphs) - wm[(k1 - 1) * WE_TX];
       we[(k1 - 1) * st] = w;
@@ -311,6 +312,7 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_cflz(Geo g, DMesh M, CflzArgs
   double* wm = wm_s + tx;
   const double* hd = M.half_dlev - 1;
   if (act)
+#pragma unroll 4
     for (int k1 = 1 + ty; k1 <= nlev + 1; k1 += WE_TY)
       wm[(k1 - 1) * WE_TX] = qdiv(__ldg(a.we + c0 + (k1 - 1) * st), __ldg(a.m_lev + c0 + (k1 - 1) * st)) * hd[k1];
   __syncthreads();
