@@ -688,12 +688,19 @@ __global__ void __launch_bounds__(128) k_accum(Geo g, AccumArgs a) {
   const int j = g.jb + blockIdx.y, k = blockIdx.z;
   if (i >= g.nlon) return;
   const long long c = gidx(g, i, j, k);
+  // both pairs' loads before the first store (the second pair's accumulator read would otherwise wait for it)
+  bool on[2]; double s[2], d[2];
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
-    if (!a.dst[q] || k >= a.nlev_[q]) continue;
-    const double s = __ldg(a.src[q] + c);
-    if (a.mode == 0) a.dst[q][c] = s;
-    else { const double t = a.dst[q][c] + s; a.dst[q][c] = a.mode == 2 ? t / (a.nstep + 1) : t; }
+    on[q] = a.dst[q] && k < a.nlev_[q];
+    s[q] = on[q] ? __ldg(a.src[q] + c) : 0.0;
+    d[q] = on[q] && a.mode != 0 ? a.dst[q][c] : 0.0;
+  }
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    if (!on[q]) continue;
+    if (a.mode == 0) a.dst[q][c] = s[q];
+    else { const double t = d[q] + s[q]; a.dst[q][c] = a.mode == 2 ? t / (a.nstep + 1) : t; }
   }
 }
 
