@@ -49,6 +49,12 @@ template <class Store> __device__ __forceinline__ void conv_row(const double* __
   }
 }
 // shared memory: [row: nlon+2*mh][row2: nlon+2*mh][w1: 2*mh+1][w2: 2*mh+1], mh = a.mh (largest half-width of any filter)
+#ifndef FILT_DIRECT3
+#define FILT_DIRECT3 1
+#endif
+#ifndef FILT_STAGE4
+#define FILT_STAGE4 1
+#endif
 __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   extern __shared__ double srow[];
   // grid = (level, row rank): rows are issued from the two ends of the band inwards, i.e. widest filters (most
@@ -66,6 +72,21 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   const int nlon = g.nlon, rs = nlon + 2 * a.mh;
   if (!a.chain && n1 <= 1 && n2 <= 1) {      // unfiltered row (block-uniform): straight from global memory
     const int base = gidx(g, 0, j, k);
+#if FILT_DIRECT3
+    if (a.post == POST_DIV_M && !a.out1 && !a.out_m) {     // pt: three points per thread in flight
+      const int B = blockDim.x;
+      for (int i = threadIdx.x; i < nlon; i += 3 * B) {
+        const bool v1 = i + B < nlon, v2 = i + 2 * B < nlon;
+        const double s0 = __ldg(a.in + base + i), m0 = __ldg(a.mdiv + base + i);
+        const double s1 = v1 ? __ldg(a.in + base + i + B) : 0.0, m1 = v1 ? __ldg(a.mdiv + base + i + B) : 1.0;
+        const double s2 = v2 ? __ldg(a.in + base + i + 2 * B) : 0.0, m2 = v2 ? __ldg(a.mdiv + base + i + 2 * B) : 1.0;
+        a.out2[base + i] = s0 / m0;
+        if (v1) a.out2[base + i + B] = s1 / m1;
+        if (v2) a.out2[base + i + 2 * B] = s2 / m2;
+      }
+      return;
+    }
+#endif
     for (int i = threadIdx.x; i < nlon; i += blockDim.x) {
       double s = __ldg(a.in + base + i);
       if (a.out1) a.out1[base + i] = s;
@@ -78,10 +99,27 @@ __global__ void __launch_bounds__(256) k_filter_rows(Geo g, FilterArgs a) {
   double* __restrict__ srow2 = srow + rs;
   double* __restrict__ ws1 = srow + 2 * rs; double* __restrict__ ws2 = ws1 + (2 * a.mh + 1);
   const double* __restrict__ row = a.in + gidx(g, 0, j, k);
+#if FILT_STAGE4
+  {  // four loads per thread in flight before the first shared-memory store (the plain loop waits on every load)
+    const int tot = nlon + 2 * hn, B = blockDim.x;
+    for (int x0 = threadIdx.x; x0 < tot; x0 += 4 * B) {
+      double v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int x = x0 + q * B;
+        int i = x - hn; i = i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
+        v[q] = x < tot ? row[i] : 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) if (x0 + q * B < tot) srow[x0 + q * B] = v[q];
+    }
+  }
+#else
   for (int x = threadIdx.x; x < nlon + 2 * hn; x += blockDim.x) {
     int i = x - hn; i = i < 0 ? i + nlon : (i >= nlon ? i - nlon : i);
     srow[x] = row[i];
   }
+#endif
   const double* __restrict__ w1 = a.half_lat ? a.f1.wgt_lat + (size_t)(j + 1) * a.f1.ld_lat : a.f1.wgt_lon + (size_t)(j + 1) * a.f1.ld_lon;
   const double* __restrict__ w2 = a.half_lat ? a.f2.wgt_lat + (size_t)(j + 1) * a.f2.ld_lat : a.f2.wgt_lon + (size_t)(j + 1) * a.f2.ld_lon;
   for (int t = threadIdx.x; t < n1; t += blockDim.x) ws1[t] = __ldg(w1 + t);
