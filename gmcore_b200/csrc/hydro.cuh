@@ -109,11 +109,16 @@ __global__ void k_axpy2d(Geo g, const double* x, const double* d, double* y, dou
   const long long c = gidx(g, i, j, 0);
   y[c] = x[c] + dt * d[c];
 }
-__global__ void k_copy3(Geo g, const double* x, double* y) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = g.jb + blockIdx.y, k = blockIdx.z;
-  if (i >= g.nlon) return;
-  const long long c = gidx(g, i, j, k);
-  y[c] = x[c];
+__global__ void k_copy3(Geo g, const double* __restrict__ x, double* __restrict__ y) {   // one block per (row, level)
+  const int j = g.jb + blockIdx.x, k = blockIdx.y;
+  const long long rb = gidx(g, 0, j, k);
+  for (int i0 = threadIdx.x; i0 < g.nlon; i0 += 4 * blockDim.x) {      // four loads in flight per thread
+    double v[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) { const int i = i0 + r * blockDim.x; v[r] = i < g.nlon ? __ldg(x + rb + i) : 0.0; }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) { const int i = i0 + r * blockDim.x; if (i < g.nlon) y[rb + i] = v[r]; }
+  }
 }
 
 // Row ranges.  In band mode (cfg.nranks > 1) most kernels run on a few rows beyond the owned
@@ -340,7 +345,7 @@ static void hydro_adv_finish(gmc_handle* h, int itime, bool advected) {
   if (h->cfg.ntracers <= 0) return;
   const Geo& g = h->g;
   if (advected) { int t = h->q_old; h->q_old = h->q_new; h->q_new = t; }
-  LAUNCH(h, k_copy3, gridg(g, g.nlev), 128, 0, g, h->st[itime].m, h->old_m);   // copy_old_m
+  LAUNCH(h, k_copy3, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, h->st[itime].m, h->old_m);   // copy_old_m
 }
 static HaloSet tracer_halo_set(gmc_handle* b, int which /*0: q_old, 1: q_new*/, int with_pt_of = 0) {
   HaloSet s = halo_set();

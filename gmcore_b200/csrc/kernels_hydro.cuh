@@ -154,9 +154,13 @@ __global__ void __launch_bounds__(256) k_pole_sum(Geo g, DMesh M, PoleSumArgs a)
   if ((north && !g.has_north) || (!north && !g.has_south)) return;
   const int j = north ? g.nlat : 1, jh = north ? g.nhalf : 1;
   double s = 0;
-  for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) {
-    const double f = __ldg(a.f + gidx(g, i, jh, k));
-    s += (north && a.signed_north) ? -f : f;
+  const double* __restrict__ fr = a.f + gidx(g, 0, jh, k);
+  for (int i0 = threadIdx.x; i0 < g.nlon; i0 += 4 * blockDim.x) {      // four loads in flight, added in the same order
+    double v[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) { const int i = i0 + r * blockDim.x; v[r] = i < g.nlon ? __ldg(fr + i) : 0.0; }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) if (i0 + r * blockDim.x < g.nlon) s += (north && a.signed_north) ? -v[r] : v[r];
   }
   s = block_sum(s, sm);
   const double pole = s * MJ(M.le_lat, jh) / g.nlon / MJ(M.area_cell, j);
@@ -732,7 +736,13 @@ __global__ void __launch_bounds__(128) k_negfill_x(Geo g, NegXArgs a) {
   const int j = g.jb + blockIdx.x, k = blockIdx.y;
   double* q = a.q + gidx(g, 0, j, k); const double* m = a.m + gidx(g, 0, j, k);
   int neg = 0;
-  for (int i = threadIdx.x; i < g.nlon; i += blockDim.x) neg |= q[i] < 0;
+  for (int i0 = threadIdx.x; i0 < g.nlon; i0 += 4 * blockDim.x) {      // four loads in flight per thread
+    double v[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) { const int i = i0 + r * blockDim.x; v[r] = i < g.nlon ? q[i] : 0.0; }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) neg |= v[r] < 0;
+  }
   neg = __syncthreads_or(neg);
   if (!neg || threadIdx.x != 0) return;
   const int n = g.nlon;
