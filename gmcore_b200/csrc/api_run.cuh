@@ -17,7 +17,7 @@ static int launch_diag(gmc_handle* h, int itime, double* dev_out) {
              h->diag_partial, h->cfg.g, h->cfg.cpd, h->cfg.baroclinic};
   const int nrows = g.je - g.jb + 1;
   LAUNCH(h, k_diag_partial, dim3(nrows, g.nlev), 256, 0, g, h->M, a);
-  LAUNCH(h, k_diag_final, 7, 1024, 0, h->diag_partial, nrows * g.nlev, dev_out);
+  LAUNCH(h, k_diag_final, 8, 1024, 0, h->diag_partial, nrows * g.nlev, dev_out, h->dflags);
   return 0;
 }
 // device sums (tm, te_ke, te_ie, te_pe, tav, tpe, tpt) -> ABI order
@@ -32,17 +32,25 @@ static int time_integrate_impl(gmc_handle* h, int old_, int nw, double dt, int t
   if (!h->cfg.baroclinic) { if (h->cfg.use_smag_damp) run_smag_damp(h, h->st[nw], dt); return 0; }
   bool adv = false;
   for_bands(h, [&](gmc_handle* b) { adv = hydro_post_compute(b, nw, dt, time_step); });
-  const bool hs = h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ;
-  if (adv || hs) {
-    auto post_set = [&](gmc_handle* b) { HaloSet s = adv ? tracer_halo_set(b, 1) : halo_set(); if (hs) halo_add(s, b->st[nw].pt, b->g.nlev); return s; };
-    if (halo_exchange(h, post_set)) return 1;
+  if (h->cfg.nranks > 1) {
+    // one packed exchange per advected batch (the alert clocks are the same on every band), pt with the first
+    bool hs = h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ;
+    for (size_t m = 0; m < h->batches.size(); ++m) {
+      if (!h->batches[m].advected) continue;
+      const bool with_pt = hs; hs = false;
+      if (halo_exchange(h, [&](gmc_handle* b) { HaloSet s = tracer_halo_set(b, (int)m, 1); if (with_pt) halo_add(s, b->st[nw].pt, b->g.nlev); return s; })) return 1;
+    }
+    if (hs && halo_exchange(h, [&](gmc_handle* b) { HaloSet s = halo_set(); halo_add(s, b->st[nw].pt, b->g.nlev); return s; })) return 1;
   }
-  for_bands(h, [&](gmc_handle* b) { hydro_adv_finish(b, nw, adv); });
+  (void)adv;
+  for_bands(h, [&](gmc_handle* b) { hydro_adv_finish(b, nw); });
   return 0;
 }
-// time_advance bookkeeping of the tracer alert (time_mod.F90:128-159), every band
+// time_advance bookkeeping of the tracer alerts (time_mod.F90:128-159), every band, every batch
 static void alert_advance(gmc_handle* h, int time_step) {
-  for_bands(h, [&](gmc_handle* b) { if (b->alert_ring) { b->alert_last = time_step * b->cfg.dt_dyn; b->alert_ring = false; } });
+  for_bands(h, [&](gmc_handle* b) {
+    for (TrBatch& T : b->batches) if (T.alert_ring) { T.alert_last = time_step * b->cfg.dt_dyn; T.alert_ring = false; }
+  });
 }
 
 extern "C" {
@@ -65,7 +73,8 @@ int gmc_prepare_run(gmc_handle* h, int old_) {
       hydro_prepare_run_1(b, old_);
     });
     if (halo_exchange(h, [&](gmc_handle* b) { return prepare_halo_set(b, old_); })) return 1;
-    if (h->cfg.ntracers > 0 && halo_exchange(h, [&](gmc_handle* b) { return tracer_halo_set(b, 0); })) return 1;
+    for (size_t m = 0; m < h->batches.size(); ++m)
+      if (halo_exchange(h, [&](gmc_handle* b) { return tracer_halo_set(b, (int)m, 0); })) return 1;
     for_bands(h, [&](gmc_handle* b) { hydro_prepare_run_2(b, old_); });
   }
   CUDA_CHECK(cudaGetLastError());
@@ -82,6 +91,9 @@ int gmc_time_integrate(gmc_handle* h, int old_, int nw, double dt, int time_step
 
 // Global sums over all bands: single-process group -> host sum in band order;
 // one process per GPU -> ncclAllReduce of the partial sums (global_sum, parallel_mod.F90:805-816).
+// Slot 7 of every set is the guard word (k_diag_final): a non-zero value anywhere means one of the reference's
+// log_error guards fired on some band -> the call fails with the guard text, as the reference stops in
+// log_error / process_stop, and the device words are cleared once reported.
 static int reduce_diag(gmc_handle* h, std::vector<double*>& dbufs, int nsets, double* out_abi) {
   std::vector<double> acc((size_t)nsets * 8, 0.0), tmp((size_t)nsets * 8);
   if (h->nccl_comm) {
@@ -94,8 +106,30 @@ static int reduce_diag(gmc_handle* h, std::vector<double*>& dbufs, int nsets, do
     CUDA_CHECK(cudaStreamSynchronize(h->stream));
     for (size_t q = 0; q < acc.size(); ++q) acc[q] += tmp[q];
   }
-  for (int s = 0; s < nsets; ++s) diag_to_abi(&acc[(size_t)s * 8], out_abi + (size_t)s * 8);
+  int guards = 0;
+  for (int s = 0; s < nsets; ++s) {
+    if (out_abi) diag_to_abi(&acc[(size_t)s * 8], out_abi + (size_t)s * 8);
+    double v = acc[(size_t)s * 8 + 7];
+    for (int b = 0; b < 5 && v > 0; ++b) { const double r = fmod(v, 256.0); if (r > 0) guards |= 1 << b; v = (v - r) / 256.0; }
+  }
+  if (guards) {
+    hydro_flags_text(h, guards);
+    for_bands(h, [&](gmc_handle* b) { if (b->dflags) cudaMemsetAsync(b->dflags, 0, sizeof(int), b->stream); });
+    return 1;
+  }
   return 0;
+}
+
+// grow-only per-band device buffer for the per-step sums of gmc_run_steps (no cudaMalloc inside a timed loop)
+static double* diag_steps_buf(gmc_handle* b, int nsteps) {
+  if (b->diag_steps_cap < nsteps) {
+    if (b->diag_steps) cudaFree(b->diag_steps);
+    b->diag_steps = nullptr; b->diag_steps_cap = 0;
+    const int cap = nsteps < 64 ? 64 : nsteps;
+    if (cudaMalloc(&b->diag_steps, (size_t)cap * 8 * sizeof(double)) != cudaSuccess) return nullptr;
+    b->diag_steps_cap = cap;
+  }
+  return b->diag_steps;
 }
 
 int gmc_diagnose(gmc_handle* h, int itime, double out[8]) {
@@ -107,12 +141,14 @@ int gmc_diagnose(gmc_handle* h, int itime, double out[8]) {
 
 int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int nsteps, double* diag) {
   if (check_ready(h)) return 1;
+  if (nsteps <= 0) return 0;
   std::vector<double*> dbufs;
   int rc = 0;
-  if (diag) for_bands(h, [&](gmc_handle* b) {
-    double* d = nullptr;
-    if (cudaMalloc(&d, (size_t)nsteps * 8 * sizeof(double)) != cudaSuccess) rc = 1;
-    cudaMemsetAsync(d, 0, (size_t)nsteps * 8 * sizeof(double), b->stream);
+  // with diag == NULL one set is still taken after the last step: it carries the guard word back
+  const int nsets = diag ? nsteps : 1;
+  for_bands(h, [&](gmc_handle* b) {
+    double* d = diag_steps_buf(b, nsets);
+    if (!d) { rc = 1; snprintf(h->err, sizeof(h->err), "cudaMalloc of the diagnostics buffer failed"); }
     dbufs.push_back(d);
   });
   for (int s = 0; s < nsteps && !rc; ++s) {
@@ -120,23 +156,21 @@ int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int
     alert_advance(h, *time_step);   // time_advance (time_mod.F90:128-159)
     int t = *old_idx; *old_idx = *new_idx; *new_idx = t;
     *time_step += 1;
-    if (diag) { int bi = 0; for_bands(h, [&](gmc_handle* b) { launch_diag(b, *old_idx, dbufs[bi++] + (size_t)s * 8); }); }
+    if (diag || s == nsteps - 1) { int bi = 0; for_bands(h, [&](gmc_handle* b) { launch_diag(b, *old_idx, dbufs[bi++] + (size_t)(diag ? s : 0) * 8); }); }
   }
   if (!rc && cudaGetLastError() != cudaSuccess) { snprintf(h->err, sizeof(h->err), "run_steps: CUDA launch error"); rc = 1; }
-  if (!rc && diag) rc = reduce_diag(h, dbufs, nsteps, diag);
-  for (double* d : dbufs) cudaFree(d);
-  if (rc) return 1;
-  int bad = 0;
-  for_bands(h, [&](gmc_handle* b) { if (hydro_check_flags(b)) { bad = 1; if (b != h) snprintf(h->err, sizeof(h->err), "%s", b->err); } });
-  return bad;
+  if (!rc) rc = reduce_diag(h, dbufs, nsets, diag);
+  return rc;
 }
 
 // Back to the state right after gmc_create + set_*: step counter bookkeeping of the tracer batch and the
 // alert clock (time_init, time_mod.F90:61-98).  The host then uploads a state and calls gmc_prepare_run again.
 int gmc_reset_clock(gmc_handle* h) {
   for_bands(h, [&](gmc_handle* b) {
-    b->uv_step = b->mf_step = b->we_step = 0; b->q_old = 0; b->q_new = 1;
-    b->alert_last = -b->cfg.dt_adv; b->alert_ring = false;
+    for (TrBatch& T : b->batches) {
+      T.uv_step = T.mf_step = T.we_step = 0; T.q_old = 0; T.q_new = 1;
+      T.alert_last = -T.dt; T.alert_ring = false; T.advected = false;
+    }
   });
   return 0;
 }
@@ -147,7 +181,7 @@ __global__ void k_fill(double* p, size_t n, double v) {
   for (size_t x = blockIdx.x * (size_t)blockDim.x + threadIdx.x; x < n; x += (size_t)gridDim.x * blockDim.x) p[x] = v;
 }
 int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double* v_f) {
-  if (!h->cfg.baroclinic || h->cfg.ntracers <= 0 || h->cfg.nranks > 1) {
+  if (!h->cfg.baroclinic || h->batches.empty() || h->cfg.nranks > 1) {
     snprintf(h->err, sizeof(h->err), "the advection-only driver needs the hydrostatic core with a tracer batch on one band"); return 1; }
   if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
   const Geo& g = h->g; DState& S = h->st[itime];
@@ -162,15 +196,27 @@ int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double*
 }
 int gmc_adv_step(gmc_handle* h, int itime, int time_step) {
   if (check_ready(h)) return 1;
-  if (!h->cfg.baroclinic || h->cfg.ntracers <= 0 || h->cfg.nranks > 1) {
+  if (!h->cfg.baroclinic || h->batches.empty() || h->cfg.nranks > 1) {
     snprintf(h->err, sizeof(h->err), "the advection-only driver needs the hydrostatic core with a tracer batch on one band"); return 1; }
   alert_advance(h, time_step - 1);
-  const bool adv = hydro_adv_run(h, itime, time_step);
-  hydro_adv_finish(h, itime, adv);
+  hydro_adv_run(h, itime, time_step);
+  hydro_adv_finish(h, itime);
   CUDA_CHECK(cudaGetLastError());
   return hydro_check_flags(h);
 }
-int gmc_set_tracers(gmc_handle* h, const double* q) { return hydro_set_tracers(h, q); }
-int gmc_get_tracers(gmc_handle* h, double* q) { return hydro_get_tracers(h, q); }
+int gmc_set_tracers(gmc_handle* h, const double* q) { return gmc_set_batch_tracers(h, 0, q); }
+int gmc_get_tracers(gmc_handle* h, double* q) { return gmc_get_batch_tracers(h, 0, q); }
+int gmc_add_tracer_batch(gmc_handle* h, int ntracers, double dt_adv, int* batch) {
+  if (!h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "tracer batches need the hydrostatic core"); return 1; }
+  return hydro_add_batch(h, ntracers, dt_adv, batch);
+}
+int gmc_set_batch_tracers(gmc_handle* h, int batch, const double* q) {
+  if (!h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "no tracer batch configured"); return 1; }
+  return hydro_set_tracers(h, batch, q);
+}
+int gmc_get_batch_tracers(gmc_handle* h, int batch, double* q) {
+  if (!h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "no tracer batch configured"); return 1; }
+  return hydro_get_tracers(h, batch, q);
+}
 
 }  // extern "C"

@@ -82,14 +82,13 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (!rc) rc = dev_alloc(h, &h->diag_partial, (size_t)7 * (g.je - g.jb + 1) * g.nlev);
   if (!rc) rc = dev_alloc(h, &h->diag_out, 8);
   if (!rc && cfg->use_smag_damp) { rc = dev_alloc(h, &h->smag_t, n3); if (!rc) rc = dev_alloc(h, &h->smag_s, n3); if (!rc) rc = dev_alloc(h, &h->smag_du, n3); if (!rc) rc = dev_alloc(h, &h->smag_dv, n3); }
+  h->H = cfg->nranks > 1 ? 4 : 0;      // halo rows exchanged per side and stage (band mode)
   if (!rc && baro) rc = hydro_alloc(h);
   if (!rc) rc = halo_alloc(h);
   h->stage_bytes = (size_t)(g.nlon + 2 * cfg->hx) * ((g.je - g.jb + 1) + 2 * cfg->hy) * (g.nlev + 4) * sizeof(double);
   if (!rc) { double* p; rc = dev_alloc(h, &p, h->stage_bytes / sizeof(double)); h->stage_img = p; }
   if (rc) { snprintf(g_create_err, sizeof(g_create_err), "%s", h->err); gmc_destroy(h); return 4; }
   { const char* e = getenv("GMCORE_DEBUG_FIELDS"); h->keep_dpt = e && e[0] == '1'; }
-  h->nstep = (int)(cfg->dt_adv / cfg->dt_dyn);
-  h->alert_period = cfg->dt_adv; h->alert_last = -cfg->dt_adv;
   *out = h;
   return 0;
 }
@@ -99,6 +98,7 @@ void gmc_destroy(gmc_handle* h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  if (h->diag_steps) cudaFree(h->diag_steps);
   if (h->nccl_comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->nccl_comm);
   if (h->group) {   // the group vector is shared: the last member to go frees it
     auto* grp = h->group;

@@ -6,9 +6,13 @@
 #include <dlfcn.h>
 #include "handle.cuh"
 
-struct HaloSet { double* p[8]; int nk[8]; int n; int ktot; };
-static inline HaloSet halo_set() { HaloSet s; s.n = 0; s.ktot = 0; return s; }
-static inline void halo_add(HaloSet& s, double* p, int nk) { s.p[s.n] = p; s.nk[s.n] = nk; s.n++; s.ktot += nk; }
+#define GMC_HALO_MAX 24     // arrays per exchange point; gmc_create rejects tracer counts that would not fit
+struct HaloSet { double* p[GMC_HALO_MAX]; int nk[GMC_HALO_MAX]; int n; int ktot; int overflow; };
+static inline HaloSet halo_set() { HaloSet s; s.n = 0; s.ktot = 0; s.overflow = 0; return s; }
+static inline void halo_add(HaloSet& s, double* p, int nk) {
+  if (s.n >= GMC_HALO_MAX) { s.overflow = 1; return; }      // reported by halo_exchange, never written past the arrays
+  s.p[s.n] = p; s.nk[s.n] = nk; s.n++; s.ktot += nk;
+}
 
 // grid (ceil(nlon/128), 2*H, ktot).  Buffer layout [kk][r][i], kk running over all levels of all arrays.
 __global__ void __launch_bounds__(128) k_halo(Geo g, HaloSet s, double* buf_s, double* buf_n, int H, int unpack) {
@@ -56,18 +60,19 @@ static NcclApi& nccl_api() {
 }
 enum { GMC_NCCL_DOUBLE = 8, GMC_NCCL_SUM = 0 };   // ncclFloat64, ncclSum (nccl.h)
 
-static int halo_alloc(gmc_handle* h) {
+// Exchange buffers (grow-only): room for ktot levels x H rows per neighbour and direction.
+static int halo_ensure(gmc_handle* h, int ktot) {
   if (h->cfg.nranks <= 1) return 0;
-  const Geo& g = h->g;
-  h->H = 4;
-  const int ktot = 3 * g.nlev + 3 + g.nlev * (h->cfg.ntracers > 0 ? h->cfg.ntracers : 0);
-  h->xbuf_elems = (size_t)ktot * h->H * g.nlon;
-  int rc = dev_alloc(h, &h->send_s, h->xbuf_elems);
-  if (!rc) rc = dev_alloc(h, &h->send_n, h->xbuf_elems);
-  if (!rc) rc = dev_alloc(h, &h->recv_s, h->xbuf_elems);
-  if (!rc) rc = dev_alloc(h, &h->recv_n, h->xbuf_elems);
+  const size_t need = (size_t)ktot * h->H * h->g.nlon;
+  if (need <= h->xbuf_elems) return 0;
+  int rc = dev_alloc(h, &h->send_s, need);
+  if (!rc) rc = dev_alloc(h, &h->send_n, need);
+  if (!rc) rc = dev_alloc(h, &h->recv_s, need);
+  if (!rc) rc = dev_alloc(h, &h->recv_n, need);
+  if (!rc) h->xbuf_elems = need;
   return rc;
 }
+static int halo_alloc(gmc_handle* h) { return halo_ensure(h, 3 * h->g.nlev + 3); }
 
 template <class F> static void for_bands(gmc_handle* h, F f) {
   if (h->group) { for (gmc_handle* b : *h->group) f(b); } else f(h);
@@ -79,8 +84,10 @@ template <class MakeSet> static int halo_exchange(gmc_handle* h, MakeSet make_se
   int rc = 0;
   for_bands(h, [&](gmc_handle* b) {
     HaloSet s = make_set(b);
+    if (s.overflow || (size_t)s.ktot * b->H * b->g.nlon > b->xbuf_elems) { rc = 1; return; }
     LAUNCH(b, k_halo, dim3((b->g.nlon + 127) / 128, 2 * b->H, s.ktot), 128, 0, b->g, s, b->send_s, b->send_n, b->H, 0);
   });
+  if (rc) { snprintf(h->err, sizeof(h->err), "halo exchange: more than %d arrays or a payload beyond the exchange buffer", GMC_HALO_MAX); return 1; }
   if (h->group) {
     // same device, same stream: plain device-to-device copies between neighbouring bands
     for (gmc_handle* b : *h->group) {

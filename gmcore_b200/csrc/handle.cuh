@@ -44,6 +44,18 @@ struct Profiler {
   case 6: LAUNCH(h, kern<6>, __VA_ARGS__); break; \
   default: LAUNCH(h, kern<1>, __VA_ARGS__); } } while (0)
 
+// adv_batch_type (adv_batch_mod.F90:19-69) of a non-dynamic 'cell' batch
+struct TrBatch {
+  int ntr = 0; double dt = 0; int nstep = 1;
+  double* q[2] = {0, 0}; int q_old = 0, q_new = 1;        // q(:,:,:,l,old|new), [l][lev][lat][lon]
+  double alert_last = 0, alert_period = 0; bool alert_ring = false;   // time_mod.F90:253-291 alert of this batch
+  bool advected = false;                                    // set by adv_run for the exchange / swap that follows
+  int wind_of = 0;                                          // batch owning the accumulators below
+  int uv_step = 0, mf_step = 0, we_step = 0;               // sample counters (owner only)
+  double *bu = 0, *bv = 0, *bmfx = 0, *bmfy = 0, *bwe = 0, *bm_lev = 0;
+  double *bcflx = 0, *bcfly = 0, *bcflz = 0, *bdivx = 0, *bdivy = 0;
+};
+
 struct gmc_handle {
   gmc_config cfg;
   Geo g;
@@ -60,19 +72,22 @@ struct gmc_handle {
   double *gzs = 0;                    // static%gzs (2-D)
   double *pole_dmf = 0;               // [2][nlev]
   double *diag_partial = 0, *diag_out = 0;
+  double *diag_steps = 0; int diag_steps_cap = 0;    // per-step sums of gmc_run_steps (grow-only)
   double *stage_img = 0; size_t stage_bytes = 0;
   // hydrostatic work arrays (allocated only when baroclinic)
   double *dphs = 0; int* dflags = 0;   // dflags: device word of the reference's log_error guards
   double *cflx = 0, *cfly = 0, *cflz = 0, *divx = 0, *divy = 0;   // adv_batch_mass
   double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
   double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)
+  double *lon_damp_wgt = 0;
   double *pole_work = 0;
   double *smag_t = 0, *smag_s = 0, *smag_du = 0, *smag_dv = 0;   // smag_damp work arrays (use_smag_damp)
-  // tracer batch
-  double *q[2] = {0, 0}, *old_m = 0, *bu = 0, *bv = 0, *bmfx = 0, *bmfy = 0, *bwe = 0, *bm_lev = 0;
-  double *bcflx = 0, *bcfly = 0, *bcflz = 0, *bdivx = 0, *bdivy = 0, *lon_damp_wgt = 0;
-  int q_old = 0, q_new = 1, uv_step = 0, mf_step = 0, we_step = 0, nstep = 1;
-  double alert_last = 0, alert_period = 0; bool alert_ring = false;
+  // tracer batches (block%adv_batches(:), adv_mod.F90:314-418): batch 0 is cfg.ntracers / cfg.dt_adv, more come from
+  // gmc_add_tracer_batch.  Batches with the same dt see the same wind samples, so they share one accumulator set
+  // (wind_of = the first batch with that dt); old_m is the same array for every batch (copy_old_m runs for all of
+  // them at every adv_run, adv_mod.F90:309).
+  std::vector<TrBatch> batches;
+  double *old_m = 0; int nstep = 1;   // nstep: divisor of the accumulation launch in flight (accum_pair)
   // latitude-band mode (cfg.nranks > 1): packed halo exchange with the two neighbours
   int H = 0;                          // halo rows exchanged per side
   double *send_s = 0, *send_n = 0, *recv_s = 0, *recv_n = 0; size_t xbuf_elems = 0;

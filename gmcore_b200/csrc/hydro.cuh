@@ -10,6 +10,34 @@ static inline VC make_vc(const gmc_handle* h) {
   return VC{c.ptop, c.hybrid_p0, c.p0, c.Rd_o_cpd, c.Rd};
 }
 
+// adv_add_tracer + adv_allocate_tracers_1 (adv_mod.F90:314-418) for one more 'cell' batch of ntr tracers advected
+// every dt seconds; adv_batch_type%init (adv_batch_mod.F90:73-149): nstep = dt / dt_dyn.
+static int halo_ensure(gmc_handle* h, int ktot);
+static int hydro_add_batch(gmc_handle* h, int ntr, double dt, int* id) {
+  const Geo& g = h->g;
+  const size_t n3 = (size_t)g.plane * g.nlev, n3h = (size_t)g.plane * (g.nlev + 1);
+  if (ntr < 1) { snprintf(h->err, sizeof(h->err), "a tracer batch needs at least one tracer"); return 1; }
+  if (h->cfg.nranks > 1 && ntr + 1 > GMC_HALO_MAX) { snprintf(h->err, sizeof(h->err), "at most %d tracers per batch in band mode", GMC_HALO_MAX - 1); return 1; }
+  if (!(dt >= h->cfg.dt_dyn)) { snprintf(h->err, sizeof(h->err), "batch dt %g is shorter than dt_dyn %g", dt, h->cfg.dt_dyn); return 1; }
+  TrBatch B; B.ntr = ntr; B.dt = dt; B.nstep = (int)(dt / h->cfg.dt_dyn);
+  B.alert_period = dt; B.alert_last = -dt;
+  int rc = 0;
+  auto A = [&](double** p, size_t n) { if (!rc) rc = dev_alloc(h, p, n); };
+  A(&B.q[0], n3 * ntr); A(&B.q[1], n3 * ntr);
+  if (!h->old_m) A(&h->old_m, n3);
+  B.wind_of = (int)h->batches.size();
+  for (size_t m = 0; m < h->batches.size(); ++m) if (h->batches[m].wind_of == (int)m && h->batches[m].dt == dt) { B.wind_of = (int)m; break; }
+  if (B.wind_of == (int)h->batches.size()) {
+    A(&B.bu, n3); A(&B.bv, n3); A(&B.bmfx, n3); A(&B.bmfy, n3); A(&B.bwe, n3h); A(&B.bm_lev, n3h);
+    A(&B.bcflx, n3); A(&B.bcfly, n3); A(&B.bcflz, n3h); A(&B.bdivx, n3); A(&B.bdivy, n3);
+  }
+  if (!rc) rc = halo_ensure(h, g.nlev * (ntr + 1));
+  if (rc) return 1;
+  if (id) *id = (int)h->batches.size();
+  h->batches.push_back(B);
+  return 0;
+}
+
 static int hydro_alloc(gmc_handle* h) {
   const Geo& g = h->g;
   const size_t n3 = (size_t)g.plane * g.nlev, n3h = (size_t)g.plane * (g.nlev + 1), n2 = (size_t)g.plane;
@@ -19,13 +47,8 @@ static int hydro_alloc(gmc_handle* h) {
   A(&h->cflx, n3); A(&h->cfly, n3); A(&h->cflz, n3h); A(&h->divx, n3); A(&h->divy, n3);
   A(&h->qx, n3); A(&h->qy, n3); A(&h->ptf_lon, n3); A(&h->ptf_lat, n3); A(&h->qmfx, n3); A(&h->qmfy, n3);
   A(&h->dpt, n3);
-  if (h->cfg.ntracers > 0) {
-    A(&h->q[0], n3 * h->cfg.ntracers); A(&h->q[1], n3 * h->cfg.ntracers);
-    A(&h->old_m, n3); A(&h->bu, n3); A(&h->bv, n3); A(&h->bmfx, n3); A(&h->bmfy, n3);
-    A(&h->bwe, n3h); A(&h->bm_lev, n3h);
-    A(&h->bcflx, n3); A(&h->bcfly, n3); A(&h->bcflz, n3h); A(&h->bdivx, n3); A(&h->bdivy, n3);
-  }
   if (!rc) { int* f = nullptr; rc = dev_alloc(h, &f, 4); h->dflags = f; }
+  if (!rc && h->cfg.ntracers > 0) rc = hydro_add_batch(h, h->cfg.ntracers, h->cfg.dt_adv, nullptr);
   return rc;
 }
 
@@ -297,62 +320,69 @@ static int accum_mode(int& step, int nstep) {
   step += 1; return 1;
 }
 static void hydro_accum_wind(gmc_handle* h, int itime) {
-  if (h->cfg.ntracers <= 0) return;
   const Geo& g = h->g; DState& S = h->st[itime];
-  int mode = accum_mode(h->uv_step, h->nstep);
-  accum_pair(h, xg(h, 4, 4), h->bu, S.u_f, g.nlev, h->bv, S.v_f, g.nlev, mode);
-  if (h->uv_step == 0) run_cfl(h, h->bu, h->bv, h->bcflx, h->bcfly, h->bdivx, h->bdivy, h->cfg.dt_adv);
-  mode = accum_mode(h->mf_step, h->nstep);
-  accum_pair(h, xg(h, 1, 1), h->bmfx, S.mfx_lon, g.nlev, h->bmfy, S.mfy_lat, g.nlev, mode);
-  mode = accum_mode(h->we_step, h->nstep);
-  accum_pair(h, g, h->bwe, S.we_lev, g.nlev + 1, h->bm_lev, S.m_lev, g.nlev + 1, mode);
-  if (h->we_step == 0) {
-    CflzArgs c{h->bwe, h->bm_lev, h->bcflz, h->cfg.dt_adv, h->dflags};
-    LAUNCH(h, k_cflz, gridg(g, 1, WE_TX), dim3(WE_TX, WE_TY), cflz_smem(g.nlev), g, h->M, c);
+  for (size_t m = 0; m < h->batches.size(); ++m) {
+    TrBatch& B = h->batches[m];
+    if (B.wind_of != (int)m) continue;      // shares the samples of an earlier batch with the same dt
+    h->nstep = B.nstep;
+    int mode = accum_mode(B.uv_step, B.nstep);
+    accum_pair(h, xg(h, 4, 4), B.bu, S.u_f, g.nlev, B.bv, S.v_f, g.nlev, mode);
+    if (B.uv_step == 0) run_cfl(h, B.bu, B.bv, B.bcflx, B.bcfly, B.bdivx, B.bdivy, B.dt);
+    mode = accum_mode(B.mf_step, B.nstep);
+    accum_pair(h, xg(h, 1, 1), B.bmfx, S.mfx_lon, g.nlev, B.bmfy, S.mfy_lat, g.nlev, mode);
+    mode = accum_mode(B.we_step, B.nstep);
+    accum_pair(h, g, B.bwe, S.we_lev, g.nlev + 1, B.bm_lev, S.m_lev, g.nlev + 1, mode);
+    if (B.we_step == 0) {
+      CflzArgs c{B.bwe, B.bm_lev, B.bcflz, B.dt, h->dflags};
+      LAUNCH(h, k_cflz, gridg(g, 1, WE_TX), dim3(WE_TX, WE_TY), cflz_smem(g.nlev), g, h->M, c);
+    }
   }
 }
 
-// adv_run (adv_mod.F90:152-312), compute part; returns true when the tracers were advected
-// (band mode: the caller then exchanges q(new) and calls hydro_adv_finish on every band).
+// adv_run (adv_mod.F90:152-312), compute part; returns true when some batch was advected
+// (band mode: the caller then exchanges q(new) of those batches and calls hydro_adv_finish on every band).
 static bool hydro_adv_run(gmc_handle* h, int itime, int time_step) {
   hydro_accum_wind(h, itime);
-  if (h->cfg.ntracers <= 0) return false;
   const Geo& g = h->g; DState& S = h->st[itime];
   const size_t n3 = (size_t)g.plane * g.nlev;
-  const double dt_adv = h->cfg.dt_adv;
-  bool alerted = false;
-  if (h->alert_last + h->alert_period <= time_step * h->cfg.dt_dyn) { h->alert_ring = true; alerted = true; }
-  const bool adv = alerted && time_step > 0;
-  if (adv) {
-    BatchRef B{h->bu, h->bv, h->bmfx, h->bmfy, h->bcflx, h->bcfly, h->bdivx, h->bdivy};
-    for (int l = 0; l < h->cfg.ntracers; ++l) {
-      const double* qo = h->q[h->q_old] + l * n3; double* qn = h->q[h->q_new] + l * n3;
-      run_ffsl_h(h, B, qo, h->ptf_lon, h->ptf_lat, dt_adv);   // ptf_* double as qmf_lon / qmf_lat
+  const double dt_adv = h->cfg.dt_adv;      // the update uses the namelist dt_adv, not batch%dt (adv_mod.F90:189,203,213,264)
+  bool any = false;
+  for (TrBatch& T : h->batches) {
+    const TrBatch& W = h->batches[T.wind_of];
+    bool alerted = false;
+    if (T.alert_last + T.alert_period <= time_step * h->cfg.dt_dyn) { T.alert_ring = true; alerted = true; }
+    T.advected = alerted && time_step > 0;
+    if (!T.advected) continue;
+    any = true;
+    BatchRef B{W.bu, W.bv, W.bmfx, W.bmfy, W.bcflx, W.bcfly, W.bdivx, W.bdivy};
+    for (int l = 0; l < T.ntr; ++l) {
+      const double* qo = T.q[T.q_old] + l * n3; double* qn = T.q[T.q_new] + l * n3;
+      run_ffsl_h(h, B, qo, h->ptf_lon, h->ptf_lat, T.dt);   // ptf_* double as qmf_lon / qmf_lat; inner step with batch%dt (ffsl_mod.F90:333)
       run_pole_sum(h, h->ptf_lat, h->pole_work + 2 * g.nlev, nullptr, 0);
       TrHArgs th{qo, h->old_m, S.m, h->ptf_lon, h->ptf_lat, h->pole_work + 2 * g.nlev, qn, dt_adv};
       LAUNCH(h, k_tracer_h, gridg(g, g.nlev), 128, 0, g, h->M, th);
       NegXArgs nx{qn, S.m, h->dflags};
       LAUNCH(h, k_negfill_x, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, nx);
-      TrVArgs tv{qn, S.m, h->bwe, h->bcflz, dt_adv, h->dflags};
+      TrVArgs tv{qn, S.m, W.bwe, W.bcflz, dt_adv, h->dflags};
       LAUNCH_LIM(h, k_tracer_v, gridg(g, 1), 128, (size_t)g.nlev * 128 * sizeof(double), g, tv);
       LonDampArgs ld{qn, h->lon_damp_wgt, 3};
       LAUNCH(h, k_lon_damp, dim3(g.je - g.jb + 1, g.nlev), 256, (size_t)2 * g.nlon * sizeof(double), g, ld);
     }
   }
-  return adv;
+  return any;
 }
-static void hydro_adv_finish(gmc_handle* h, int itime, bool advected) {
-  if (h->cfg.ntracers <= 0) return;
+static void hydro_adv_finish(gmc_handle* h, int itime) {
+  if (h->batches.empty()) return;
   const Geo& g = h->g;
-  if (advected) { int t = h->q_old; h->q_old = h->q_new; h->q_new = t; }
-  LAUNCH(h, k_copy3, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, h->st[itime].m, h->old_m);   // copy_old_m
+  for (TrBatch& T : h->batches) if (T.advected) { int t = T.q_old; T.q_old = T.q_new; T.q_new = t; T.advected = false; }
+  LAUNCH(h, k_copy3, dim3(g.je - g.jb + 1, g.nlev), 128, 0, g, h->st[itime].m, h->old_m);   // copy_old_m, every batch
 }
-static HaloSet tracer_halo_set(gmc_handle* b, int which /*0: q_old, 1: q_new*/, int with_pt_of = 0) {
+// tracer arrays of batch m that travel at an exchange point (which: 0 q_old, 1 q_new)
+static HaloSet tracer_halo_set(gmc_handle* b, int m, int which) {
   HaloSet s = halo_set();
   const size_t n3 = (size_t)b->g.plane * b->g.nlev;
-  if (b->cfg.ntracers > 0)
-    for (int l = 0; l < b->cfg.ntracers; ++l) halo_add(s, b->q[which ? b->q_new : b->q_old] + l * n3, b->g.nlev);
-  if (with_pt_of) halo_add(s, b->st[with_pt_of].pt, b->g.nlev);
+  const TrBatch& T = b->batches[m];
+  for (int l = 0; l < T.ntr; ++l) halo_add(s, T.q[which ? T.q_new : T.q_old] + l * n3, b->g.nlev);
   return s;
 }
 
@@ -392,32 +422,39 @@ static bool hydro_post_compute(gmc_handle* h, int nw, double dt, int time_step) 
 }
 
 // Maps the reference's log_error guards onto the ABI error text.
+static void hydro_flags_text(gmc_handle* h, int f) {
+  snprintf(h->err, sizeof(h->err), "%s%s%s%s%s",
+           f & 1 ? "cflx exceeds mesh%lon_halo_width; " : "", f & 2 ? "cfly exceeds 1; " : "", f & 4 ? "cflz exceeds range; " : "",
+           f & 8 ? "The pressure levels are not monotonic!; " : "", f & 16 ? "Negative tracer!; " : "");
+}
+// Reads the device guard word; non-zero -> error text, word cleared (reported once).
 static int hydro_check_flags(gmc_handle* h) {
   if (!h->dflags) return 0;
   int f = 0;
   if (cudaMemcpyAsync(&f, h->dflags, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) return 0;
   cudaStreamSynchronize(h->stream);
   if (!f) return 0;
-  snprintf(h->err, sizeof(h->err), "%s%s%s%s%s",
-           f & 1 ? "cflx exceeds mesh%lon_halo_width; " : "", f & 2 ? "cfly exceeds 1; " : "", f & 4 ? "cflz exceeds range; " : "",
-           f & 8 ? "The pressure levels are not monotonic!; " : "", f & 16 ? "Negative tracer!; " : "");
+  hydro_flags_text(h, f);
+  cudaMemsetAsync(h->dflags, 0, sizeof(int), h->stream);
   return 1;
 }
 
 static size_t host_cell_elems(const gmc_handle* h) {
   return (size_t)(h->cfg.nlon + 2 * h->cfg.hx) * ((h->g.je - h->g.jb + 1) + 2 * h->cfg.hy) * (h->cfg.nlev + 4);
 }
-static int hydro_set_tracers(gmc_handle* h, const double* q) {
-  if (h->cfg.ntracers <= 0 || !h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "no tracer batch configured"); return 1; }
+static int hydro_set_tracers(gmc_handle* h, int m, const double* q) {
+  if (m < 0 || m >= (int)h->batches.size()) { snprintf(h->err, sizeof(h->err), "no tracer batch %d configured", m); return 1; }
   const size_t n3 = (size_t)h->g.plane * h->g.nlev, host_n = host_cell_elems(h);
-  for (int l = 0; l < h->cfg.ntracers; ++l)
-    if (xfer(h, h->q[h->q_old] + l * n3, const_cast<double*>(q) + l * host_n, 0, 0)) return 1;
+  TrBatch& T = h->batches[m];
+  for (int l = 0; l < T.ntr; ++l)
+    if (xfer(h, T.q[T.q_old] + l * n3, const_cast<double*>(q) + l * host_n, 0, 0)) return 1;
   return 0;
 }
-static int hydro_get_tracers(gmc_handle* h, double* q) {
-  if (h->cfg.ntracers <= 0 || !h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "no tracer batch configured"); return 1; }
+static int hydro_get_tracers(gmc_handle* h, int m, double* q) {
+  if (m < 0 || m >= (int)h->batches.size()) { snprintf(h->err, sizeof(h->err), "no tracer batch %d configured", m); return 1; }
   const size_t n3 = (size_t)h->g.plane * h->g.nlev, host_n = host_cell_elems(h);
-  for (int l = 0; l < h->cfg.ntracers; ++l)
-    if (xfer(h, h->q[h->q_old] + l * n3, q + l * host_n, 0, 1)) return 1;
+  TrBatch& T = h->batches[m];
+  for (int l = 0; l < T.ntr; ++l)
+    if (xfer(h, T.q[T.q_old] + l * n3, q + l * host_n, 0, 1)) return 1;
   return 0;
 }

@@ -341,9 +341,19 @@ __global__ void __launch_bounds__(256) k_diag_partial(Geo g, DMesh M, DiagArgs a
     if (lane == 0) a.partial[(size_t)w * ns + slot] = r;
   }
 }
-__global__ void __launch_bounds__(1024) k_diag_final(const double* partial, int ns, double* out /*[7]*/) {
+// Block 7 carries the device guard word (the reference's log_error guards, hydro_check_flags) out with the sums:
+// out[7] = sum_b [bit b set] * 256^b, so that an all-reduce over <= 255 bands still tells which guards fired.
+__global__ void __launch_bounds__(1024) k_diag_final(const double* partial, int ns, double* out /*[8]*/, const int* flags) {
   __shared__ double sm[32];
   const int q = blockIdx.x;            // one block per diagnostic; the summation order within one is fixed
+  if (q == 7) {
+    if (threadIdx.x == 0) {
+      const int f = flags ? *flags : 0; double v = 0, w = 1;
+      for (int b = 0; b < 5; ++b, w *= 256.0) if (f & (1 << b)) v += w;
+      out[7] = v;
+    }
+    return;
+  }
   double s = 0;
   for (int x = threadIdx.x; x < ns; x += blockDim.x) s += partial[(size_t)q * ns + x];
   s = block_sum(s, sm);

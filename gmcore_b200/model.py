@@ -19,7 +19,8 @@ ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
                "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_step",
-               "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host"]
+               "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host",
+               "gmc_add_tracer_batch", "gmc_set_batch_tracers", "gmc_get_batch_tracers"]
 
 
 def load_library():
@@ -43,6 +44,9 @@ def load_library():
     lib.gmc_download_state.argtypes = [V, C.c_int, P, P, P, P]
     lib.gmc_set_tracers.argtypes = [V, P]
     lib.gmc_get_tracers.argtypes = [V, P]
+    lib.gmc_add_tracer_batch.argtypes = [V, C.c_int, C.c_double, I]
+    lib.gmc_set_batch_tracers.argtypes = [V, C.c_int, P]
+    lib.gmc_get_batch_tracers.argtypes = [V, C.c_int, P]
     lib.gmc_prepare_run.argtypes = [V, C.c_int]
     lib.gmc_time_integrate.argtypes = [V, C.c_int, C.c_int, C.c_double, C.c_int]
     lib.gmc_run_steps.argtypes = [V, I, I, I, C.c_int, P]
@@ -108,12 +112,26 @@ class GmcoreGPU:
         self._chk(self.lib.gmc_upload_state(self.h, itime, abi.dptr(ic["u_lon"]), abi.dptr(ic["v_lat"]),
                                             abi.dptr(ic["pt_or_gz"]), abi.dptr(ic.get("phs"))))
 
-    def set_tracers(self, q):
-        self._chk(self.lib.gmc_set_tracers(self.h, abi.dptr(q)))
+    def add_tracer_batch(self, ntracers, dt_adv):
+        """adv_add_tracer + adv_allocate_tracers (adv_mod.F90:314-418): one more batch; returns its index."""
+        b = C.c_int(-1)
+        self._chk(self.lib.gmc_add_tracer_batch(self.h, ntracers, float(dt_adv), C.byref(b)))
+        self._batch_ntr()[b.value] = ntracers
+        return b.value
 
-    def get_tracers(self):
-        q = np.zeros((self.host.cfg.ntracers,) + self.host.shape("cell"))
-        self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
+    def _batch_ntr(self):
+        if not hasattr(self, "batch_ntr"):
+            n = self.host.cfg.ntracers
+            self.batch_ntr = {0: n} if n > 0 else {}
+        return self.batch_ntr
+
+    def set_tracers(self, q, batch=0):
+        assert q.shape[0] == self._batch_ntr()[batch]
+        self._chk(self.lib.gmc_set_batch_tracers(self.h, batch, abi.dptr(q)))
+
+    def get_tracers(self, batch=0):
+        q = np.zeros((self._batch_ntr()[batch],) + self.host.shape("cell"))
+        self._chk(self.lib.gmc_get_batch_tracers(self.h, batch, abi.dptr(q)))
         return q
 
     # advection-only driver (gmcore_adv_driver.F90:84-88): set_uv(new) -> adv_run(new) -> time_advance
@@ -333,8 +351,8 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_upload_state(self.h, itime, abi.dptr(self._b(ic["u_lon"], "lon")), abi.dptr(self._b(ic["v_lat"], "lat")),
                                             abi.dptr(self._b(ic["pt_or_gz"], "cell")), abi.dptr(self._b(ic.get("phs"), "2d"))))
 
-    def set_tracers(self, q):
-        self.set_tracers_sliced(self.slice_tracers(q))
+    def set_tracers(self, q, batch=0):
+        self.set_tracers_sliced(self.slice_tracers(q), batch)
 
     # band slicing of global arrays is host set-up; the *_sliced entry points take this rank's rows directly
     # (what a banded Fortran host owns in the first place)
@@ -349,8 +367,9 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_set_static(self.h, abi.dptr(b["gzs"])))
         self._chk(self.lib.gmc_upload_state(self.h, itime, abi.dptr(b["u_lon"]), abi.dptr(b["v_lat"]), abi.dptr(b["pt_or_gz"]), abi.dptr(b["phs"])))
 
-    def set_tracers_sliced(self, qb):
-        self._chk(self.lib.gmc_set_tracers(self.h, abi.dptr(qb)))
+    def set_tracers_sliced(self, qb, batch=0):
+        assert qb.shape[0] == self._batch_ntr()[batch]
+        self._chk(self.lib.gmc_set_batch_tracers(self.h, batch, abi.dptr(qb)))
 
     def band_shape(self, loc):
         s = list(self.host.shape(loc))
@@ -366,9 +385,9 @@ class GmcoreBand(GmcoreGPU):
         self._chk(self.lib.gmc_get_field(self.h, itime, name.encode(), abi.dptr(a)))
         return a
 
-    def get_tracers(self):
-        q = np.zeros((self.host.cfg.ntracers,) + self.band_shape("cell"))
-        self._chk(self.lib.gmc_get_tracers(self.h, abi.dptr(q)))
+    def get_tracers(self, batch=0):
+        q = np.zeros((self._batch_ntr()[batch],) + self.band_shape("cell"))
+        self._chk(self.lib.gmc_get_batch_tracers(self.h, batch, abi.dptr(q)))
         return q
 
     def download_state(self, itime=None, out=None):
@@ -439,9 +458,12 @@ class GmcoreBandGroup:
         for b in self.bands:
             b.set_state(ic)
 
-    def set_tracers(self, q):
+    def add_tracer_batch(self, ntracers, dt_adv):
+        return [b.add_tracer_batch(ntracers, dt_adv) for b in self.bands][0]
+
+    def set_tracers(self, q, batch=0):
         for b in self.bands:
-            b.set_tracers(q)
+            b.set_tracers(q, batch)
 
     def prepare_run(self):
         self.lead.prepare_run()
@@ -462,10 +484,10 @@ class GmcoreBandGroup:
             scatter_rows(self.host, b.cfg, b.field(name), g, loc)
         return g
 
-    def get_tracers(self):
-        g = np.zeros((self.host.cfg.ntracers,) + self.host.shape("cell"))
+    def get_tracers(self, batch=0):
+        g = np.zeros((self.lead._batch_ntr()[batch],) + self.host.shape("cell"))
         for b in self.bands:
-            qb = b.get_tracers()
+            qb = b.get_tracers(batch)
             for l in range(g.shape[0]):
                 scatter_rows(self.host, b.cfg, qb[l], g[l], "cell")
         return g

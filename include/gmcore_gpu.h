@@ -106,6 +106,15 @@ int gmc_download_state(gmc_handle* h, int itime, double* u_lon, double* v_lat,
 int gmc_set_tracers(gmc_handle* h, const double* q);
 int gmc_get_tracers(gmc_handle* h, double* q);
 
+/* More advection batches (block%adv_batches(:)): adv_add_tracer + adv_allocate_tracers (adv_mod.F90:314-418).
+ * Batch 0 is the one the config struct describes (ntracers, dt_adv); each call adds a 'cell' batch of `ntracers`
+ * tracers advected every `dt_adv` seconds (nstep = dt_adv / dt_dyn wind samples, adv_batch_mod.F90:73-149,239-252)
+ * and returns its index.  Call after gmc_create and before gmc_prepare_run, on every band.  adv_run
+ * (adv_mod.F90:165-312) then loops over the batches in this order.  q is (lon,lat,lev,ntracers) of that batch. */
+int gmc_add_tracer_batch(gmc_handle* h, int ntracers, double dt_adv, int* batch);
+int gmc_set_batch_tracers(gmc_handle* h, int batch, const double* q);
+int gmc_get_batch_tracers(gmc_handle* h, int batch, double* q);
+
 /* The pre-loop block of gmcore_run (gmcore_mod.F90:101-136): filters -> u_f,
  * v_f, phs_f|gz_f; copy_old_m; adv_accum_wind; operators_prepare(all). */
 int gmc_prepare_run(gmc_handle* h, int old_idx);

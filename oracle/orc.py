@@ -32,6 +32,9 @@ def _load(fast):
     lib.orc_upload_state.argtypes = [C.c_void_p, C.c_int, P, P, P, P]
     lib.orc_set_tracers.argtypes = [C.c_void_p, P]
     lib.orc_get_tracers.argtypes = [C.c_void_p, P]
+    lib.orc_add_tracer_batch.argtypes = [C.c_void_p, C.c_int, C.c_double]
+    lib.orc_set_batch_tracers.argtypes = [C.c_void_p, C.c_int, P]
+    lib.orc_get_batch_tracers.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_adv_prescribe.argtypes = [C.c_void_p, C.c_int, P, P]
     lib.orc_adv_step.argtypes = [C.c_void_p]
     lib.orc_prepare_run.argtypes = [C.c_void_p]
@@ -64,6 +67,7 @@ class Oracle:
         self.lib = _load(fast)
         self.host = host
         self.h = self.lib.orc_create(C.addressof(host.cfg), C.addressof(host.mesh_vectors), _dp(host.vec["full_lat_deg"]))
+        self.batch_ntr = {0: host.cfg.ntracers} if host.cfg.ntracers > 0 else {}
         for which, (ngl, wl, ldl, nga, wa, lda) in enumerate(host.filters):
             self.lib.orc_set_filters(self.h, which, ngl.ctypes.data_as(C.POINTER(C.c_int)), _dp(wl), ldl,
                                      nga.ctypes.data_as(C.POINTER(C.c_int)), _dp(wa), lda)
@@ -72,13 +76,19 @@ class Oracle:
         self.lib.orc_set_static(self.h, _dp(ic["gzs"]))
         self.lib.orc_upload_state(self.h, itime, _dp(ic["u_lon"]), _dp(ic["v_lat"]), _dp(ic["pt_or_gz"]), _dp(ic.get("phs")))
 
-    def set_tracers(self, q):
-        self.lib.orc_set_tracers(self.h, _dp(q))
+    def add_tracer_batch(self, ntracers, dt_adv):
+        """adv_add_tracer + adv_allocate_tracers (adv_mod.F90:314-418); returns the batch index."""
+        b = self.lib.orc_add_tracer_batch(self.h, ntracers, float(dt_adv))
+        self.batch_ntr[b] = ntracers
+        return b
 
-    def get_tracers(self):
-        n = self.host.cfg.ntracers
-        q = np.zeros((n,) + self.host.shape("cell"))
-        self.lib.orc_get_tracers(self.h, _dp(q))
+    def set_tracers(self, q, batch=0):
+        assert q.shape[0] == self.batch_ntr[batch]
+        self.lib.orc_set_batch_tracers(self.h, batch, _dp(q))
+
+    def get_tracers(self, batch=0):
+        q = np.zeros((self.batch_ntr[batch],) + self.host.shape("cell"))
+        self.lib.orc_get_batch_tracers(self.h, batch, _dp(q))
         return q
 
     # advection-only driver (gmcore_adv_driver.F90:84-88)

@@ -41,6 +41,16 @@ void copy_interior_full3(const Mesh& mesh, A3& dst, const double* src, bool full
 
 extern "C" {
 
+// adv_add_tracer + adv_allocate_tracers_1 (adv_mod.F90:314-418); returns the batch index
+int orc_add_tracer_batch(void* h, int ntracers, double dt) {
+  Model* m = (Model*)h; const Mesh& mesh = m->b.mesh;
+  m->b.adv_batches.emplace_back();
+  AdvBatch& B = m->b.adv_batches.back();
+  B.init(mesh, dt, m->b.cfg.dt_dyn, false);
+  B.alloc_tracers(mesh, ntracers);
+  B.alert_period = dt; B.alert_last = -dt;
+  return (int)m->b.adv_batches.size() - 1;
+}
 void* orc_create(const gmc_config* cfg, const gmc_mesh_vectors* mv, const double* full_lat_deg) {
   Model* m = new Model();
   m->b.cfg = *cfg;
@@ -49,12 +59,7 @@ void* orc_create(const gmc_config* cfg, const gmc_mesh_vectors* mv, const double
   for (int i = 1; i <= 3; ++i) { m->b.state[i].init(mesh, *cfg); m->b.tend[i].init(mesh); }
   mesh.alloc2(m->b.st.gzs, true);
   m->b.adv_batch_mass.init(mesh, cfg->dt_dyn, cfg->dt_dyn, true);
-  if (cfg->ntracers > 0) {
-    m->b.has_tracers = true;
-    m->b.adv_batch.init(mesh, cfg->dt_adv, cfg->dt_dyn, false);
-    m->b.adv_batch.alloc_tracers(mesh, cfg->ntracers);
-    m->alert_period = cfg->dt_adv; m->alert_last = -cfg->dt_adv;
-  }
+  if (cfg->ntracers > 0) orc_add_tracer_batch(m, cfg->ntracers, cfg->dt_adv);
   m->div_damp_init();
   m->lon_damp_init(full_lat_deg);
   return m;
@@ -87,8 +92,8 @@ int orc_upload_state(void* h, int itime, const double* u, const double* v, const
   }
   return 0;
 }
-int orc_set_tracers(void* h, const double* q) {
-  Model* m = (Model*)h; AdvBatch& B = m->b.adv_batch;
+int orc_set_batch_tracers(void* h, int batch, const double* q) {
+  Model* m = (Model*)h; AdvBatch& B = m->b.adv_batches.at(batch);
   for (int l = 0; l < B.ntracers; ++l) {
     A3& a = B.q[B.old - 1][l];
     std::memcpy(a.d.data(), q + (size_t)l * a.d.size(), a.d.size() * sizeof(double));
@@ -114,14 +119,16 @@ int orc_adv_step(void* h) {
   m->time_advance();
   return m->b.error.empty() ? 0 : 1;
 }
-int orc_get_tracers(void* h, double* q) {
-  Model* m = (Model*)h; AdvBatch& B = m->b.adv_batch;
+int orc_get_batch_tracers(void* h, int batch, double* q) {
+  Model* m = (Model*)h; AdvBatch& B = m->b.adv_batches.at(batch);
   for (int l = 0; l < B.ntracers; ++l) {
     A3& a = B.q[B.old - 1][l];
     std::memcpy(q + (size_t)l * a.d.size(), a.d.data(), a.d.size() * sizeof(double));
   }
   return 0;
 }
+int orc_set_tracers(void* h, const double* q) { return orc_set_batch_tracers(h, 0, q); }
+int orc_get_tracers(void* h, double* q) { return orc_get_batch_tracers(h, 0, q); }
 int orc_prepare_run(void* h) { Model* m = (Model*)h; m->prepare_run(m->old_idx); return m->b.error.empty() ? 0 : 1; }
 
 // n x { time_integrate; time_advance; diagnose(old) }  (gmcore_mod.F90:138-144)

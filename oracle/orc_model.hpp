@@ -16,7 +16,6 @@ struct Model {
   std::vector<double> c_lon, c_lat;            // div_damp coefficients (j,k)
   std::vector<double> wgt_full_lat;            // lon_damp latitude profile
   int old_idx = 1, new_idx = 2, time_step = 0;
-  double alert_last = 0, alert_period = 0; bool alert_ring = false;   // 'moist' batch alert
 
   double& clon(int j, int k) { return c_lon[(size_t)(k - 1) * b.mesh.nlat + (j - 1)]; }
   double& clat(int j, int k) { return c_lat[(size_t)(k - 1) * b.mesh.nhalf + (j - 1)]; }
@@ -337,17 +336,18 @@ struct Model {
 
   // ---- adv_mod.F90:420-455 ----------------------------------------------------------
   void adv_accum_wind(int itime) {
-    if (!b.has_tracers) return;
     State& s = b.state[itime];
-    accum_uv_cell(b, b.adv_batch, s.u_f, s.v_f, 0.0, false);
-    accum_mf_cell(b.adv_batch, s.mfx_lon, s.mfy_lat);
-    if (b.mesh.nlev > 1) accum_we_lev(b, b.adv_batch, s.we_lev, s.m_lev, 0.0, false);
+    for (AdvBatch& B : b.adv_batches) {
+      accum_uv_cell(b, B, s.u_f, s.v_f, 0.0, false);
+      accum_mf_cell(B, s.mfx_lon, s.mfy_lat);
+      if (b.mesh.nlev > 1) accum_we_lev(b, B, s.we_lev, s.m_lev, 0.0, false);
+    }
   }
 
-  // time_mod.F90:270-291 for the single tracer batch alert; clock = time_step * dt_dyn
-  bool time_is_alerted() {
+  // time_mod.F90:270-291 for the alert of one batch; clock = time_step * dt_dyn
+  bool time_is_alerted(AdvBatch& B) {
     double curr = time_step * b.cfg.dt_dyn;
-    if (alert_last + alert_period <= curr) { alert_ring = true; return true; }
+    if (B.alert_last + B.alert_period <= curr) { B.alert_ring = true; return true; }
     return false;
   }
 
@@ -355,10 +355,10 @@ struct Model {
   void adv_run(int itime) {
     const Mesh& mesh = b.mesh;
     adv_accum_wind(itime);
-    if (!b.has_tracers) return;
-    AdvBatch& B = b.adv_batch; State& st = b.state[itime];
-    const double dt_adv = b.cfg.dt_adv;
-    bool alerted = time_is_alerted();
+    State& st = b.state[itime];
+    const double dt_adv = b.cfg.dt_adv;      // the namelist dt_adv, not batch%dt (adv_mod.F90:189)
+    for (AdvBatch& B : b.adv_batches) {      // do m = 1, size(block%adv_batches) (adv_mod.F90:165)
+    bool alerted = time_is_alerted(B);
     if (alerted && time_step > 0) {
       for (int l = 0; l < B.ntracers; ++l) {
         A3& qo = B.q[B.old - 1][l]; A3& qn = B.q[B.nw - 1][l];
@@ -434,6 +434,7 @@ struct Model {
       std::swap(B.old, B.nw);
     }
     copy_arr(B.old_m, st.m);
+    }
   }
 
   // ---- gmcore_mod.F90:213-341 ---------------------------------------------------------
@@ -498,7 +499,7 @@ struct Model {
       filter_full_lat(mesh, b.big_filter, s.gz, &s.gz_f, 1, mesh.nlev);
       fill_halo(mesh, s.gz_f, true);
     }
-    if (b.has_tracers) copy_arr(b.adv_batch.old_m, s.m);
+    for (AdvBatch& B : b.adv_batches) copy_arr(B.old_m, s.m);
     copy_arr(b.adv_batch_mass.old_m, s.m);
     adv_accum_wind(old);
     operators_prepare_1(s, b.cfg.dt_dyn);
@@ -514,7 +515,7 @@ struct Model {
   }
   // time_advance (time_mod.F90:128-159)
   void time_advance() {
-    if (alert_ring) { alert_last = time_step * b.cfg.dt_dyn; alert_ring = false; }
+    for (AdvBatch& B : b.adv_batches) if (B.alert_ring) { B.alert_last = time_step * b.cfg.dt_dyn; B.alert_ring = false; }
     std::swap(old_idx, new_idx);
     time_step += 1;
   }

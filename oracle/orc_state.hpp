@@ -108,6 +108,7 @@ inline void filter_half_lat(const Mesh& m, const Filter& f, A3& x, A3* y, int k0
 
 // adv_batch_type, loc='cell' (adv_batch_mod.F90:73-149)
 struct AdvBatch {
+  double alert_last = 0, alert_period = 0; bool alert_ring = false;   // time_mod.F90:253-291 alert named after the batch
   bool dynamic = false; int nstep = 0, uv_step = 0, we_step = 0, mf_step = 0, old = 1, nw = 2; double dt = 0;
   int ntracers = 0;
   A3 old_m, mfx, mfy, m_lev, u, v, we, cflx, cfly, cflz, divx, divy, qx, qy, qlx, qly, dqx, dqy, q6x, q6y;
@@ -137,8 +138,7 @@ struct Block {
   Static st;
   Filter big_filter, small_filter1, small_filter2;
   AdvBatch adv_batch_mass;
-  bool has_tracers = false;
-  AdvBatch adv_batch;          // the single non-dynamic 'moist'-like batch
+  std::vector<AdvBatch> adv_batches;   // block%adv_batches(:) (adv_mod.F90:314-418): non-dynamic 'cell' batches, each with its own samples
   std::string error;           // first log_error raised (reference aborts)
   void fail(const std::string& s) { if (error.empty()) error = s; }
 };

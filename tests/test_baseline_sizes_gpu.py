@@ -1,0 +1,197 @@
+"""GPU parity at the BASELINE.json grid sizes and on the code paths only they reach.
+
+The small-grid tests (test_swm_gpu.py, test_hydro_gpu.py) never meet: zonal filter rows wider than 47
+taps (C2: 161, C3: 85, C5: 247 taps with max_hn = 123 shared-memory staging), |cflx| >= 1 gathers and
+whole-cell segment sums of the FFSL x sweep INSIDE the dynamics (polar rows at 0.25 deg), the out-of-window
+gather of the RK4 departure search, and the dt_adv > dt_dyn sampling cadence of a tracer batch (SURVEY T8,
+adv_batch_mod.F90:239-252).  Every case compares the CUDA path (through the C ABI) with the CPU oracle on
+identical inputs: per-step relative L2 <= 1e-12 on every prognostic field (BASELINE.json north_star).
+
+Reference loops exercised: filter_mod.F90:57-91 (wide rows), ffsl_mod.F90:831-851 (|cfl| >= 1 branch),
+adv_batch_mod.F90:256-335 (RK4 gathers), adv_mod.F90:165-312 (batch loop).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from test_hydro_gpu import DERIVED, check, pair, start
+from util import PROGNOSTIC_HYDRO, PROGNOSTIC_SWM, assert_diag_close, make_pair, rel_l2, smooth_tracer
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-12
+# work arrays of the last stage (mass batch CFL numbers, FFSL intermediates and fluxes, forward-pass tendencies)
+WORK_BATCH = [("cflx", "lon"), ("cfly", "lat"), ("cflz", "cell+lev"), ("divx", "cell"), ("divy", "cell"),
+              ("qx", "cell"), ("qy", "cell")]
+
+
+def mem_available_gb():
+    try:
+        return [int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0] / 1e6
+    except Exception:
+        return 0.0
+
+
+def work_errors(host, orc, gpu):
+    """rel L2 of the last stage's work arrays.  Oracle side: mass-batch arrays; ptf_* of the star state of the
+    last wrfrk3 stage (state 3); du / dpt of tend1 = tend(old at the time of the step) = tend(orc.new_index now)."""
+    errs = {}
+    for name, loc in WORK_BATCH:
+        a = host.interior(gpu.field(name), loc); b = host.interior(orc.field(name), loc)
+        if name == "cflz":
+            a, b = a[1:-1], b[1:-1]
+        errs[name] = rel_l2(a, b)
+    for name, loc in (("ptf_lon", "lon"), ("ptf_lat", "lat")):
+        errs[name] = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name, 3), loc))
+    for name, loc in (("du", "lon"), ("dpt", "cell")):
+        errs[name] = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name, orc.new_index), loc))
+    return errs
+
+
+def test_c2_mountain_zonal_flow_720x360(gpu_required):
+    """BASELINE configs[1]: Williamson 5 at 0.5 deg, dt 75 s: 161-tap polar rows, hx = 80."""
+    host, ic, orc, gpu = make_pair(720, 360, 1, 75.0, "mountain_zonal_flow")
+    assert host.hx >= 60, host.hx
+    orc.prepare_run(); gpu.prepare_run()
+    assert_diag_close(gpu.diagnose(), orc.diagnose())
+    for step in range(3):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        for name, loc in PROGNOSTIC_SWM + [("u_f", "lon"), ("v_f", "lat"), ("gz_f", "cell"), ("pv", "vtx")]:
+            e = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name), loc))
+            assert e <= TOL, (step, name, e)
+        assert_diag_close(dg, do)
+    gpu.close()
+
+
+def test_c3_baroclinic_wave_360x180x32(gpu_required):
+    """BASELINE configs[2]: JW baroclinic wave at 1 deg x L32, dt 150 s (85-tap rows), with the qv-like tracer."""
+    host, ic, orc, gpu = start(360, 180, 32, 150.0, "baroclinic_wave")
+    check(host, orc, gpu, [f for f in DERIVED if f[0] != "we_lev"], TOL, "prepare_run")
+    for step in range(2):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
+        check(host, orc, gpu, DERIVED, 1e-10, f"step {step} derived", loose={"pv_lon": 1e-7})
+        qg, qo = gpu.get_tracers(), orc.get_tracers()
+        assert rel_l2(host.interior(qg[0], "cell"), host.interior(qo[0], "cell")) <= TOL, f"step {step} tracer"
+        assert_diag_close(dg, do)
+    gpu.close()
+
+
+@pytest.mark.parametrize("nlon,nlat,nlev,dt", [(360, 180, 32, 150.0), (1440, 720, 4, 30.0)])
+def test_work_arrays_of_the_last_stage(gpu_required, nlon, nlat, nlev, dt):
+    """The WORK list (CFL numbers, FFSL intermediates, fluxes, forward tendencies) against the oracle, without a
+    tracer batch (it would reuse qx / qy / ptf_* after the dynamics).  The 1440x720 case is the full-width one:
+    247-tap filter rows (max_hn = 123), |cflx| >= 1 on the polar rows inside the dynamics -- the same row length
+    as BASELINE configs[4] at 1/8 of the levels (equal_eta coordinate)."""
+    if nlon == 1440 and mem_available_gb() < 40:
+        pytest.skip("needs ~25 GB of host memory for the oracle")
+    host, ic, orc, gpu = start(nlon, nlat, nlev, dt, "baroclinic_wave", ntracers=0)
+    if nlon == 1440:
+        assert host.hx >= 100, host.hx
+    for step in range(2):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
+        errs = work_errors(host, orc, gpu)
+        bad = {k: v for k, v in errs.items() if not v <= 1e-11}
+        assert not bad, f"step {step}: {bad}"
+        assert_diag_close(dg, do)
+    if nlon == 1440:      # the case must actually reach the |cflx| >= 1 branch
+        cflx = host.interior(gpu.field("cflx"), "lon")
+        assert np.abs(cflx).max() >= 1.0, np.abs(cflx).max()
+    gpu.close()
+
+
+def test_fullwidth_with_tracer_1440x720x4(gpu_required):
+    """Full-width rows with the tracer batch on: FFSL x sweeps with |cflx| >= 1 on the tracer, negative filling,
+    lon_damp on 1440-point rows."""
+    if mem_available_gb() < 40:
+        pytest.skip("needs ~25 GB of host memory for the oracle")
+    host, ic, orc, gpu = start(1440, 720, 4, 30.0, "baroclinic_wave")
+    for step in range(3):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
+        qg, qo = gpu.get_tracers(), orc.get_tracers()
+        assert rel_l2(host.interior(qg[0], "cell"), host.interior(qo[0], "cell")) <= TOL, f"step {step} tracer"
+        assert_diag_close(dg, do)
+    gpu.close()
+
+
+@pytest.mark.parametrize("mult", [2, 3])
+def test_dt_adv_multiple_of_dt_dyn(gpu_required, mult):
+    """T8 cadence: nstep = dt_adv / dt_dyn wind samples are averaged over nstep + 1 calls, the CFL numbers are
+    recomputed only when the counter wraps, the batch advects when its alert rings (adv_batch_mod.F90:239-252,
+    adv_mod.F90:166, time_mod.F90:270-291)."""
+    host, ic, orc, gpu = start(64, 33, 8, 600.0, "baroclinic_wave", dt_adv=mult * 600.0, ntracers=2)
+    moved = 0
+    prev = gpu.get_tracers()
+    for step in range(7):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
+        qg, qo = gpu.get_tracers(), orc.get_tracers()
+        for l in range(2):
+            assert rel_l2(host.interior(qg[l], "cell"), host.interior(qo[l], "cell")) <= TOL, f"step {step} tracer {l}"
+        moved += int(not np.array_equal(qg, prev)); prev = qg
+        assert_diag_close(dg, do)
+    assert 0 < moved < 7, moved        # advected on some steps only
+    gpu.close()
+
+
+def test_two_tracer_batches(gpu_required):
+    """adv_run loops over block%adv_batches (adv_mod.F90:165): batch 0 (1 tracer) and batch 1 (2 tracers) at
+    dt_adv = dt_dyn -- same wind samples, shared on the device, separate in the oracle -- plus batch 2 with its own
+    cadence (dt = 2 dt_dyn; the update still uses the namelist dt_adv, adv_mod.F90:189, a quirk both sides keep)."""
+    host, ic, orc, gpu = make_pair(64, 33, 8, 600.0, "baroclinic_wave")
+    for m in (orc, gpu):
+        assert m.add_tracer_batch(2, 600.0) == 1
+        assert m.add_tracer_batch(1, 1200.0) == 2
+    qs = [smooth_tracer(host, 1), smooth_tracer(host, 2)[::-1].copy(), 2.0 * smooth_tracer(host, 1)]
+    for b, q in enumerate(qs):
+        orc.set_tracers(q, b); gpu.set_tracers(q, b)
+    orc.prepare_run(); gpu.prepare_run()
+    for step in range(6):
+        dg = gpu.run_steps(1); do = orc.run_steps(1)
+        check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
+        for b in range(3):
+            qg, qo = gpu.get_tracers(b), orc.get_tracers(b)
+            for l in range(qg.shape[0]):
+                e = rel_l2(host.interior(qg[l], "cell"), host.interior(qo[l], "cell"))
+                assert e <= TOL, (step, b, l, e)
+        assert_diag_close(dg, do)
+    # batches 0 and 1 saw the same winds: the first tracer of smooth_tracer(2) reversed is tracer 1 of batch 1
+    q0 = gpu.get_tracers(0)[0]; q1 = gpu.get_tracers(1)[1]
+    assert np.array_equal(q0, q1)
+    gpu.close()
+
+
+@pytest.mark.skipif(os.environ.get("GMCORE_SLOW") != "1", reason="slow: one BASELINE configs[4] step on the CPU oracle (~80 GB, minutes); set GMCORE_SLOW=1")
+def test_c5_one_step_against_the_oracle(gpu_required):
+    """One 1440x720x32 step (the configuration the metric is quoted on) against the oracle."""
+    print("MemAvailable GB:", mem_available_gb())
+    if mem_available_gb() < 110:
+        pytest.skip("needs ~90 GB of host memory")
+    host, ic, orc, gpu = start(1440, 720, 32, 30.0, "baroclinic_wave")
+    dg = gpu.run_steps(1); do = orc.run_steps(1)
+    check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, "step 0")
+    qg, qo = gpu.get_tracers(), orc.get_tracers()
+    assert rel_l2(host.interior(qg[0], "cell"), host.interior(qo[0], "cell")) <= TOL
+    assert_diag_close(dg, do)
+    gpu.close()
+
+
+def test_guards_reach_the_host_through_time_integrate_and_diagnose(gpu_required):
+    """The reference stops in log_error when |cfly| > 1 (adv_batch_mod.F90:366-369).  The Fortran shim's loop is
+    gmc_time_integrate + gmc_diagnose (fortran/gmcore_gpu_mod.F90): the device guard word must come back through
+    gmc_diagnose as a non-zero return with the guard text, and be cleared once reported."""
+    from gmcore_b200.host import Host
+    from gmcore_b200.model import GmcoreGPU
+    host = Host(64, 33, 8, 600.0, "baroclinic_wave")
+    ic = host.initial_condition()
+    ic["v_lat"][...] = 3000.0        # |cfly| = 3000 * 600 / 6.2e5 m ~ 3
+    gpu = GmcoreGPU(host); gpu.set_state(ic)
+    gpu.set_tracers(smooth_tracer(host, 1))
+    gpu.prepare_run()
+    gpu.time_integrate()
+    with pytest.raises(RuntimeError, match="cfly exceeds 1"):
+        gpu.diagnose()
+    gpu.close()
