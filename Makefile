@@ -36,7 +36,7 @@ oracle/_build/liboracle.so: $(ORCSRC) $(ORCHDR)
 	$(CXX) $(CXXFLAGS) -shared -o $@ $(ORCSRC)
 oracle/_build/liboracle_fast.so: $(ORCSRC) $(ORCHDR)
 	@mkdir -p oracle/_build
-	$(CXX) -std=c++17 -O3 -march=native -fPIC -fno-fast-math -fopenmp -DORC_OPENMP -shared -o $@ $(ORCSRC)
+	$(CXX) -std=c++17 -O3 -march=x86-64-v3 -fPIC -fno-fast-math -fopenmp -DORC_OPENMP -DORC_OPENMP_LOOPS -shared -o $@ $(ORCSRC)
 
 clean:
 	rm -rf $(LIBDIR) oracle/_build

@@ -39,8 +39,8 @@ WORKLOADS = {
 # BASELINE.json quotes its metric on the 0.25 deg x 32-level baroclinic wave; it fits one B200
 # (about 27 GB of device state), so that is the N=1 workload.
 DEFAULT_WORKLOAD = "bw_1440x720x32"
-# CPU sample for workloads whose oracle state (~80 GB at 0.25 deg) does not fit / finish in
-# bounded time: same case and levels on a coarser grid, cost scaled by the column count.
+# Fallback CPU sample ONLY when the host cannot hold the oracle state (~80 GB at 0.25 deg): same case and
+# levels on a coarser grid, cost scaled by the cell count, and labelled as such in the line.
 CPU_SAMPLE = {"bw_1440x720x32": "bw_360x180x32"}
 
 # Algorithmic 3-D r8 array passes per launch of each kernel (SURVEY.md §8d / DESIGN.md):
@@ -163,66 +163,82 @@ def pinned_like(a):
     return n, t
 
 
-def cpu_baseline(wl, name, budget_s=20.0):
-    """Time the CPU restatement (oracle, -O3 -march=native build) on a bounded sample, on ALL host cores.
+def bench_tracer(host):
+    """The advected tracer of the timed workloads: a positive, smooth specific-humidity-like field (wavenumber-2 in
+    longitude, moist tropics, decaying upwards) so that the FFSL limiter, the negative-filling sweeps and lon_damp see
+    real gradients (an all-zero field would be a best case)."""
+    q = np.zeros((host.cfg.ntracers,) + host.shape("cell"))
+    lon = host.vec["full_lon"][host.hx:host.hx + host.nlon]
+    lat = host.vec["full_lat"][host.hy:host.hy + host.nlat]
+    for l in range(host.cfg.ntracers):
+        f = 1.0e-2 * (np.cos(lat)[:, None] ** 2 * (1.0 + 0.5 * np.sin((l + 2) * lon)[None, :]) + 0.05)
+        for k in range(host.nlev):
+            host.interior(q[l], "cell")[k] = f * ((k + 1.0) / host.nlev) ** 2
+    return q
 
-    The restatement is scalar; the reference parallelises by MPI over latitude bands.  The stand-in is
-    one independent single-thread replica of the sample per core (tools/cpu_worker.py), run
-    concurrently: aggregate simulated days per day = the perfect-scaling upper bound of an MPI run on
-    the same cores (no halo exchange, no load imbalance), memory-bandwidth contention included.
-    """
-    if name in CPU_SAMPLE:
-        sname = CPU_SAMPLE[name]; swl = WORKLOADS[sname]
-        cb = cpu_baseline(swl, sname, budget_s)
-        scale = (wl["nlon"] * wl["nlat"] * wl["nlev"]) / (swl["nlon"] * swl["nlat"] * swl["nlev"])
-        cb["s_per_step"] *= scale
-        cb["value"] = wl["dt"] / cb["s_per_step"]
-        cb["sample"] += f"; cost per step scaled x{scale:g} by cell count to {name} (dt={wl['dt']} s)"
-        return cb
-    cores = os.cpu_count() or 1
+
+def oracle_mem_gb(wl):
+    """Host memory of one oracle instance: ~225 halo'd r8 arrays (the reference's own allocation)."""
+    hx = 130 if wl["nlon"] >= 1440 else 90
+    return 225 * (wl["nlon"] + 2 * hx) * (wl["nlat"] + 4) * (wl["nlev"] + 4) * 8 / 1e9 + 1.0
+
+
+def mem_available_gb():
     try:
-        avail_gb = [int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0] / 1e6
+        return [int(l.split()[1]) for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0] / 1e6
     except Exception:
-        avail_gb = 8.0
-    per_gb = 220 * wl["nlon"] * wl["nlat"] * (wl["nlev"] + 4) * 8 * 1.35 / 1e9 + 0.5    # ~220 halo'd arrays per replica
-    workers = int(max(1, min(cores, 0.6 * avail_gb / per_gb)))
-    env = dict(os.environ, OMP_NUM_THREADS="1")
+        return 8.0
+
+
+def cpu_baseline(wl, name, budget_s=20.0, min_steps=2, max_steps=200):
+    """Time the CPU restatement (oracle/, the -O3 OpenMP build liboracle_fast.so) on the host cores.
+
+    ONE instance of the named workload itself on ALL host cores: the level loops of the restatement are OpenMP-
+    parallel (oracle/orc_core.hpp ORC_PAR), the shared-memory stand-in for the reference's MPI decomposition.  The
+    sample is bounded in STEPS (1 warm-up + >= min_steps timed), never in grid size, unless the host cannot hold the
+    ~80 GB oracle state of the 0.25 degree case: then the same case on the coarser grid of CPU_SAMPLE is timed and the
+    line says so ("workload_timed" / "scaled_to")."""
+    cores = os.cpu_count() or 1
+    timed_name, twl, scale = name, wl, 1.0
+    if oracle_mem_gb(wl) > 0.8 * mem_available_gb() and name in CPU_SAMPLE:
+        timed_name = CPU_SAMPLE[name]; twl = WORKLOADS[timed_name]
+        scale = (wl["nlon"] * wl["nlat"] * wl["nlev"]) / (twl["nlon"] * twl["nlat"] * twl["nlev"])
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores), OMP_PROC_BIND="close", OMP_PLACES="cores")
     t0 = time.perf_counter()
-    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tools", "cpu_worker.py"), name, str(budget_s)],
-                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env) for _ in range(workers)]
-    rate = 0.0; nsteps = []
-    for p in procs:
-        out, _ = p.communicate()
-        try:
-            n, el, _rss = out.split()[-3:]
-            rate += int(n) / float(el); nsteps.append(int(n))
-        except Exception:
-            pass
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cpu_worker.py"), timed_name, str(budget_s), str(min_steps), str(max_steps)],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env)
     wall = time.perf_counter() - t0
-    if not nsteps and env.get("ORC_FAST", "1") == "1":
-        # the -march=native build was made on another CPU model: fall back to the portable -O2 build
-        os.environ["ORC_FAST"] = "0"
-        try:
-            return cpu_baseline(wl, name, budget_s)
-        finally:
-            os.environ.pop("ORC_FAST", None)
-    if not nsteps:
-        raise RuntimeError("CPU baseline workers failed")
-    s_per_step = 1.0 / rate            # aggregate: seconds of wall clock per simulated step
-    return {"value": wl["dt"] / s_per_step, "unit": "simulated days/day", "cores": len(nsteps), "kind": "port",
-            "sample": f"{len(nsteps)} concurrent single-thread replicas x {min(nsteps)}-{max(nsteps)} steps of {name} after 1 warm-up step "
-                      f"({wall:.1f} s wall incl. set-up; host has {cores} cores)", "s_per_step": s_per_step}
+    try:
+        n, el, rss, threads = p.stdout.split()[-4:]
+        n, el, rss, threads = int(n), float(el), float(rss), int(threads)
+    except Exception:
+        raise RuntimeError("CPU baseline worker failed: " + p.stderr[-300:])
+    s_per_step = el / n * scale
+    sample = (f"1 instance of {timed_name} on {threads} OpenMP threads (liboracle_fast.so: g++ -O3 -march=x86-64-v3 -fopenmp, "
+              f"level loops parallel): {n} steps timed after 1 warm-up step, {el / n:.2f} s/step, rss {rss / 1024:.1f} GB, "
+              f"{wall:.0f} s wall incl. set-up; host has {cores} cores")
+    if scale != 1.0:
+        sample += f"; host memory too small for {name} ({oracle_mem_gb(wl):.0f} GB): cost per step scaled x{scale:g} by cell count"
+    return {"value": wl["dt"] / s_per_step, "unit": "simulated days/day", "cores": threads, "kind": "port", "sample": sample,
+            "s_per_step": s_per_step, "workload_timed": timed_name, "steps_timed": n}
 
 
 def run_reference(args, name, wl, rank, world, out=sys.stdout):
+    """--impl reference: the reference's CPU implementation of the path.  The Fortran itself cannot be built (no
+    Fortran compiler, MPI or netCDF on this image or on the GPU box -- probed), so this is the
+    oracle port on all host cores, on this arm's own config.  Rank 0 only."""
     if rank != 0:
         return
     t0 = time.perf_counter()
-    cb = cpu_baseline(wl, name, budget_s=max(5.0, 6.0 * (args.steps + args.warmup)))
+    # steps: the requested K, bounded so that the whole run ends within a few minutes (>= 3 timed steps)
+    cb = cpu_baseline(wl, name, budget_s=150.0, min_steps=min(3, max(1, args.steps)), max_steps=max(1, args.steps))
+    cfg = {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")}, "time_scheme": "wrfrk3"}
+    if cb["workload_timed"] != name:
+        cfg["workload_timed"] = cb["workload_timed"]; cfg["scaled_to"] = name
     line = {"impl": "reference", "metric": "simulated days per wall-clock day", "value": cb["value"], "unit": "simulated days/day",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["s_per_step"] * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")}},
+            "n_gpus": args.gpus, "steps": cb["steps_timed"], "steps_requested": args.steps, "warmup": 1, "ms_per_step": cb["s_per_step"] * 1e3,
+            "higher_is_better": True, "scaling": "strong" if wl["nlev"] > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": cfg,
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "simulated days/day", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "wall_s": time.perf_counter() - t0}
@@ -273,7 +289,7 @@ def _main(out):
     gpu.set_state(ic)
     q0 = None
     if host.cfg.ntracers:
-        q0 = np.zeros((host.cfg.ntracers,) + host.shape("cell"))
+        q0 = bench_tracer(host)
         gpu.set_tracers(q0)
     gpu.prepare_run()
     # nvidia-smi takes a while to deliver its first sample (longer with 8 ranks starting one each): start it before
@@ -370,13 +386,14 @@ def _main(out):
         cb = None
         if not args.no_cpu_baseline:
             try:
-                cb = cpu_baseline(wl, name)
-                cb.pop("s_per_step")
+                cb = cpu_baseline(wl, name, budget_s=25.0, min_steps=2, max_steps=50)
+                for k in ("s_per_step", "workload_timed", "steps_timed"):
+                    cb.pop(k)
             except Exception as e:      # never lose the GPU line to a CPU-side failure
                 cb = {"value": None, "unit": "simulated days/day", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
         line = {"metric": "simulated days per wall-clock day", "value": value, "unit": "simulated days/day", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
-                "scaling": "strong" if banded else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "scaling": "strong" if wl["nlev"] > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": name, **{k: wl[k] for k in ("nlon", "nlat", "nlev", "dt", "case")},
                            "time_scheme": "wrfrk3", "hx": host.hx, "parallelism": (f"{world} latitude bands ({band_rows} rows: {band_sizes}), NCCL halo exchange" if banded else f"replicas x{world}") if world > 1 else "1 GPU",
                            "l2": "flushed between timed steps (256 MB write)" if flush else "working set >> L2 (no flush)"},

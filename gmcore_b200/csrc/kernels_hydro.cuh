@@ -102,7 +102,10 @@ template <bool EDGE> __device__ __forceinline__ void cfl_body(const Geo& g, cons
   for (int s = 0; s < 3; ++s) {
     const double h = s == 1 ? a.dt : a.dt / 2;
     if (dox) {
-      const int lx = __double2int_rd(i1 + (x - x0) * rdx), d = lx - i1;
+      int lx = __double2int_rd(i1 + (x - x0) * rdx), d = lx - i1;
+      // a departure point outside the longitude halo is the reference's "cflx exceeds mesh%lon_halo_width" abort
+      // (adv_batch_mod.F90:284-287): raise the guard and keep the gather inside the coefficient table
+      if (d < -M.hx || d > M.hx - 2) { atomicOr(a.flags, 1); d = d < 0 ? -M.hx : M.hx - 2; lx = i1 + d; }
       double ua, ub, xl, xr;
       if (d == 0) { ua = u1; ub = u_p; xl = x0; xr = xp; }
       else if (d == -1) { ua = u_m; ub = u1; xl = xm; xr = x0; }
@@ -367,7 +370,8 @@ template <bool EDGE, int LIM> __device__ __forceinline__ void hflx_body(const Ge
   if (dox) {
     double flux = 0;
     if (cx != 0) {
-      const int ci = (int)cx;
+      int ci = (int)cx;
+      if (ci >= n || ci <= -n) ci = 0;      // |cflx| > lon_halo_width: the guard word is already up (k_cfl); stay in the row
       const double cf = cx - ci;
       const bool pos = cx > 0;
       double x0, x1, x2, x3, x4, sm = 0;
@@ -463,7 +467,8 @@ struct ColQ {
 // flux through half level k1 (2..nlev)
 template <int LIM> __device__ __forceinline__ double vflx_one(const ColQ& q, int k1, double cz, double w) {
   if (cz == 0) return 0.0;
-  const int ci = (int)cz;
+  int ci = (int)cz;
+  if (ci > q.nlev || ci < -q.nlev) ci = 0;      // only reachable after a raised cflz guard (garbage in, bounded loop out)
   const double cf = cz - ci;
   int ku; double s1, s2, sm = 0;
   if (cz > 0) { ku = k1 - ci - 1; s1 = 1 - cf; s2 = 1; for (int l = k1 - ci; l <= k1 - 1; ++l) sm += q(l); }

@@ -13,10 +13,20 @@ inline double fsign(double a, double b) { return std::signbit(b) ? -std::fabs(a)
 inline double min3(double a, double b, double c) { return std::fmin(std::fmin(a, b), c); }
 inline double max3(double a, double b, double c) { return std::fmax(std::fmax(a, b), c); }
 
-inline void copy_arr(A3& dst, const A3& src) { dst.d = src.d; }
+inline void copy_arr(A3& dst, const A3& src) {
+#if defined(_OPENMP) && defined(ORC_OPENMP_LOOPS)
+  if (dst.d.size() == src.d.size()) {
+    const long long N = (long long)src.d.size(); double* d = dst.d.data(); const double* s = src.d.data();
+    ORC_PAR for (long long n = 0; n < N; ++n) d[n] = s[n];
+    return;
+  }
+#endif
+  dst.d = src.d;
+}
 inline void axpby_arr(A3& x, const A3& y, bool average, int nstep) {
   // this%u = this%u + u   |  this%u = (this%u + u) / (nstep + 1)
-  for (size_t n = 0; n < x.d.size(); ++n) {
+  const long long N = (long long)x.d.size();
+  ORC_PAR for (long long n = 0; n < N; ++n) {
     double s = x.d[n] + y.d[n];
     x.d[n] = average ? s / (nstep + 1) : s;
   }
@@ -38,7 +48,7 @@ inline void accum_uv_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, doubl
     B.uv_step = B.uv_step + 1;
   }
   if (B.uv_step != 0) return;
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) {
       double dx = mesh.de_lon(j);
       for (int i = 1; i <= mesh.nlon; ++i) {
@@ -155,7 +165,7 @@ inline void accum_we_lev(Block& b, AdvBatch& B, const A3& we, const A3& m_lev, d
     return ((mesh.half_lev(l + 1) - z) * B.we(i, j, l) / B.m_lev(i, j, l) * mesh.half_dlev(l) +
             (z - mesh.half_lev(l)) * B.we(i, j, l + 1) / B.m_lev(i, j, l + 1) * mesh.half_dlev(l + 1)) / mesh.full_dlev(l);
   };
-  for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = mesh.full_lat_ibeg; j <= mesh.full_lat_iend; ++j)
       for (int i = 1; i <= mesh.nlon; ++i) {
         double z0 = mesh.half_lev(k);
@@ -220,7 +230,7 @@ inline void hflx_ppm_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const
   const Mesh& mesh = b.mesh;
   A3 &mlx = B.qlx, &mly = B.qly, &dmx = B.dqx, &dmy = B.dqy, &m6x = B.q6x, &m6y = B.q6y;
   const A3 &cflx = B.cflx, &cfly = B.cfly;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       ppm(b.cfg.limiter_type, mx(i - 2, j, k), mx(i - 1, j, k), mx(i, j, k), mx(i + 1, j, k), mx(i + 2, j, k), mlx(i, j, k), dmx(i, j, k), m6x(i, j, k));
       ppm(b.cfg.limiter_type, my(i, j - 2, k), my(i, j - 1, k), my(i, j, k), my(i, j + 1, k), my(i, j + 2, k), mly(i, j, k), dmy(i, j, k), m6y(i, j, k));
@@ -231,7 +241,7 @@ inline void hflx_ppm_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const
   fill_halo(mesh, mly, true, false, false, true, true);
   fill_halo(mesh, dmy, true, false, false, true, true);
   fill_halo(mesh, m6y, true, false, false, true, true);
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       int ci = (int)cflx(i, j, k);
       double cf = cflx(i, j, k) - ci;
@@ -273,10 +283,10 @@ inline void hflx_ppm_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, const
 inline void vflx_ppm_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, A3& mfz) {
   const Mesh& mesh = b.mesh;
   A3 &mlz = B.qlx, &dmz = B.dqx, &m6z = B.q6x; const A3& cflz = B.cflz;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       ppm(b.cfg.limiter_type, m(i, j, k - 2), m(i, j, k - 1), m(i, j, k), m(i, j, k + 1), m(i, j, k + 2), mlz(i, j, k), dmz(i, j, k), m6z(i, j, k));
-  for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       int ci = (int)cflz(i, j, k);
       double cf = cflz(i, j, k) - ci;
@@ -303,7 +313,7 @@ inline void hflx_van_leer_cell(Block& b, AdvBatch& B, const A3& u, const A3& v, 
   const Mesh& mesh = b.mesh;
   const int lim = b.cfg.limiter_type;
   const A3 &cflx = B.cflx, &cfly = B.cfly;
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       int ci = (int)cflx(i, j, k);
       double cf = cflx(i, j, k) - ci;
@@ -335,7 +345,7 @@ inline void vflx_van_leer_cell(Block& b, AdvBatch& B, const A3& w, const A3& m, 
   const Mesh& mesh = b.mesh;
   const int lim = b.cfg.limiter_type;
   const A3& cflz = B.cflz;
-  for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       int ci = (int)cflz(i, j, k);
       double cf = cflz(i, j, k) - ci;
@@ -373,7 +383,7 @@ inline void ffsl_calc_tracer_hflx_cell(Block& b, AdvBatch& B, const A3& q, A3& q
   hflx_cell(b, B, B.u, B.v, q, q, qmfx, qmfy);
   fill_halo(mesh, qmfx, true, true, true, false, false);
   fill_halo(mesh, qmfy, false, false, false, true, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       qx(i, j, k) = q(i, j, k) - 0.5 * ((qmfx(i, j, k) - qmfx(i - 1, j, k)) * mesh.le_lon(j) / mesh.area_cell(j) - divx(i, j, k) * q(i, j, k)) * dt_;
       qy(i, j, k) = q(i, j, k) - 0.5 * ((qmfy(i, j, k) * mesh.le_lat(j) - qmfy(i, j - 1, k) * mesh.le_lat(j - 1)) / mesh.area_cell(j) - divy(i, j, k) * q(i, j, k)) * dt_;

@@ -22,6 +22,18 @@
 #include <vector>
 #include "../include/gmcore_gpu.h"
 
+// Loop-level OpenMP for the TIMED build only (liboracle_fast.so, -DORC_OPENMP_LOOPS): the level loops of the
+// restatement are independent, which is how the reference's MPI ranks split the work too.  The parity build
+// (liboracle.so) compiles these macros away and stays scalar, left-to-right.
+#if defined(_OPENMP) && defined(ORC_OPENMP_LOOPS)
+#define ORC_PRAGMA(x) _Pragma(#x)
+#define ORC_PAR ORC_PRAGMA(omp parallel for schedule(static))
+#define ORC_PAR_FP(v) ORC_PRAGMA(omp parallel for schedule(static) firstprivate(v))
+#else
+#define ORC_PAR
+#define ORC_PAR_FP(v)
+#endif
+
 namespace orc {
 
 struct A3 {
@@ -121,16 +133,18 @@ inline void fill_halo(const Mesh& m, A3& a, bool full_lat, bool west = true, boo
   // W/E types cover local rows of the *full* index range lat_ibeg..lat_iend
   // (halo_mod.F90:90-96: half_lat_ibeg/iend = full ones unless orient==north).
   const int jb = 1, je = nlat;
-  if (west)
-    for (int k = k0; k <= k1; ++k) for (int j = jb; j <= je; ++j) for (int i = 1 - hx; i <= 0; ++i)
+  if (west) {
+    ORC_PAR for (int k = k0; k <= k1; ++k) for (int j = jb; j <= je; ++j) for (int i = 1 - hx; i <= 0; ++i)
       a(i, j, k) = a(i + nlon, j, k);
-  if (east)
-    for (int k = k0; k <= k1; ++k) for (int j = jb; j <= je; ++j) for (int i = nlon + 1; i <= nlon + hx; ++i)
+  }
+  if (east) {
+    ORC_PAR for (int k = k0; k <= k1; ++k) for (int j = jb; j <= je; ++j) for (int i = nlon + 1; i <= nlon + hx; ++i)
       a(i, j, k) = a(i - nlon, j, k);
+  }
   const int half = nlon / 2;
   std::vector<double> tmp((size_t)a.ni * hy);
   if (south) {
-    for (int k = k0; k <= k1; ++k) {
+    ORC_PAR_FP(tmp) for (int k = k0; k <= k1; ++k) {
       // Sendrecv: send rows s=1..hy -> halo rows (s-hy), all columns
       for (int s = 1; s <= hy; ++s) {
         int src = full_lat ? 1 + s : s;
@@ -146,7 +160,7 @@ inline void fill_halo(const Mesh& m, A3& a, bool full_lat, bool west = true, boo
     }
   }
   if (north) {
-    for (int k = k0; k <= k1; ++k) {
+    ORC_PAR_FP(tmp) for (int k = k0; k <= k1; ++k) {
       for (int s = 1; s <= hy; ++s) {
         int src = N - hy - (full_lat ? 1 : 0) + s;
         for (int i = a.ilb; i < a.ilb + a.ni; ++i) a(i, N + s, k) = a(i, src, k);

@@ -26,22 +26,22 @@ struct Model {
     ffsl_calc_tracer_hflx_cell(b, b.adv_batch_mass, s.pt, s.ptf_lon, s.ptf_lat, dt, true);
     fill_halo(mesh, s.ptf_lon, true, true, false, false, false);
     fill_halo(mesh, s.ptf_lat, false, false, false, true, false);
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         t.dptfdlon(i, j, k) = (s.ptf_lon(i, j, k) - s.ptf_lon(i - 1, j, k)) * mesh.le_lon(j) / mesh.area_cell(j);
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         t.dptfdlat(i, j, k) = (s.ptf_lat(i, j, k) * mesh.le_lat(j) - s.ptf_lat(i, j - 1, k) * mesh.le_lat(j - 1)) / mesh.area_cell(j);
     pole_flux_div(mesh, s.ptf_lat, t.dptfdlat);
     A3& pt = s.pt;
-    for (int k = mesh.full_lev_ibeg - 1; k >= mesh.full_lev_ibeg - 2; --k)
-      for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
+    for (int k = mesh.full_lev_ibeg - 1; k >= mesh.full_lev_ibeg - 2; --k)      // k = -1 reads k = 0: serial in k
+      ORC_PAR for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
         pt(i, j, k) = 2 * pt(i, j, k + 1) - pt(i, j, k + 2);
     for (int k = mesh.full_lev_iend + 1; k <= mesh.full_lev_iend + 2; ++k)
-      for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
+      ORC_PAR for (int j = pt.jlb; j < pt.jlb + pt.nj; ++j) for (int i = pt.ilb; i < pt.ilb + pt.ni; ++i)
         pt(i, j, k) = 2 * pt(i, j, k - 1) - pt(i, j, k - 2);
     ffsl_calc_tracer_vflx_cell(b, b.adv_batch_mass, pt, s.ptf_lev);
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         t.dptfdlev(i, j, k) = s.ptf_lev(i, j, k + 1) - s.ptf_lev(i, j, k);
   }
@@ -88,7 +88,7 @@ struct Model {
         calc_grad_ptf(star, tend1, dt);
         calc_coriolis(b, star, tend1);
         calc_grad_ke(b, star, tend1);
-        for (int k = 1; k <= mesh.nlev; ++k) {
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
           for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             tend1.du(i, j, k) = tend1.qhv(i, j, k) - tend1.dkedlon(i, j, k) - tend1.wedudlev(i, j, k);
           for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
@@ -101,7 +101,7 @@ struct Model {
         calc_grad_mf(b, star, tend1);
         calc_coriolis(b, star, tend1);
         calc_grad_ke(b, star, tend1);
-        for (int k = 1; k <= mesh.nlev; ++k) {
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
           for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             tend1.du(i, j, k) = tend1.qhv(i, j, k) - tend1.dkedlon(i, j, k);
           for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
@@ -114,7 +114,7 @@ struct Model {
     } else {
       operators_prepare(nw, dt, pass);
       pgf_run(b, nw, tend1);
-      for (int k = 1; k <= mesh.nlev; ++k) {
+      ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
         for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
           tend1.du(i, j, k) = tend2.du(i, j, k) - tend1.pgf_lon(i, j, k);
         for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
@@ -138,19 +138,19 @@ struct Model {
         calc_m(b, ns);
       }
       if (tend.update_pt) {
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             ns.pt(i, j, k) = old_state.pt(i, j, k) * old_state.m(i, j, k) + dt * tend.dpt(i, j, k);
         fill_halo(mesh, ns.pt, true, true, true, false, false);
         filter_full_lat(mesh, b.small_filter1, ns.pt, nullptr, 1, mesh.nlev);
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             ns.pt(i, j, k) = ns.pt(i, j, k) / ns.m(i, j, k);
         fill_halo(mesh, ns.pt, true);
       }
     } else {
       if (tend.update_gz) {
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             ns.gz(i, j, k) = old_state.gz(i, j, k) + dt * tend.dgz(i, j, k);
         fill_halo(mesh, ns.gz, true, true, true, false, false);
@@ -161,10 +161,10 @@ struct Model {
       }
     }
     if (tend.update_u && tend.update_v) {
-      for (int k = 1; k <= mesh.nlev; ++k)
+      ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
         for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
           ns.u_lon(i, j, k) = old_state.u_lon(i, j, k) + dt * tend.du(i, j, k);
-      for (int k = 1; k <= mesh.nlev; ++k)
+      ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
         for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
           ns.v_lat(i, j, k) = old_state.v_lat(i, j, k) + dt * tend.dv(i, j, k);
       if (b.cfg.baroclinic) {
@@ -180,10 +180,10 @@ struct Model {
       const double wgt = 0.6;
       {
         int j = mesh.half_lat_ibeg; A3& v = ns.v_lat;
-        for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
+        ORC_PAR for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
           v(i, j, k) = (1 - wgt) * v(i, j, k) + wgt * v(i, j + 1, k);
         j = mesh.half_lat_iend;
-        for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
+        ORC_PAR for (int k = v.klb; k <= v.kub(); ++k) for (int i = v.ilb; i < v.ilb + v.ni; ++i)
           v(i, j, k) = (1 - wgt) * v(i, j, k) + wgt * v(i, j - 1, k);
       }
       fill_halo(mesh, ns.v_lat, false, false, false, true, true);
@@ -244,12 +244,12 @@ struct Model {
     calc_div(b, s);
     A3 &u = s.u_lon, &v = s.v_lat; const A3& d = b.cfg.div_damp_order == 2 ? s.div : s.div2;
     const double sgn = b.cfg.div_damp_order == 2 ? 1.0 : -1.0;
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
         double inc = clon(j, k) * (d(i + 1, j, k) - d(i, j, k)) / mesh.de_lon(j);
         u(i, j, k) = sgn > 0 ? u(i, j, k) + inc : u(i, j, k) - inc;
       }
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
         double inc = clat(j, k) * (d(i, j + 1, k) - d(i, j, k)) / mesh.de_lat(j);
         v(i, j, k) = sgn > 0 ? v(i, j, k) + inc : v(i, j, k) - inc;
@@ -263,21 +263,21 @@ struct Model {
     const double coef = b.cfg.smag_damp_coef;
     A3 &u = s.u_lon, &v = s.v_lat, &st = s.smag_t, &ss = s.smag_s, &klon = s.kmh_lon, &klat = s.kmh_lat;
     const int nlon = mesh.nlon, nlat = mesh.nlat, nhalf = mesh.nhalf, nlev = mesh.nlev;
-    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
       st(i, j, k) = (u(i, j, k) - u(i - 1, j, k)) / mesh.de_lon(j) -
                     (v(i, j, k) * mesh.half_cos_lat(j) - v(i, j - 1, k) * mesh.half_cos_lat(j - 1)) / mesh.le_lon(j) / mesh.full_cos_lat(j);
     fill_halo(mesh, st, true, false, true, false, true);
-    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
       ss(i, j, k) = (v(i + 1, j, k) - v(i, j, k)) / mesh.le_lat(j) +
                     (u(i, j + 1, k) * mesh.full_cos_lat(j + 1) - u(i, j, k) * mesh.full_cos_lat(j)) / mesh.de_lat(j) / mesh.half_cos_lat(j);
     fill_halo(mesh, ss, false, true, false, true, false);
-    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) {
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) {
       const double ls2 = coef / (1 / (mesh.de_lon(j) * mesh.de_lon(j)) + 1 / (mesh.le_lon(j) * mesh.le_lon(j))) * 1.0;
       for (int i = 1; i <= nlon; ++i)
         klon(i, j, k) = ls2 * std::sqrt(0.5 * (st(i, j, k) * st(i, j, k) + st(i + 1, j, k) * st(i + 1, j, k)) +
                                         0.5 * (ss(i, j, k) * ss(i, j, k) + ss(i, j - 1, k) * ss(i, j - 1, k)));
     }
-    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) {
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) {
       const double ls2 = coef / (1 / (mesh.le_lat(j) * mesh.le_lat(j)) + 1 / (mesh.de_lat(j) * mesh.de_lat(j))) * 1.0;
       for (int i = 1; i <= nlon; ++i)
         klat(i, j, k) = ls2 * std::sqrt(0.5 * (st(i, j, k) * st(i, j, k) + st(i, j + 1, k) * st(i, j + 1, k)) +
@@ -286,21 +286,21 @@ struct Model {
     // tendencies from the un-updated winds, then the updates (smag_damp_mod.F90:131-176)
     std::vector<double> tu((size_t)nlon * nlat * nlev), tv((size_t)nlon * nlat * nlev);
     auto T = [&](int i, int j, int k) { return ((size_t)(k - 1) * nlat + (j - 1)) * nlon + (i - 1); };
-    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
       tu[T(i, j, k)] = klon(i, j, k) * ((u(i - 1, j, k) - 2 * u(i, j, k) + u(i + 1, j, k)) / (mesh.de_lon(j) * mesh.de_lon(j)) +
                         ((u(i, j + 1, k) - u(i, j, k)) / mesh.de_lat(j) * mesh.half_cos_lat(j) -
                          (u(i, j, k) - u(i, j - 1, k)) / mesh.de_lat(j - 1) * mesh.half_cos_lat(j - 1)) / mesh.le_lon(j) / mesh.full_cos_lat(j));
-    for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 2; j <= nlat - 1; ++j) for (int i = 1; i <= nlon; ++i)
       u(i, j, k) = u(i, j, k) + dt * tu[T(i, j, k)];
     fill_halo(mesh, u, true);
-    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i) {
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i) {
       double lap = (v(i - 1, j, k) - 2 * v(i, j, k) + v(i + 1, j, k)) / (mesh.le_lat(j) * mesh.le_lat(j));
       if (!(j == 1 || j == nhalf))
         lap = lap + ((v(i, j + 1, k) - v(i, j, k)) / mesh.le_lon(j + 1) * mesh.full_cos_lat(j + 1) -
                      (v(i, j, k) - v(i, j - 1, k)) / mesh.le_lon(j) * mesh.full_cos_lat(j)) / mesh.de_lat(j) / mesh.half_cos_lat(j);
       tv[T(i, j, k)] = klat(i, j, k) * lap;
     }
-    for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
+    ORC_PAR for (int k = 1; k <= nlev; ++k) for (int j = 1; j <= nhalf; ++j) for (int i = 1; i <= nlon; ++i)
       v(i, j, k) = v(i, j, k) + dt * tv[T(i, j, k)];
     fill_halo(mesh, v, false);
   }
@@ -323,7 +323,7 @@ struct Model {
     const Mesh& mesh = b.mesh;
     std::vector<double> g(mesh.nlon + 2);
     const double c = 0.25;  // 0.5**2
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR_FP(g) for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 2; j <= mesh.nlat - 1; ++j) {
         double wgt = wgt_full_lat[j];
         if (wgt == 0) continue;
@@ -366,7 +366,7 @@ struct Model {
         ffsl_calc_tracer_hflx_cell(b, B, qo, qmf_lon, qmf_lat, 0.0, false);
         fill_halo(mesh, qmf_lon, true, true, false, false, false);
         fill_halo(mesh, qmf_lat, false, false, false, true, false);
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 2; j <= mesh.nlat - 1; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             qn(i, j, k) = old_m(i, j, k) * qo(i, j, k) - ((qmf_lon(i, j, k) - qmf_lon(i - 1, j, k)) * mesh.le_lon(j) +
                           (qmf_lat(i, j, k) * mesh.le_lat(j) - qmf_lat(i, j - 1, k) * mesh.le_lat(j - 1))) / mesh.area_cell(j) * dt_adv;
@@ -387,11 +387,11 @@ struct Model {
             for (int i = 1; i <= mesh.nlon; ++i) qn(i, j, k) = old_m(i, j, k) * qo(i, j, k) + pole;
           }
         }
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             qn(i, j, k) = qn(i, j, k) / m(i, j, k);
         // negative filling along x (sequential, order dependent)
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             if (qn(i, j, k) < 0) {
               double qm0 = qn(i, j, k) * m(i, j, k), qm1 = qn(i - 1, j, k) * m(i - 1, j, k), qm2 = qn(i + 1, j, k) * m(i + 1, j, k);
@@ -404,16 +404,18 @@ struct Model {
               else b.fail("Negative tracer!");
               qn(i, j, k) = 0;
             }
-        for (int k = mesh.full_lev_lb; k <= 0; ++k)
+        ORC_PAR for (int k = mesh.full_lev_lb; k <= 0; ++k)
           for (int j = qn.jlb; j < qn.jlb + qn.nj; ++j) for (int i = qn.ilb; i < qn.ilb + qn.ni; ++i) qn(i, j, k) = qn(i, j, 1);
-        for (int k = mesh.nlev + 1; k <= mesh.full_lev_ub; ++k)
+        ORC_PAR for (int k = mesh.nlev + 1; k <= mesh.full_lev_ub; ++k)
           for (int j = qn.jlb; j < qn.jlb + qn.nj; ++j) for (int i = qn.ilb; i < qn.ilb + qn.ni; ++i) qn(i, j, k) = qn(i, j, mesh.nlev);
         ffsl_calc_tracer_vflx_cell(b, B, qn, qmf_lev);
-        for (int k = 1; k <= mesh.nlev; ++k)
+        ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
           for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
             qn(i, j, k) = qn(i, j, k) - ((qmf_lev(i, j, k + 1) - qmf_lev(i, j, k)) * dt_adv) / m(i, j, k);
-        for (int k = 1; k <= mesh.nlev; ++k)
-          for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+        // negative filling along z: order dependent in k inside a column only, so rows may run side by side
+        // (j outermost) with the reference's k-then-i order kept inside each row -- same values as k, j, i
+        ORC_PAR for (int j = 1; j <= mesh.nlat; ++j)
+          for (int k = 1; k <= mesh.nlev; ++k) for (int i = 1; i <= mesh.nlon; ++i)
             if (qn(i, j, k) < 0) {
               double qm0 = qn(i, j, k) * m(i, j, k);
               double qm1 = k > 1 ? qn(i, j, k - 1) * m(i, j, k - 1) : 0.0;

@@ -27,13 +27,13 @@ inline double calc_dphdt_lev_k(const Block& b, int k, double dphsdt) { return b.
 // operators_mod.F90:136-168
 inline void calc_ph(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
-  for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       s.ph_lev(i, j, k) = calc_ph_lev_k(b, k, s.phs_f(i, j));
       s.ph_exn_lev(i, j, k) = std::pow(s.ph_lev(i, j, k), b.cfg.Rd_o_cpd);
     }
   fill_halo(mesh, s.ph_exn_lev, true, false, true, false, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.ph(i, j, k) = 0.5 * (s.ph_lev(i, j, k) + s.ph_lev(i, j, k + 1));
   fill_halo(mesh, s.ph, true);
@@ -45,7 +45,7 @@ inline double temperature(const Block& b, double pt, double p) { return pt * std
 // operators_mod.F90:170-190
 inline void calc_t(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.t(i, j, k) = temperature(b, s.pt(i, j, k), s.ph(i, j, k));
 }
@@ -54,12 +54,12 @@ inline void calc_t(Block& b, State& s) {
 inline void calc_m(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
   if (b.cfg.baroclinic) {
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
         s.m(i, j, k) = s.ph_lev(i, j, k + 1) - s.ph_lev(i, j, k);
         if (s.m(i, j, k) <= 0) b.fail("The pressure levels are not monotonic!");
       }
-    for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+    ORC_PAR for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
       for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         s.m_lev(i, j, k) = s.ph(i, j, k) - s.ph(i, j, k - 1);
     int k = mesh.half_lev_ibeg;
@@ -74,15 +74,15 @@ inline void calc_m(Block& b, State& s) {
       s.m(i, j, 1) = (s.gz(i, j, 1) - b.st.gzs(i, j)) / b.cfg.g;
   }
   fill_halo(mesh, s.m, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.m_lon(i, j, k) = (s.m(i, j, k) + s.m(i + 1, j, k)) * 0.5;
   fill_halo(mesh, s.m_lon, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.m_lat(i, j, k) = (s.m(i, j, k) + s.m(i, j + 1, k)) * 0.5;
   fill_halo(mesh, s.m_lat, false);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.m_vtx(i, j, k) = ((s.m(i, j, k) + s.m(i + 1, j, k)) * mesh.area_subcell(2, j) +
                           (s.m(i, j + 1, k) + s.m(i + 1, j + 1, k)) * mesh.area_subcell(1, j + 1)) / mesh.area_vtx(j);
@@ -92,21 +92,21 @@ inline void calc_m(Block& b, State& s) {
 inline void calc_mf(Block& b, State& s, double dt) {
   const Mesh& mesh = b.mesh;
   accum_uv_cell(b, b.adv_batch_mass, s.u_f, s.v_f, dt, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 0; i <= mesh.nlon; ++i)
       s.mfx_lon(i, j, k) = s.m_lon(i, j, k) * s.u_f(i, j, k);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon + 1; ++i)
       s.mfy_lat(i, j, k) = s.m_lat(i, j, k) * s.v_f(i, j, k);
   accum_mf_cell(b.adv_batch_mass, s.mfx_lon, s.mfy_lat);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       s.mfx_lat(i, j, k) = mesh.half_tangent_wgt(1, j) * (s.mfx_lon(i - 1, j, k) + s.mfx_lon(i, j, k)) +
                            mesh.half_tangent_wgt(2, j) * (s.mfx_lon(i - 1, j + 1, k) + s.mfx_lon(i, j + 1, k));
       s.u_lat(i, j, k) = s.mfx_lat(i, j, k) / s.m_lat(i, j, k);
     }
   fill_halo(mesh, s.u_lat, false);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       s.mfy_lon(i, j, k) = mesh.full_tangent_wgt(1, j) * (s.mfy_lat(i, j - 1, k) + s.mfy_lat(i + 1, j - 1, k)) +
                            mesh.full_tangent_wgt(2, j) * (s.mfy_lat(i, j, k) + s.mfy_lat(i + 1, j, k));
@@ -119,13 +119,13 @@ inline void calc_mf(Block& b, State& s, double dt) {
 inline void calc_ke(Block& b, State& s) {
   const Mesh& mesh = b.mesh; const A3& u = s.u_f; const A3& v = s.v_f; A3& ke = s.ke;
   auto sq = [](double x) { return x * x; };
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon + 1; ++i)
       ke(i, j, k) = (mesh.area_lon_west(j) * sq(u(i - 1, j, k)) + mesh.area_lon_east(j) * sq(u(i, j, k)) +
                      mesh.area_lat_north(j - 1) * sq(v(i, j - 1, k)) + mesh.area_lat_south(j) * sq(v(i, j, k))) / mesh.area_cell(j);
   if (b.cfg.ke_scheme == 2) {
     const double w = b.cfg.ke_cell_wgt;
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon + 1; ++i) {
         double kv1 = (mesh.area_lat_east(j) * sq(v(i - 1, j, k)) + mesh.area_lat_west(j) * sq(v(i, j, k)) +
                       mesh.area_lon_north(j) * sq(u(i - 1, j, k)) + mesh.area_lon_south(j + 1) * sq(u(i - 1, j + 1, k))) / mesh.area_vtx(j);
@@ -154,7 +154,7 @@ inline void calc_ke(Block& b, State& s) {
 // operators_mod.F90:354-431
 inline void calc_div(Block& b, State& s) {
   const Mesh& mesh = b.mesh; const A3& u = s.u_f; const A3& v = s.v_f; A3& div = s.div;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       div(i, j, k) = ((u(i, j, k) * mesh.le_lon(j) - u(i - 1, j, k) * mesh.le_lon(j)) +
                       (v(i, j, k) * mesh.le_lat(j) - v(i, j - 1, k) * mesh.le_lat(j - 1))) / mesh.area_cell(j);
@@ -179,7 +179,7 @@ inline void calc_div(Block& b, State& s) {
   else fill_halo(mesh, div, true, false, true, false, true);
   if (b.cfg.div_damp_order == 4) {
     A3& div2 = s.div2;
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         div2(i, j, k) = (div(i + 1, j, k) - 2 * div(i, j, k) + div(i - 1, j, k)) / (mesh.de_lon(j) * mesh.de_lon(j)) +
                         ((div(i, j + 1, k) - div(i, j, k)) * mesh.half_cos_lat(j) / mesh.de_lat(j) -
@@ -192,7 +192,7 @@ inline void calc_div(Block& b, State& s) {
 // operators_mod.F90:612-677
 inline void calc_vor(Block& b, State& s, const A3& u, const A3& v) {
   const Mesh& mesh = b.mesh; A3& vor = s.vor;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 0; i <= mesh.nlon; ++i)
       vor(i, j, k) = (u(i, j, k) * mesh.de_lon(j) - u(i, j + 1, k) * mesh.de_lon(j + 1) +
                       v(i + 1, j, k) * mesh.de_lat(j) - v(i, j, k) * mesh.de_lat(j)) / mesh.area_vtx(j);
@@ -221,7 +221,7 @@ inline void calc_vor(Block& b, State& s, const A3& u, const A3& v) {
 inline void calc_pv(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
   calc_vor(b, s, s.u_f, s.v_f);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.pv(i, j, k) = (s.vor(i, j, k) + mesh.half_f(j)) / s.m_vtx(i, j, k);
   fill_halo(mesh, s.pv, false);
@@ -231,11 +231,11 @@ inline void calc_pv(Block& b, State& s) {
 // operators_mod.F90:705-736
 inline void interp_pv_midpoint(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.pv_lat(i, j, k) = 0.5 * (s.pv(i - 1, j, k) + s.pv(i, j, k));
   fill_halo(mesh, s.pv_lat, false, true, true, true, false);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.pv_lon(i, j, k) = 0.5 * (s.pv(i, j, k) + s.pv(i, j - 1, k));
   fill_halo(mesh, s.pv_lon, true, true, true, false, true);
@@ -246,7 +246,7 @@ inline void interp_pv_upwind(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
   const A3 &un = s.u_f, &vn = s.v_f, &ut = s.u_lat, &vt = s.v_lon, &pv = s.pv;
   const double eps = 2.220446049250313e-16, wgt = b.cfg.upwind_wgt_pv;
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       double bb = std::fabs(vt(i, j, k)) / (std::sqrt(un(i, j, k) * un(i, j, k) + vt(i, j, k) * vt(i, j, k)) + eps);
       double up = b.cfg.upwind_order_pv == 1
@@ -284,7 +284,7 @@ inline void interp_pv_tvd(Block& b, State& s, double dt) {
   const Mesh& mesh = b.mesh;
   const A3 &ut = s.u_lat, &vt = s.v_lon, &pv = s.pv;
   const int type = b.cfg.tvd_limiter_type;
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       double cfl = vt(i, j, k) * dt / mesh.le_lon(j);
       s.pv_lon(i, j, k) = tvd(type, cfl, pv(i, j - 2, k), pv(i, j - 1, k), pv(i, j, k), pv(i, j + 1, k));
@@ -309,7 +309,7 @@ inline void interp_pv(Block& b, State& s, double dt) {
 inline void calc_coriolis(Block& b, State& s, Tend& t) {
   const Mesh& mesh = b.mesh;
   const A3 &mfx_lon = s.mfx_lon, &mfy_lat = s.mfy_lat, &pv_lon = s.pv_lon, &pv_lat = s.pv_lat;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       if (b.cfg.coriolis_scheme == 1)
         t.qhu(i, j, k) = (mesh.half_tangent_wgt(1, j) * (mfx_lon(i - 1, j, k) * (pv_lat(i, j, k) + pv_lon(i - 1, j, k)) +
@@ -319,7 +319,7 @@ inline void calc_coriolis(Block& b, State& s, Tend& t) {
       else
         t.qhu(i, j, k) = s.mfx_lat(i, j, k) * pv_lat(i, j, k);
     }
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       if (b.cfg.coriolis_scheme == 1)
         t.qhv(i, j, k) = (mesh.full_tangent_wgt(1, j) * (mfy_lat(i, j - 1, k) * (pv_lon(i, j, k) + pv_lat(i, j - 1, k)) +
@@ -334,10 +334,10 @@ inline void calc_coriolis(Block& b, State& s, Tend& t) {
 // operators_mod.F90:908-937
 inline void calc_grad_ke(Block& b, State& s, Tend& t) {
   const Mesh& mesh = b.mesh;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.dkedlon(i, j, k) = (s.ke(i + 1, j, k) - s.ke(i, j, k)) / mesh.de_lon(j);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.dkedlat(i, j, k) = (s.ke(i, j + 1, k) - s.ke(i, j, k)) / mesh.de_lat(j);
 }
@@ -367,10 +367,10 @@ inline void pole_flux_div(const Mesh& mesh, const A3& f_lat, A3& d) {
 // operators_mod.F90:939-1006
 inline void calc_grad_mf(Block& b, State& s, Tend& t) {
   const Mesh& mesh = b.mesh;
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.dmfdlon(i, j, k) = (s.mfx_lon(i, j, k) - s.mfx_lon(i - 1, j, k)) * mesh.le_lon(j) / mesh.area_cell(j);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.dmfdlat(i, j, k) = (s.mfy_lat(i, j, k) * mesh.le_lat(j) - s.mfy_lat(i, j - 1, k) * mesh.le_lat(j - 1)) / mesh.area_cell(j);
   pole_flux_div(mesh, s.mfy_lat, t.dmfdlat);
@@ -380,15 +380,15 @@ inline void calc_grad_mf(Block& b, State& s, Tend& t) {
 inline void calc_dphsdt(Block& b, Tend& t) {
   const Mesh& mesh = b.mesh;
   std::fill(t.dphs.d.begin(), t.dphs.d.end(), 0.0);
-  for (int k = 1; k <= mesh.nlev; ++k)
-    for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
+  ORC_PAR for (int j = 1; j <= mesh.nlat; ++j)       // per-point sums over k in the reference's order (k outermost there)
+    for (int k = 1; k <= mesh.nlev; ++k) for (int i = 1; i <= mesh.nlon; ++i)
       t.dphs(i, j) = t.dphs(i, j) - t.dmfdlon(i, j, k) - t.dmfdlat(i, j, k);
 }
 
 // operators_mod.F90:192-232 (+ interp_mod.F90:361-369,426-434)
 inline void calc_we_lev(Block& b, State& s, Tend& t, double dt) {
   const Mesh& mesh = b.mesh;
-  for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg + 1; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       double mf = 0.0;
       for (int l = 1; l <= k - 1; ++l) mf = mf + t.dmfdlon(i, j, l) + t.dmfdlat(i, j, l);
@@ -399,10 +399,10 @@ inline void calc_we_lev(Block& b, State& s, Tend& t, double dt) {
   }
   fill_halo(mesh, s.we_lev, true);
   accum_we_lev(b, b.adv_batch_mass, s.we_lev, s.m_lev, dt, true);
-  for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
     for (int j = mesh.full_lat_ibeg_no_pole; j <= mesh.full_lat_iend_no_pole; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.we_lev_lon(i, j, k) = (mesh.area_lon_west(j) * s.we_lev(i, j, k) + mesh.area_lon_east(j) * s.we_lev(i + 1, j, k)) / mesh.area_lon(j);
-  for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.we_lev_lat(i, j, k) = (mesh.area_lat_north(j) * s.we_lev(i, j + 1, k) + mesh.area_lat_south(j) * s.we_lev(i, j, k)) / mesh.area_lat(j);
 }
@@ -412,7 +412,7 @@ inline void calc_wedudlev_wedvdlev(Block& b, State& s, Tend& t) {
   const Mesh& mesh = b.mesh; const A3 &u = s.u_f, &v = s.v_f;
   const int kb = mesh.full_lev_ibeg, ke = mesh.full_lev_iend;
   const int jb = mesh.full_lat_ibeg_no_pole, je = mesh.full_lat_iend_no_pole;
-  for (int k = kb + 1; k <= ke - 1; ++k)
+  ORC_PAR for (int k = kb + 1; k <= ke - 1; ++k)
     for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.wedudlev(i, j, k) = (s.we_lev_lon(i, j, k + 1) * (u(i, j, k + 1) - u(i, j, k)) +
                              s.we_lev_lon(i, j, k) * (u(i, j, k) - u(i, j, k - 1))) / s.m_lon(i, j, k) / 2.0;
@@ -420,7 +420,7 @@ inline void calc_wedudlev_wedvdlev(Block& b, State& s, Tend& t) {
     t.wedudlev(i, j, kb) = (s.we_lev_lon(i, j, kb + 1) * (u(i, j, kb + 1) - u(i, j, kb))) / s.m_lon(i, j, kb) / 2.0;
   for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
     t.wedudlev(i, j, ke) = (s.we_lev_lon(i, j, ke) * (u(i, j, ke) - u(i, j, ke - 1))) / s.m_lon(i, j, ke) / 2.0;
-  for (int k = kb + 1; k <= ke - 1; ++k)
+  ORC_PAR for (int k = kb + 1; k <= ke - 1; ++k)
     for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       t.wedvdlev(i, j, k) = (s.we_lev_lat(i, j, k + 1) * (v(i, j, k + 1) - v(i, j, k)) +
                              s.we_lev_lat(i, j, k) * (v(i, j, k) - v(i, j, k - 1))) / s.m_lat(i, j, k) / 2.0;
@@ -433,7 +433,7 @@ inline void calc_wedudlev_wedvdlev(Block& b, State& s, Tend& t) {
 // operators_mod.F90:433-469
 inline void calc_gz_lev(Block& b, State& s) {
   const Mesh& mesh = b.mesh;
-  for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend - 1; ++k)
+  ORC_PAR for (int k = mesh.half_lev_ibeg; k <= mesh.half_lev_iend - 1; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       double dgz = 0.0;
       for (int l = k; l <= mesh.nlev; ++l)
@@ -441,7 +441,7 @@ inline void calc_gz_lev(Block& b, State& s) {
       s.gz_lev(i, j, k) = b.st.gzs(i, j) + dgz;
     }
   fill_halo(mesh, s.gz_lev, true);
-  for (int k = 1; k <= mesh.nlev; ++k)
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
     for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i)
       s.gz(i, j, k) = 0.5 * (s.gz_lev(i, j, k) + s.gz_lev(i, j, k + 1));
 }
@@ -452,16 +452,16 @@ inline void pgf_run(Block& b, State& s, Tend& t) {
   const int jb = mesh.full_lat_ibeg_no_pole, je = mesh.full_lat_iend_no_pole;
   if (!b.cfg.baroclinic) {
     const A3& gz = s.gz_f;
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         t.pgf_lon(i, j, k) = (gz(i + 1, j, k) - gz(i, j, k)) / mesh.de_lon(j);
-    for (int k = 1; k <= mesh.nlev; ++k)
+    ORC_PAR for (int k = 1; k <= mesh.nlev; ++k)
       for (int j = 1; j <= mesh.nhalf; ++j) for (int i = 1; i <= mesh.nlon; ++i)
         t.pgf_lat(i, j, k) = (gz(i, j + 1, k) - gz(i, j, k)) / mesh.de_lat(j);
     return;
   }
   const A3 &pe = s.ph_exn_lev, &gz = s.gz_lev;
-  for (int k = 1; k <= mesh.nlev; ++k) {
+  ORC_PAR for (int k = 1; k <= mesh.nlev; ++k) {
     for (int j = jb; j <= je; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
       double dph1 = pe(i + 1, j, k + 1) - pe(i, j, k);
       double dph2 = pe(i, j, k + 1) - pe(i + 1, j, k);

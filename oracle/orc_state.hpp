@@ -70,7 +70,7 @@ struct Filter {
 // T3: the whole tmp row incl. (stale) halo entries is copied back.
 inline void filter_full_lat(const Mesh& m, const Filter& f, A3& x, A3* y, int k0, int k1) {
   std::vector<double> tmp(x.ni, 0.0);
-  for (int k = k0; k <= k1; ++k)
+  ORC_PAR_FP(tmp) for (int k = k0; k <= k1; ++k)
     for (int j = m.full_lat_ibeg; j <= m.full_lat_iend; ++j) {
       if (f.nlon_at(j) > 1) {
         int n = f.nlon_at(j), hn = (n - 1) / 2; const double* w = f.wlon(j);
@@ -89,7 +89,7 @@ inline void filter_full_lat(const Mesh& m, const Filter& f, A3& x, A3* y, int k0
 // filter_on_lat_edge (filter_mod.F90:129-163)
 inline void filter_half_lat(const Mesh& m, const Filter& f, A3& x, A3* y, int k0, int k1) {
   std::vector<double> tmp(x.ni, 0.0);
-  for (int k = k0; k <= k1; ++k)
+  ORC_PAR_FP(tmp) for (int k = k0; k <= k1; ++k)
     for (int j = m.half_lat_ibeg; j <= m.half_lat_iend; ++j) {
       if (f.nlat_at(j) > 1) {
         int n = f.nlat_at(j), hn = (n - 1) / 2; const double* w = f.wlat(j);
@@ -140,7 +140,12 @@ struct Block {
   AdvBatch adv_batch_mass;
   std::vector<AdvBatch> adv_batches;   // block%adv_batches(:) (adv_mod.F90:314-418): non-dynamic 'cell' batches, each with its own samples
   std::string error;           // first log_error raised (reference aborts)
-  void fail(const std::string& s) { if (error.empty()) error = s; }
+  void fail(const std::string& s) {
+#if defined(_OPENMP) && defined(ORC_OPENMP_LOOPS)
+#pragma omp critical(orc_fail)
+#endif
+    if (error.empty()) error = s;
+  }
 };
 
 }  // namespace orc

@@ -33,19 +33,39 @@ def mem_available_gb():
         return 0.0
 
 
+# Tolerances for the work arrays.  The JW initial state has v = 0 exactly, so for the first steps every v-like
+# quantity (cfly, divy, ptf_lat) is a tiny residual next to its zonal partner, and every DIFFERENTIATED quantity
+# (divx / divy, cflz = RK4 of the column-integrated flux divergence, du, dpt) turns the grid-scale 1e-13 rounding noise
+# of the prognostic fields into noise / dx against a signal of field / L: an amplification of L / dx ~ 1e2 .. 1e3.
+# Each array is therefore normalised by the norm of the vector it is a component of (x and y partner together), and
+# held to 1e-11 when it is an interpolated / flux quantity and to 1e-9 when it is a derivative of one.
+WORK_PARTNER = {"cflx": "cfly", "cfly": "cflx", "divx": "divy", "divy": "divx", "qx": "qy", "qy": "qx",
+                "ptf_lon": "ptf_lat", "ptf_lat": "ptf_lon"}
+WORK_TOL = {"cflx": 1e-11, "cfly": 1e-11, "qx": 1e-11, "qy": 1e-11, "ptf_lon": 1e-11, "ptf_lat": 1e-11,
+            "divx": 1e-9, "divy": 1e-9, "cflz": 1e-9, "du": 1e-9, "dpt": 1e-9}
+
+
 def work_errors(host, orc, gpu):
-    """rel L2 of the last stage's work arrays.  Oracle side: mass-batch arrays; ptf_* of the star state of the
-    last wrfrk3 stage (state 3); du / dpt of tend1 = tend(old at the time of the step) = tend(orc.new_index now)."""
-    errs = {}
+    """Error of the last stage's work arrays, each relative to the RMS size of its vector (see WORK_TOL).
+    Oracle side: mass-batch arrays; ptf_* of the star state of the last wrfrk3 stage (state 3); du / dpt of
+    tend1 = tend(old at the time of the step) = tend(orc.new_index now)."""
+    pairs = {}
     for name, loc in WORK_BATCH:
         a = host.interior(gpu.field(name), loc); b = host.interior(orc.field(name), loc)
         if name == "cflz":
             a, b = a[1:-1], b[1:-1]
-        errs[name] = rel_l2(a, b)
+        pairs[name] = (a, b)
     for name, loc in (("ptf_lon", "lon"), ("ptf_lat", "lat")):
-        errs[name] = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name, 3), loc))
+        pairs[name] = (host.interior(gpu.field(name), loc), host.interior(orc.field(name, 3), loc))
     for name, loc in (("du", "lon"), ("dpt", "cell")):
-        errs[name] = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name, orc.new_index), loc))
+        pairs[name] = (host.interior(gpu.field(name), loc), host.interior(orc.field(name, orc.new_index), loc))
+    rms = lambda x: float(np.sqrt(np.mean(np.square(x))))
+    errs = {}
+    for name, (a, b) in pairs.items():
+        scale = rms(b)
+        if name in WORK_PARTNER:
+            scale = max(scale, rms(pairs[WORK_PARTNER[name]][1]))
+        errs[name] = rms(a - b) / scale if scale > 0 else rms(a - b)
     return errs
 
 
@@ -57,9 +77,19 @@ def test_c2_mountain_zonal_flow_720x360(gpu_required):
     assert_diag_close(gpu.diagnose(), orc.diagnose())
     for step in range(3):
         dg = gpu.run_steps(1); do = orc.run_steps(1)
+        # |v| is a small residual of this zonal flow (RMS v ~ 1e-3 of RMS u after two steps): ONE ulp of gz
+        # (7e-12 m2/s2, from a differently rounded reciprocal upstream) divided by de_lat and times dt is 1e-14 m/s
+        # = 2e-12 of ||v||.  The meridional wind is therefore held to 1e-12 of the RMS wind speed (the size of the
+        # vector it is a component of) and to 1e-11 of its own norm; every other field to 1e-12 of its own norm.
+        wind = np.sqrt(np.mean(host.interior(orc.field("u_lon"), "lon") ** 2))
         for name, loc in PROGNOSTIC_SWM + [("u_f", "lon"), ("v_f", "lat"), ("gz_f", "cell"), ("pv", "vtx")]:
-            e = rel_l2(host.interior(gpu.field(name), loc), host.interior(orc.field(name), loc))
-            assert e <= TOL, (step, name, e)
+            a = host.interior(gpu.field(name), loc); b = host.interior(orc.field(name), loc)
+            e = rel_l2(a, b)
+            if name in ("v_lat", "v_f"):
+                assert np.sqrt(np.mean((a - b) ** 2)) <= TOL * wind, (step, name, e)
+                assert e <= 10 * TOL, (step, name, e)
+            else:
+                assert e <= TOL, (step, name, e)
         assert_diag_close(dg, do)
     gpu.close()
 
@@ -93,7 +123,7 @@ def test_work_arrays_of_the_last_stage(gpu_required, nlon, nlat, nlev, dt):
         dg = gpu.run_steps(1); do = orc.run_steps(1)
         check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
         errs = work_errors(host, orc, gpu)
-        bad = {k: v for k, v in errs.items() if not v <= 1e-11}
+        bad = {k: v for k, v in errs.items() if not v <= WORK_TOL[k]}
         assert not bad, f"step {step}: {bad}"
         assert_diag_close(dg, do)
     if nlon == 1440:      # the case must actually reach the |cflx| >= 1 branch
