@@ -108,17 +108,38 @@ def test_c3_baroclinic_wave_360x180x32(gpu_required):
     gpu.close()
 
 
+def cross_polar_flow(host, ic, U=20.0):
+    """Adds a solid-body rotation whose axis lies in the equatorial plane (the flow of the reference's
+    mountain_zonal_flow / solid_rotation cases with alpha = 90 degrees: u = U cos(lon) sin(lat), v = -U sin(lon)),
+    so that air crosses both poles.  The JW jet vanishes at the poles, where |cflx| stays ~0.06 at 0.25 degrees; with
+    20 m/s across the pole the zonal CFL number of the polar rows is ~5: integer-CFL gathers and whole-cell
+    segment sums in the FFSL x sweeps and out-of-window RK4 gathers, INSIDE the dynamics."""
+    hl = host.vec["half_lon"][host.hx:host.hx + host.nlon]; fl = host.vec["full_lon"][host.hx:host.hx + host.nlon]
+    sf = host.vec["full_sin_lat"][host.hy:host.hy + host.nlat]
+    host.interior(ic["u_lon"], "lon")[...] += U * np.cos(hl)[None, None, :] * sf[None, :, None]
+    host.interior(ic["v_lat"], "lat")[...] += -U * np.sin(fl)[None, None, :]
+    return ic
+
+
 @pytest.mark.parametrize("nlon,nlat,nlev,dt", [(360, 180, 32, 150.0), (1440, 720, 4, 30.0)])
 def test_work_arrays_of_the_last_stage(gpu_required, nlon, nlat, nlev, dt):
     """The WORK list (CFL numbers, FFSL intermediates, fluxes, forward tendencies) against the oracle, without a
     tracer batch (it would reuse qx / qy / ptf_* after the dynamics).  The 1440x720 case is the full-width one:
-    247-tap filter rows (max_hn = 123), |cflx| >= 1 on the polar rows inside the dynamics -- the same row length
-    as BASELINE configs[4] at 1/8 of the levels (equal_eta coordinate)."""
+    247-tap filter rows (max_hn = 123) and, with a cross-polar flow added to the JW state, |cflx| >= 1 on the polar
+    rows inside the dynamics -- the same row length as BASELINE configs[4] at 1/8 of the levels (equal_eta)."""
     if nlon == 1440 and mem_available_gb() < 40:
         pytest.skip("needs ~25 GB of host memory for the oracle")
-    host, ic, orc, gpu = start(nlon, nlat, nlev, dt, "baroclinic_wave", ntracers=0)
     if nlon == 1440:
+        from gmcore_b200.host import Host
+        from gmcore_b200.model import GmcoreGPU
+        from oracle.orc import Oracle
+        host = Host(nlon, nlat, nlev, dt, "baroclinic_wave", ntracers=0)
         assert host.hx >= 100, host.hx
+        ic = cross_polar_flow(host, host.initial_condition())
+        orc = Oracle(host); orc.set_state(ic); gpu = GmcoreGPU(host); gpu.set_state(ic)
+        orc.prepare_run(); gpu.prepare_run()
+    else:
+        host, ic, orc, gpu = start(nlon, nlat, nlev, dt, "baroclinic_wave", ntracers=0)
     for step in range(2):
         dg = gpu.run_steps(1); do = orc.run_steps(1)
         check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
@@ -128,7 +149,7 @@ def test_work_arrays_of_the_last_stage(gpu_required, nlon, nlat, nlev, dt):
         assert_diag_close(dg, do)
     if nlon == 1440:      # the case must actually reach the |cflx| >= 1 branch
         cflx = host.interior(gpu.field("cflx"), "lon")
-        assert np.abs(cflx).max() >= 1.0, np.abs(cflx).max()
+        assert np.abs(cflx).max() >= 2.0, np.abs(cflx).max()
     gpu.close()
 
 
@@ -137,7 +158,15 @@ def test_fullwidth_with_tracer_1440x720x4(gpu_required):
     lon_damp on 1440-point rows."""
     if mem_available_gb() < 40:
         pytest.skip("needs ~25 GB of host memory for the oracle")
-    host, ic, orc, gpu = start(1440, 720, 4, 30.0, "baroclinic_wave")
+    from gmcore_b200.host import Host
+    from gmcore_b200.model import GmcoreGPU
+    from oracle.orc import Oracle
+    host = Host(1440, 720, 4, 30.0, "baroclinic_wave")
+    ic = cross_polar_flow(host, host.initial_condition())
+    orc = Oracle(host); orc.set_state(ic); gpu = GmcoreGPU(host); gpu.set_state(ic)
+    q = smooth_tracer(host, host.cfg.ntracers)
+    orc.set_tracers(q); gpu.set_tracers(q)
+    orc.prepare_run(); gpu.prepare_run()
     for step in range(3):
         dg = gpu.run_steps(1); do = orc.run_steps(1)
         check(host, orc, gpu, PROGNOSTIC_HYDRO, TOL, f"step {step}")
