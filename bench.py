@@ -286,6 +286,12 @@ def _main(out):
         gpu = make_band_nccl(host, rank, world, local)
     else:
         gpu = GmcoreGPU(host, device=local)
+    # N > 1: the serial-vs-parallel check of the NCCL path, outside every timed region (small grid, this rank's band
+    # over ncclSend/Recv with the overlap on against one band on the same device; bar 1e-13)
+    bpar = None
+    if banded:
+        from gmcore_b200.model import band_parity
+        bpar = band_parity(rank, world, local)
     gpu.set_state(ic)
     q0 = None
     if host.cfg.ntracers:
@@ -398,6 +404,8 @@ def _main(out):
                            "time_scheme": "wrfrk3", "hx": host.hx, "parallelism": (f"{world} latitude bands ({band_rows} rows: {band_sizes}), NCCL halo exchange" if banded else f"replicas x{world}") if world > 1 else "1 GPU",
                            "l2": "flushed between timed steps (256 MB write)" if flush else "working set >> L2 (no flush)"},
                 "gpu_launches": launches, "clocks": clk, "e2e": e2e, "roofline": roofline, "cpu_baseline": cb}
+        if bpar is not None:
+            line["band_parity"] = bpar
         print(json.dumps(line), file=out, flush=True)
     gpu.close()
     if world > 1:

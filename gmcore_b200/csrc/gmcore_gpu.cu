@@ -293,6 +293,15 @@ int gmc_group_link(gmc_handle** hs, int n) {
     if (r > 0) { if (b->owns_stream && b->stream) cudaStreamDestroy(b->stream); b->stream = hs[0]->stream; b->owns_stream = false; }
     b->group = grp;
   }
+  // The production ordering (edge rows -> ev_edge -> exchange on a second stream next to the interior rows ->
+  // ev_xdone) on ONE device too, so that the single-GPU band tests exercise the same row split and event
+  // dependencies as the NCCL path (GMCORE_NO_OVERLAP=1 restores the single-stream order in both modes).
+  { const char* e = getenv("GMCORE_NO_OVERLAP"); if (!(e && e[0] == '1')) for (int r = 0; r < n; ++r) {
+    gmc_handle* b = hs[r];
+    if (b->comm_stream) continue;
+    cudaStreamCreateWithFlags(&b->comm_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&b->ev_edge, cudaEventDisableTiming); cudaEventCreateWithFlags(&b->ev_xdone, cudaEventDisableTiming);
+  } }
   return 0;
 }
 // (b) one process per GPU: rank 0 creates the id, the host broadcasts its 128 bytes (MPI_Bcast /

@@ -83,12 +83,13 @@ static int do_step(gmc_handle* h, int old_, int star, int nw, double dt) {
   if (h->comm_stream) {
     // the edge rows of new%{u_f, v_f, pt, phs_f} are final at ev_edge: the exchange runs on comm_stream next to
     // the interior rows of the last filter launches; the compute stream rejoins before it touches halo rows
+    // (band group: every band's edge event; all bands share the leader's compute stream)
     cudaStream_t s0 = h->stream;
-    cudaStreamWaitEvent(h->comm_stream, h->ev_edge, 0);
-    h->stream = h->comm_stream;
+    for_bands(h, [&](gmc_handle* b) { cudaStreamWaitEvent(h->comm_stream, b->ev_edge, 0); });
+    for_bands(h, [&](gmc_handle* b) { b->stream = h->comm_stream; });
     const int rc = halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); });
     cudaEventRecord(h->ev_xdone, h->comm_stream);
-    h->stream = s0;
+    for_bands(h, [&](gmc_handle* b) { b->stream = s0; });
     cudaStreamWaitEvent(s0, h->ev_xdone, 0);
     if (rc) return 1;
   } else if (halo_exchange(h, [&](gmc_handle* b) { return stage_halo_set(b, nw); })) return 1;

@@ -495,3 +495,44 @@ class GmcoreBandGroup:
     def close(self):
         for b in self.bands:
             b.close()
+
+
+def band_parity(rank, world, device, nlon=192, nlat=97, nlev=16, dt=300.0, nsteps=6, case="baroclinic_wave"):
+    """The reference's serial-vs-parallel check for the NCCL path: this rank's latitude band of a `world`-rank run
+    (stage exchange over ncclSend/ncclRecv, overlapped with the interior filter rows unless GMCORE_NO_OVERLAP=1)
+    against ONE band owning the sphere on the same device, on this rank's own rows.  Needs an initialised
+    torch.distributed NCCL group.  Returns {"worst_rel_l2", "diag"} (max over ranks); the bar is 1e-13."""
+    import torch
+    import torch.distributed as dist
+    from .host import Host
+    host = Host(nlon, nlat, nlev, dt, case)
+    ic = host.initial_condition()
+    q = np.zeros((host.cfg.ntracers,) + host.shape("cell"))
+    kk, jj, ii = np.meshgrid(np.arange(q.shape[1]), np.arange(q.shape[2]), np.arange(q.shape[3]), indexing="ij")
+    q[0] = 1.0 + 0.5 * np.sin(2 * np.pi * ii / q.shape[3]) * np.cos(np.pi * (jj / q.shape[2] - 0.5)) + 0.01 * kk
+    band = make_band_nccl(host, rank, world, device)
+    band.set_state(ic); band.set_tracers(q); band.prepare_run()
+    db = band.run_steps(nsteps)
+    one = GmcoreGPU(host, device=device)
+    one.set_state(ic); one.set_tracers(q); one.prepare_run()
+    d1 = one.run_steps(nsteps)
+    hy, hx = host.hy, host.hx
+    worst = 0.0
+    for name, loc in (("u_lon", "lon"), ("v_lat", "lat"), ("pt", "cell"), ("phs", "2d"), ("u_f", "lon"), ("v_f", "lat")):
+        a = band.field(name); b = band_slice(host, band.cfg, one.field(name), loc)
+        if loc == "2d":
+            a = a.reshape(a.shape[-2:]); b = b.reshape(b.shape[-2:])
+        a = a[..., hy:a.shape[-2] - hy, hx:-hx]; b = b[..., hy:b.shape[-2] - hy, hx:-hx]
+        if loc != "2d":
+            a = a[2:2 + nlev]; b = b[2:2 + nlev]
+        worst = max(worst, float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)))
+    qa = band.get_tracers()[0]; qb = band_slice(host, band.cfg, one.get_tracers()[0], "cell")
+    sl = (slice(2, 2 + nlev), slice(hy, -hy), slice(hx, -hx))
+    worst = max(worst, float(np.linalg.norm((qa - qb)[sl].ravel()) / np.linalg.norm(qb[sl].ravel())))
+    dd = float(np.abs(db[:, [0, 1, 7]] / d1[:, [0, 1, 7]] - 1).max())
+    band.close(); one.close()
+    t = torch.tensor([worst, dd], dtype=torch.float64, device=f"cuda:{device}")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"worst_rel_l2": float(t[0].item()), "diag": float(t[1].item()),
+            "case": f"{case} {nlon}x{nlat}x{nlev}, {nsteps} steps, {world} NCCL bands vs 1 band, overlap "
+                    f"{'off' if os.environ.get('GMCORE_NO_OVERLAP') == '1' else 'on'}"}
