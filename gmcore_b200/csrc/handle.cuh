@@ -44,6 +44,14 @@ struct Profiler {
   case 6: LAUNCH(h, kern<6>, __VA_ARGS__); break; \
   default: LAUNCH(h, kern<1>, __VA_ARGS__); } } while (0)
 
+// the same for kernels with a second (bool) template parameter; profiled under the name kern_<flag>
+#define LAUNCH2_(h, kern, M_, flag, ...) do { if (flag) LAUNCH(h, kern##_in<M_>, __VA_ARGS__); else LAUNCH(h, kern##_out<M_>, __VA_ARGS__); } while (0)
+#define LAUNCH_LIM2(h, kern, flag, ...) do { switch ((h)->cfg.limiter_type + 4 * (h)->cfg.ffsl_flux_type) { \
+  case 0: LAUNCH2_(h, kern, 0, flag, __VA_ARGS__); break; case 2: LAUNCH2_(h, kern, 2, flag, __VA_ARGS__); break; \
+  case 4: LAUNCH2_(h, kern, 4, flag, __VA_ARGS__); break; case 5: LAUNCH2_(h, kern, 5, flag, __VA_ARGS__); break; \
+  case 6: LAUNCH2_(h, kern, 6, flag, __VA_ARGS__); break; \
+  default: LAUNCH2_(h, kern, 1, flag, __VA_ARGS__); } } while (0)
+
 // adv_batch_type (adv_batch_mod.F90:19-69) of a non-dynamic 'cell' batch
 struct TrBatch {
   int ntr = 0; double dt = 0; int nstep = 1;

@@ -4,6 +4,7 @@
 #pragma once
 #include <cmath>
 #include "kernels_hydro.cuh"
+#include "kernels_ffsl.cuh"
 
 static inline VC make_vc(const gmc_handle* h) {
   const gmc_config& c = h->cfg;
@@ -182,6 +183,28 @@ static void run_pole_sum(gmc_handle* h, const double* f, double* out, double* ro
 struct BatchRef { const double *u, *v, *mfx, *mfy, *cflx, *cfly, *divx, *divy; };
 static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double* flx, double* fly, double dt) {
   const Geo gw = xg(h, 3, 4), gn = xg(h, 1, 1), g0 = h->g;
+  static const bool old_path = getenv("GMCORE_OLD_HFLX") && getenv("GMCORE_OLD_HFLX")[0] == '1';   // round-1 kernels (A/B runs)
+  static const bool tile_path = getenv("GMCORE_FFSL_TILE") && getenv("GMCORE_FFSL_TILE")[0] == '1';   // 2-D tile variant (measured slower)
+  if (!old_path) {
+    // inner advective half step: fluxes stay on chip, the block writes qx / qy (and the pole-adjacent y fluxes)
+    const Geo g01 = xg(h, 0, 1);
+    FfslArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qx, h->qy, B.divx, B.divy, h->qmfy, dt, gw.jb, gw.je, gn.jb, gn.je, g01.jb, g01.je};
+    if (tile_path) LAUNCH_LIM(h, k_ffsl_in, ffsl_grid(gw, gw.nlev), dim3(32, FT_Y), 0, gw, h->M, in);
+    else { const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj), FM_W, 0, gw, h->M, in, rj); }
+    if (g0.has_south || g0.has_north) {
+      run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);
+      FfslQArgs qa{q, h->qmfx, h->qmfy, B.divx, B.divy, h->pole_work, h->qx, h->qy, dt, g01.jb, g01.je};
+      for (int north = 0; north < 2; ++north) {            // the two pole rows (ffsl_mod.F90:375-406)
+        if (north ? !g0.has_north : !g0.has_south) continue;
+        Geo gp = gw; gp.jb = gp.je = north ? gw.nlat : 1;
+        LAUNCH(h, k_ffsl_q, tile_grid(gp, gp.nlev), tile_block(), 0, gp, h->M, qa);
+      }
+    }
+    FfslArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, nullptr, nullptr, nullptr, 0.0, g0.jb, g01.je, gn.jb, gn.je, 0, 0};
+    if (tile_path) LAUNCH_LIM(h, k_ffsl_out, ffsl_grid(gn, gn.nlev), dim3(32, FT_Y), 0, gn, h->M, out);
+    else { const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj), FM_W, 0, gn, h->M, out, rj); }
+    return;
+  }
   HflxArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qmfx, h->qmfy, gw.jb, gw.je, gn.jb, gn.je};
   LAUNCH_LIM(h, k_hflx, tile_grid(gw, gw.nlev), tile_block(), 0, gw, in);
   run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);

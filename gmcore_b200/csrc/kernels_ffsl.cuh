@@ -1,0 +1,386 @@
+// FFSL horizontal sweeps with block-shared limited slopes (round 2).
+//
+// hflx_ppm_cell (ffsl_mod.F90:778-881) builds the PPM coefficients of EVERY cell once (three mono-limited slopes
+// per cell and direction, :813-826) and then lets each edge pick the coefficients of its upwind cell.  The round-1
+// kernel (k_hflx, kernels_hydro.cuh) re-formed those coefficients per EDGE from a 5-point window, i.e. three limited
+// slopes per edge and direction -- every cell's slope was evaluated three times by three neighbouring threads, and the
+// kernel was bound by FP64 / issue slots (432 instructions per point, FP64 pipe 64 %), not by bytes.  Here a block owns
+// a tile of FT_X x FT_Y cells:
+//   phase 1  one limited slope per cell and direction (x: of mx along the row, y: of my along the column), stored in
+//            shared memory with the apron the tile's edges need (2 cells west / 2 east, 2 rows south / 2 north);
+//   phase 2  each edge selects its upwind cell (west / east, south / north neighbour; |cfl| < 1), reads that cell's
+//            three slopes from shared memory and its three values through L1, and evaluates the PPM edge values and
+//            the flux integral ONCE (ffsl_mod.F90:1147-1173, 831-851).  Lanes with |cflx| >= 1 (polar rows) take the
+//            round-1 gather path (own 5-point stencil + whole-cell segment sum, :831-848);
+//   phase 3  (inner call of ffsl_calc_tracer_hflx_cell only, :354-372) the fluxes stay in shared memory and the block
+//            forms the half-step fields qx, qy directly: the inner fluxes are never written to HBM and the separate
+//            k_ffsl_q pass (7 array passes) is gone.  Only the pole rows -- whose qy needs a zonal mean of the
+//            pole-adjacent y fluxes (:375-406) -- are finished by k_ffsl_q on those two rows.
+// Arithmetic is operation-for-operation the round-1 one (same slope, edge-value and integral expressions), so the
+// results are bit-identical to k_hflx + k_ffsl_q.
+//   algorithmic passes: inner 7 reads (u, v, q, cflx, cfly, divx, divy) + 2 writes (qx, qy) = 9;
+//                       outer 6 reads (mfx, mfy, qy, qx, cflx, cfly) + 2 writes = 8      
+#pragma once
+#include "kernels_hydro.cuh"
+
+#ifndef FT_X
+#define FT_X 128          // tile width in cells: FT_X / 32 points per thread, a warp's points 32 apart (coalesced)
+#endif
+#ifndef FT_Y
+#define FT_Y 8            // tile rows = warps per block
+#endif
+#define FT_Q (FT_X / 32)
+
+struct FfslArgs {
+  const double *u, *v;          // advecting wind (inner) or mass flux (outer)
+  const double *mx, *my;        // field swept in x / in y
+  const double *cflx, *cfly;
+  double *ox, *oy;              // outer: mfx, mfy      inner: qx, qy
+  const double *divx, *divy;    // inner only
+  double *qmfy;                 // inner only: y flux on the two pole-adjacent half rows (for the zonal means)
+  double dt;
+  int jx0, jx1, jy0, jy1;       // rows of the x flux / half rows of the y flux (band mode)
+  int jq0, jq1;                 // inner only: rows of qy
+};
+
+// limited slope of cell (f) from its two neighbours: exactly the slope expressions inside ppm() / vl_slope()
+template <int MODE> __device__ __forceinline__ double cell_slope(double fm1, double f, double fp1) {
+  return slope_mono_d<MODE>(f - fm1, fp1 - f, (fp1 - fm1) * 0.5, f);
+}
+// PPM edge values + parabola of one cell from its three slopes (ffsl_mod.F90:1156-1172; same expressions as ppm())
+__device__ __forceinline__ void ppm_from_slopes(double fm1, double f, double fp1, double dfl, double dfc, double dfr,
+                                                double& fl, double& df, double& f6) {
+  fl = 0.5 * (fm1 + f) + (dfl - dfc) * (1.0 / 6.0);
+  double fr = 0.5 * (fp1 + f) + (dfc - dfr) * (1.0 / 6.0);
+  fl = f - fsign(dmin(fabs(dfc), fabs(fl - f)), dfc);
+  fr = f + fsign(dmin(fabs(dfc), fabs(fr - f)), dfc);
+  f6 = 6 * f - 3 * (fl + fr);
+  df = fr - fl;
+}
+
+// x flux through the east edge of cell (i, j); sx = this row's slopes, indexed by tile-local cell + 2
+template <bool EDGE, int LIM> __device__ __forceinline__ double ffsl_flux_x(const double* __restrict__ mxr, const double* __restrict__ sx,
+                                                                           int i, int lc, int n, double cx, double uu) {
+  if (cx == 0) return 0.0;
+  int ci = (int)cx;
+  if (ci >= n || ci <= -n) ci = 0;      // |cflx| > lon_halo_width: the guard word is already up (k_cfl); stay in the row
+  const double cf = cx - ci;
+  const bool pos = cx > 0;
+  if (ci == 0) {
+    const int o = pos ? 0 : 1;                           // upwind cell = i + o
+    const double f = __ldg(mxr + wrapE<EDGE>(i + o, n));
+    const double dfc = sx[lc + o + 2];
+    if (LIM >= 4) {
+      const double t = pos ? cf * (f + dfc * 0.5 * (1 - cf)) : cf * (f - dfc * 0.5 * (1 + cf));
+      return qdiv(uu * t, cx);
+    }
+    const double fm1 = __ldg(mxr + wrapE<EDGE>(i + o - 1, n)), fp1 = __ldg(mxr + wrapE<EDGE>(i + o + 1, n));
+    const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+    double ml, dm, m6;
+    ppm_from_slopes(fm1, f, fp1, sx[lc + o + 1], dfc, sx[lc + o + 3], ml, dm, m6);
+    return qdiv((pos ? uu : -uu) * ppm_integral(0.0, ml, dm, m6, s1, s2), cx);
+  }
+  // |cflx| >= 1: gather around the lane's own upwind cell and add the whole-cell segment sum (ffsl_mod.F90:831-848)
+  const int iu = wrapi(pos ? i - ci : i - ci + 1, n);
+  const double x0 = __ldg(mxr + wrapi(iu - 2, n)), x1 = __ldg(mxr + wrapi(iu - 1, n)), x2 = __ldg(mxr + iu);
+  const double x3 = __ldg(mxr + wrapi(iu + 1, n)), x4 = __ldg(mxr + wrapi(iu + 2, n));
+  double sm = 0;
+  if (pos) { for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+  else { for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+  if (LIM >= 4) return vl_flux<LIM>(x1, x2, x3, sm, cf, cx, uu);
+  const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+  double ml, dm, m6;
+  ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
+  return qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
+}
+// y flux through the north edge of cell (i, j) (half row j); sy = this column's slopes, sy[r * FT_X] = row j0 - 2 + r
+template <int LIM> __device__ __forceinline__ double ffsl_flux_y(const double* __restrict__ my, const Geo& g, const double* __restrict__ sy,
+                                                                 int i, int j, int k, int lr, double cy, double vv, bool direct) {
+  const bool pos = cy > 0;
+  const int o = pos ? 0 : 1;                             // upwind cell = row j + o
+  if (LIM < 4 && cy == 0) return 0.0;
+  const double f = direct ? __ldg(my + gidx(g, i, j + o, k)) : ldF(my, g, i, j + o, k);
+  const double dfc = sy[(lr + o + 2) * FT_X];
+  if (LIM >= 4) return vv * (f + dfc * 0.5 * (copysign(1.0, cy) - cy));      // ffsl_mod.F90:605-611: no zero-CFL branch
+  const double fm1 = direct ? __ldg(my + gidx(g, i, j + o - 1, k)) : ldF(my, g, i, j + o - 1, k);
+  const double fp1 = direct ? __ldg(my + gidx(g, i, j + o + 1, k)) : ldF(my, g, i, j + o + 1, k);
+  const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
+  double ml, dm, m6;
+  ppm_from_slopes(fm1, f, fp1, sy[(lr + o + 1) * FT_X], dfc, sy[(lr + o + 3) * FT_X], ml, dm, m6);
+  return qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
+}
+
+template <bool EDGE, int LIM, bool INNER> __device__ __forceinline__ void ffsl_tile(const Geo& g, const DMesh& M, const FfslArgs& a,
+                                                                                  double* __restrict__ Sx, double* __restrict__ Sy,
+                                                                                  double* __restrict__ Fx, double* __restrict__ Fy) {
+  const int n = g.nlon, tx = threadIdx.x, ty = threadIdx.y, k = blockIdx.z;
+  const int x0 = blockIdx.x * FT_X, j0 = g.jb + blockIdx.y * FT_Y;
+  const int j = j0 + ty;
+  const bool rowok = j <= g.je;
+  const bool dox = rowok && j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;     // warp-uniform
+  const bool doy = rowok && j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
+  // rows j0-3 .. j0+FT_Y+2 are read by the y sweep: away from the poles they sit at fixed strides from one address
+  const bool direct = j0 - 3 >= 1 && j0 + FT_Y + 2 <= g.nlat;                     // block-uniform
+  // ---- phase 1: one limited slope per cell and direction ---------------------------------------------
+  if (dox) {
+    const double* __restrict__ mxr = a.mx + gidx(g, 0, j, k);
+    double* __restrict__ sx = Sx + ty * (FT_X + 4);
+#pragma unroll
+    for (int q = 0; q < FT_Q; ++q) {
+      const int lc = tx + 32 * q, c = x0 + lc;
+      if (c <= n + 1) sx[lc + 2] = cell_slope<LIM>(__ldg(mxr + wrapE<EDGE>(c - 1, n)), __ldg(mxr + wrapE<EDGE>(c, n)), __ldg(mxr + wrapE<EDGE>(c + 1, n)));
+    }
+    if (tx < 4) {                                        // apron cells x0-2, x0-1, x0+FT_X, x0+FT_X+1
+      const int lc = tx < 2 ? tx - 2 : FT_X + tx - 2, c = x0 + lc;
+      if (c <= n + 1) sx[lc + 2] = cell_slope<LIM>(__ldg(mxr + wrapi(c - 1, n)), __ldg(mxr + wrapi(c, n)), __ldg(mxr + wrapi(c + 1, n)));
+    }
+  }
+  {
+    // slopes in y of rows j0-2 .. j0+FT_Y+1; row r is needed when it is within one row below / two rows above a
+    // y-flux row (the upwind cell of half row jy is jy or jy+1 and its PPM needs the slopes of its two neighbours)
+    for (int rr = ty; rr < FT_Y + 4; rr += FT_Y) {
+      const int r = j0 - 2 + rr;
+      if (r < a.jy0 - 1 || r > a.jy1 + 2 || r > g.je + 2) continue;                // warp-uniform
+      double* __restrict__ sy = Sy + rr * FT_X;
+#pragma unroll
+      for (int q = 0; q < FT_Q; ++q) {
+        const int lc = tx + 32 * q, i = x0 + lc;
+        if (i >= n) continue;
+        double fm1, f, fp1;
+        if (direct) { const double* __restrict__ p = a.my + gidx(g, i, r, k); fm1 = __ldg(p - n); f = __ldg(p); fp1 = __ldg(p + n); }
+        else { fm1 = ldF(a.my, g, i, r - 1, k); f = ldF(a.my, g, i, r, k); fp1 = ldF(a.my, g, i, r + 1, k); }
+        sy[lc] = cell_slope<LIM>(fm1, f, fp1);
+      }
+    }
+  }
+  __syncthreads();
+  // ---- phase 2: fluxes ----------------------------------------------------------------------------------
+  const double* __restrict__ mxr = a.mx + gidx(g, 0, rowok ? j : g.je, k);
+  const double* __restrict__ sx = Sx + ty * (FT_X + 4);
+  const int rb = gidx(g, 0, rowok ? j : g.je, k);
+#pragma unroll
+  for (int q = 0; q < FT_Q; ++q) {
+    const int lc = tx + 32 * q, i = x0 + lc;
+    if (i >= n) continue;
+    const int c = rb + i;
+    double fx = 0, fy = 0;
+    if (dox) fx = ffsl_flux_x<EDGE, LIM>(mxr, sx, i, lc, n, __ldg(a.cflx + c), __ldg(a.u + c));
+    if (doy) fy = ffsl_flux_y<LIM>(a.my, g, Sy + lc, i, j, k, ty, __ldg(a.cfly + c), __ldg(a.v + c), direct);
+    if (!INNER) {
+      if (dox) a.ox[c] = fx;
+      if (doy) a.oy[c] = fy;
+    } else {
+      Fx[ty * (FT_X + 1) + lc + 1] = fx;
+      Fy[(ty + 1) * FT_X + lc] = fy;
+      if (doy && (j == 1 || j == g.nhalf)) a.qmfy[c] = fy;      // pole-adjacent half rows: zonal means of the pole rows
+    }
+  }
+  if (!INNER) return;
+  // west apron edge x0-1 of every row, south apron half row j0-1 (one extra flux per row / per column)
+  if (tx == 0 && dox) {
+    const int i = wrapi(x0 - 1, n), c = rb + i;
+    Fx[ty * (FT_X + 1)] = ffsl_flux_x<true, LIM>(mxr, sx, i, -1, n, __ldg(a.cflx + c), __ldg(a.u + c));
+  }
+  if (ty == 0) {
+    const int js = j0 - 1;
+    const bool doys = js >= 1 && js <= g.nhalf && js >= a.jy0 && js <= a.jy1;
+#pragma unroll
+    for (int q = 0; q < FT_Q; ++q) {
+      const int lc = tx + 32 * q, i = x0 + lc;
+      if (i >= n) continue;
+      double fy = 0;
+      if (doys) { const int c = gidx(g, i, js, k); fy = ffsl_flux_y<LIM>(a.my, g, Sy + lc, i, js, k, -1, __ldg(a.cfly + c), __ldg(a.v + c), direct); }
+      Fy[lc] = fy;
+    }
+  }
+  __syncthreads();
+  // ---- phase 3: half-step fields of the inner advective step (ffsl_mod.F90:354-372) ------------------------
+  if (!dox) return;                                       // pole rows are finished by k_ffsl_q after the zonal means
+  const RowCoef* __restrict__ R = M.rows + (j + 1);
+  const double rac = R->r_area_cell, lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
+  const bool doq = j >= a.jq0 && j <= a.jq1;
+#pragma unroll
+  for (int q = 0; q < FT_Q; ++q) {
+    const int lc = tx + 32 * q, i = x0 + lc;
+    if (i >= n) continue;
+    const int c = rb + i;
+    const double qv = __ldg(a.mx + c);
+    const double fx0 = Fx[ty * (FT_X + 1) + lc + 1], fxm = Fx[ty * (FT_X + 1) + lc];
+    a.ox[c] = qv - 0.5 * ((fx0 - fxm) * lel * rac - __ldg(a.divx + c) * qv) * a.dt;
+    if (doq) {
+      const double fy0 = Fy[(ty + 1) * FT_X + lc], fys = Fy[ty * FT_X + lc];
+      a.oy[c] = qv - 0.5 * ((fy0 * lea - fys * leas) * rac - __ldg(a.divy + c) * qv) * a.dt;
+    }
+  }
+}
+
+// ---- row-marching variant -------------------------------------------------------------------------------
+// A block owns FM_W columns of one level and marches over a strip of rows.  The y sweep lives entirely in
+// registers: every thread keeps the 5 values / 4 limited slopes of its own column that the two candidate upwind
+// cells of the current half row need, and rolls them by one row per iteration (one new load and ONE new slope per
+// row -- no y apron at all except the 5 start-up rows of a strip).  The x sweep shares the row through shared
+// memory: the row of mx (+3 apron cells either side) is staged, every thread forms the slope of its own cell, and
+// each edge reads the three slopes and values of its upwind cell.  Operands of row r+1 are loaded while row r is
+// computed (software pipelining), so the only exposed latency is the shared-memory round trip between barriers.
+#ifndef FM_W
+#define FM_W 128
+#endif
+#ifndef FM_MINB
+#define FM_MINB 6
+#endif
+template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_march_body(const Geo& g, const DMesh& M, const FfslArgs& a, int rj) {
+  __shared__ double xr[2][FM_W + 6];     // x-swept field of the current row, cells x0-3 .. x0+FM_W+2
+  __shared__ double sxr[2][FM_W + 4];    // its limited slopes, cells x0-2 .. x0+FM_W+1
+  __shared__ double fxr[2][FM_W + 1];    // INNER: x fluxes of the edges x0-1 .. x0+FM_W-1
+  const int n = g.nlon, tx = threadIdx.x, k = blockIdx.z, x0 = blockIdx.x * FM_W, i = x0 + tx;
+  const bool act = i < n;
+  // idle lanes of the last block: the first three stand in for the wrapped cells n, n+1, n+2 of the x sweep (their
+  // row values feed the slopes of the row's last cells), the rest read a valid column; none of them stores anything
+  const int ic = act ? i : (i <= n + 2 ? i - n : n - 1);
+  const int rs = g.jb + blockIdx.y * rj;
+  if (rs > g.je) return;
+  const int re = rs + rj - 1 > g.je ? g.je : rs + rj - 1;
+  const int r0 = INNER ? rs - 1 : rs;    // INNER: qy of the strip's first row needs the y flux below it
+  // y windows: rows jy0-2 .. jy1+3 are the only ones the y sweep may read (band mode: materialised halo rows)
+  const int ylo = a.jy0 - 2, yhi = a.jy1 + 3;
+  const bool direct = r0 - 2 >= 1 && re + 3 <= g.nlat;       // no pole mirror inside this strip's windows
+  auto ldy = [&](int r) -> double {
+    if (r < ylo || r > yhi) return 0.0;
+    return direct ? __ldg(a.my + gidx(g, ic, r, k)) : ldF(a.my, g, ic, r, k);
+  };
+  // apron cell handled by this thread (threads 0..5): x0-3..x0-1 and x0+FM_W..x0+FM_W+2
+  const int alc = tx < 3 ? tx - 3 : FM_W + tx - 3;
+  const bool hasap = tx < 6 && x0 + alc <= n + 2;
+  const int aic = wrapi(x0 + alc, n);
+  auto rowx = [&](int r) { return r > 1 && r < g.nlat && r >= a.jx0 && r <= a.jx1 && r >= rs; };   // block-uniform
+  auto rowy = [&](int r) { return r >= 1 && r <= g.nhalf && r >= a.jy0 && r <= a.jy1; };
+  // ---- start-up: the y window of row r0 ----------------------------------------------------------------
+  double fm1 = ldy(r0 - 1), f0 = ldy(r0), fp1 = ldy(r0 + 1), fp2 = ldy(r0 + 2), fp3 = ldy(r0 + 3);
+  double sm1, s0, sp1;
+  { const double fm2 = ldy(r0 - 2);
+    sm1 = cell_slope<LIM>(fm2, fm1, f0); s0 = cell_slope<LIM>(fm1, f0, fp1); sp1 = cell_slope<LIM>(f0, fp1, fp2); }
+  // operands of the current row (pipelined: the next row's are loaded one iteration ahead)
+  double cx = 0, uu = 0, cy = 0, vv = 0, xv = 0, xa = 0, dvx = 0, dvy = 0, cxw = 0, uuw = 0;
+  auto load_row = [&](int r, double& cx_, double& uu_, double& cy_, double& vv_, double& xv_, double& xa_, double& dvx_, double& dvy_,
+                      double& cxw_, double& uuw_) {
+    if (r > re) return;
+    const int c = gidx(g, ic, r, k);
+    if (rowx(r)) {
+      cx_ = __ldg(a.cflx + c); uu_ = __ldg(a.u + c);
+      if (a.mx != a.my || r < ylo || r > yhi) xv_ = __ldg(a.mx + c);
+      if (hasap) xa_ = __ldg(a.mx + gidx(g, aic, r, k));
+      if (INNER) { dvx_ = __ldg(a.divx + c); if (tx == 0) { const int cw = gidx(g, wrapi(x0 - 1, n), r, k); cxw_ = __ldg(a.cflx + cw); uuw_ = __ldg(a.u + cw); } }
+    }
+    if (rowy(r)) { cy_ = __ldg(a.cfly + c); vv_ = __ldg(a.v + c); }
+    if (INNER && r >= a.jq0 && r <= a.jq1) dvy_ = __ldg(a.divy + c);
+  };
+  load_row(r0, cx, uu, cy, vv, xv, xa, dvx, dvy, cxw, uuw);
+  double fy_prev = 0;                    // INNER: y flux of half row r-1
+  for (int r = r0; r <= re; ++r) {
+    const int b = r & 1;
+    // ---- issue the next row's loads -------------------------------------------------------------------
+    double ncx = 0, nuu = 0, ncy = 0, nvv = 0, nxv = 0, nxa = 0, ndvx = 0, ndvy = 0, ncxw = 0, nuuw = 0;
+    load_row(r + 1, ncx, nuu, ncy, nvv, nxv, nxa, ndvx, ndvy, ncxw, nuuw);
+    const double fp4 = r + 1 <= re ? ldy(r + 4) : 0.0;
+    const bool dox = rowx(r), doy = rowy(r);
+    const int c = gidx(g, ic, r, k);
+    // ---- y sweep: registers only --------------------------------------------------------------------------
+    const double sp2 = cell_slope<LIM>(fp1, fp2, fp3);
+    double fy = 0;
+    if (doy) {
+      const bool pos = cy > 0;
+      const double f = pos ? f0 : fp1, dfc = pos ? s0 : sp1;
+      if (LIM >= 4) fy = vv * (f + dfc * 0.5 * (copysign(1.0, cy) - cy));       // ffsl_mod.F90:605-611
+      else if (cy != 0) {
+        const double fa = pos ? fm1 : f0, fb = pos ? fp1 : fp2, dfl = pos ? sm1 : s0, dfr = pos ? sp1 : sp2;
+        const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
+        double ml, dm, m6;
+        ppm_from_slopes(fa, f, fb, dfl, dfc, dfr, ml, dm, m6);
+        fy = qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
+      }
+      if (!INNER) { if (act) a.oy[c] = fy; }
+      else if (act && (r == 1 || r == g.nhalf)) a.qmfy[c] = fy;     // pole-adjacent half rows: zonal means of the pole rows
+    }
+    // ---- x sweep: the row shared through shared memory --------------------------------------------------
+    if (dox) {
+      const double qv = (a.mx != a.my || r < ylo || r > yhi) ? xv : f0;   // mx == my: the row value is already in the y window
+      xr[b][tx + 3] = qv;
+      if (hasap) xr[b][alc + 3] = xa;
+      __syncthreads();
+      sxr[b][tx + 2] = cell_slope<LIM>(xr[b][tx + 2], qv, xr[b][tx + 4]);
+      if (tx < 4) { const int lc = tx < 2 ? tx - 2 : FM_W + tx - 2; sxr[b][lc + 2] = cell_slope<LIM>(xr[b][lc + 2], xr[b][lc + 3], xr[b][lc + 4]); }
+      __syncthreads();
+      const double* __restrict__ mxr = a.mx + gidx(g, 0, r, k);
+      auto flux_x = [&](int lc, int ii, double cx_, double uu_) -> double {
+        if (cx_ == 0) return 0.0;
+        int ci = (int)cx_;
+        if (ci >= n || ci <= -n) ci = 0;
+        const double cf = cx_ - ci; const bool pos = cx_ > 0;
+        if (ci == 0) {
+          const int o = lc + (pos ? 0 : 1);              // tile-local upwind cell
+          const double f = xr[b][o + 3], dfc = sxr[b][o + 2];
+          if (LIM >= 4) { const double t = pos ? cf * (f + dfc * 0.5 * (1 - cf)) : cf * (f - dfc * 0.5 * (1 + cf)); return qdiv(uu_ * t, cx_); }
+          const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+          double ml, dm, m6;
+          ppm_from_slopes(xr[b][o + 2], f, xr[b][o + 4], sxr[b][o + 1], dfc, sxr[b][o + 3], ml, dm, m6);
+          return qdiv((pos ? uu_ : -uu_) * ppm_integral(0.0, ml, dm, m6, s1, s2), cx_);
+        }
+        // |cflx| >= 1: own 5-point stencil around the upwind cell + whole-cell segment sum (ffsl_mod.F90:831-848)
+        const int iu = wrapi(pos ? ii - ci : ii - ci + 1, n);
+        const double x0_ = __ldg(mxr + wrapi(iu - 2, n)), x1 = __ldg(mxr + wrapi(iu - 1, n)), x2 = __ldg(mxr + iu);
+        const double x3 = __ldg(mxr + wrapi(iu + 1, n)), x4 = __ldg(mxr + wrapi(iu + 2, n));
+        double sm = 0;
+        if (pos) { for (int l = ii + 1 - ci; l <= ii; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+        else { for (int l = ii + 1; l <= ii - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+        if (LIM >= 4) return vl_flux<LIM>(x1, x2, x3, sm, cf, cx_, uu_);
+        const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+        double ml, dm, m6;
+        ppm<LIM>(x0_, x1, x2, x3, x4, ml, dm, m6);
+        return qdiv((pos ? uu_ : -uu_) * ppm_integral(sm, ml, dm, m6, s1, s2), cx_);
+      };
+      const double fx = flux_x(tx, ic, cx, uu);
+      if (!INNER) { if (act) a.ox[c] = fx; }
+      else {
+        fxr[b][tx + 1] = fx;
+        if (tx == 0) fxr[b][0] = flux_x(-1, wrapi(x0 - 1, n), cxw, uuw);
+        __syncthreads();
+        if (act) {
+          const RowCoef* __restrict__ R = M.rows + (r + 1);
+          const double rac = R->r_area_cell;
+          a.ox[c] = qv - 0.5 * ((fx - fxr[b][tx]) * R->le_lon * rac - dvx * qv) * a.dt;
+          if (r >= a.jq0 && r <= a.jq1) a.oy[c] = qv - 0.5 * ((fy * R->le_lat - fy_prev * R[-1].le_lat) * rac - dvy * qv) * a.dt;
+        }
+      }
+    }
+    // ---- roll the window ----------------------------------------------------------------------------------
+    fy_prev = fy;
+    fm1 = f0; f0 = fp1; fp1 = fp2; fp2 = fp3; fp3 = fp4;
+    sm1 = s0; s0 = sp1; sp1 = sp2;
+    cx = ncx; uu = nuu; cy = ncy; vv = nvv; xv = nxv; xa = nxa; dvx = ndvx; dvy = ndvy; cxw = ncxw; uuw = nuuw;
+  }
+}
+// named entry points (the profiler keys on the kernel name): inner = half-step fields, outer = fluxes
+template <int LIM> __global__ void __launch_bounds__(FM_W, FM_MINB) k_ffsl_march_in(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, true>(g, M, a, rj); }
+template <int LIM> __global__ void __launch_bounds__(FM_W, FM_MINB) k_ffsl_march_out(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, false>(g, M, a, rj); }
+// strips of about 40 rows: the 5 start-up rows of a strip cost ~12 % more loads of `my`, the grid keeps >= 4 waves
+static inline int ffsl_strip_rows(const Geo& g) {
+  const int rows = g.je - g.jb + 1;
+  const int strips = (rows + 39) / 40;
+  return (rows + strips - 1) / strips;
+}
+static inline dim3 ffsl_march_grid(const Geo& g, int nk, int rj) { return dim3((g.nlon + FM_W - 1) / FM_W, (g.je - g.jb + 1 + rj - 1) / rj, nk); }
+
+#ifndef FFSL_MINB
+#define FFSL_MINB 3
+#endif
+template <int LIM> __global__ void __launch_bounds__(32 * FT_Y, FFSL_MINB) k_ffsl_out(Geo g, DMesh M, FfslArgs a) {
+  __shared__ double Sx[FT_Y * (FT_X + 4)], Sy[(FT_Y + 4) * FT_X];
+  if (blockIdx.x == 0 || (int)(blockIdx.x + 1) * FT_X + 3 > g.nlon) ffsl_tile<true, LIM, false>(g, M, a, Sx, Sy, nullptr, nullptr);
+  else ffsl_tile<false, LIM, false>(g, M, a, Sx, Sy, nullptr, nullptr);
+}
+template <int LIM> __global__ void __launch_bounds__(32 * FT_Y, FFSL_MINB) k_ffsl_in(Geo g, DMesh M, FfslArgs a) {
+  __shared__ double Sx[FT_Y * (FT_X + 4)], Sy[(FT_Y + 4) * FT_X], Fx[FT_Y * (FT_X + 1)], Fy[(FT_Y + 1) * FT_X];
+  if (blockIdx.x == 0 || (int)(blockIdx.x + 1) * FT_X + 3 > g.nlon) ffsl_tile<true, LIM, true>(g, M, a, Sx, Sy, Fx, Fy);
+  else ffsl_tile<false, LIM, true>(g, M, a, Sx, Sy, Fx, Fy);
+}
+static inline dim3 ffsl_grid(const Geo& g, int nk) { return dim3((g.nlon + FT_X - 1) / FT_X, (g.je - g.jb + 1 + FT_Y - 1) / FT_Y, nk); }
