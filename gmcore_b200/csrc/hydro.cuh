@@ -190,7 +190,7 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
     const Geo g01 = xg(h, 0, 1);
     FfslArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qx, h->qy, B.divx, B.divy, h->qmfy, dt, gw.jb, gw.je, gn.jb, gn.je, g01.jb, g01.je};
     if (tile_path) LAUNCH_LIM(h, k_ffsl_in, ffsl_grid(gw, gw.nlev), dim3(32, FT_Y), 0, gw, h->M, in);
-    else { const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj), FM_W, 0, gw, h->M, in, rj); }
+    else { const int rj = ffsl_strip_rows(gw), w = ffsl_block_width(gw.nlon); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj, w), w, 0, gw, h->M, in, rj); }
     if (g0.has_south || g0.has_north) {
       run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);
       FfslQArgs qa{q, h->qmfx, h->qmfy, B.divx, B.divy, h->pole_work, h->qx, h->qy, dt, g01.jb, g01.je};
@@ -202,7 +202,7 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
     }
     FfslArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, nullptr, nullptr, nullptr, 0.0, g0.jb, g01.je, gn.jb, gn.je, 0, 0};
     if (tile_path) LAUNCH_LIM(h, k_ffsl_out, ffsl_grid(gn, gn.nlev), dim3(32, FT_Y), 0, gn, h->M, out);
-    else { const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj), FM_W, 0, gn, h->M, out, rj); }
+    else { const int rj = ffsl_strip_rows(gn), w = ffsl_block_width(gn.nlon); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj, w), w, 0, gn, h->M, out, rj); }
     return;
   }
   HflxArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qmfx, h->qmfy, gw.jb, gw.je, gn.jb, gn.je};

@@ -215,75 +215,128 @@ template <bool EDGE, int LIM, bool INNER> __device__ __forceinline__ void ffsl_t
 }
 
 // ---- row-marching variant -------------------------------------------------------------------------------
-// A block owns FM_W columns of one level and marches over a strip of rows.  The y sweep lives entirely in
+// A block owns blockDim.x columns of one level and marches over a strip of rows.  The y sweep lives entirely in
 // registers: every thread keeps the 5 values / 4 limited slopes of its own column that the two candidate upwind
 // cells of the current half row need, and rolls them by one row per iteration (one new load and ONE new slope per
 // row -- no y apron at all except the 5 start-up rows of a strip).  The x sweep shares the row through shared
 // memory: the row of mx (+3 apron cells either side) is staged, every thread forms the slope of its own cell, and
-// each edge reads the three slopes and values of its upwind cell.  Operands of row r+1 are loaded while row r is
-// computed (software pipelining), so the only exposed latency is the shared-memory round trip between barriers.
-#ifndef FM_W
-#define FM_W 128
+// each edge reads the three slopes and values of its upwind cell.  Within a strip every load address is valid for
+// every row (rows are clamped to the strip / to the y window), so the loop body carries no load predicates; which
+// results are stored is decided by block-uniform row ranges.
+#define FM_WMAX 256
+#define FM_RJMAX 64        // rows per strip (ffsl_strip_rows stays below this)
+// measured at 0.25 deg L32 (tools/kprof.py): outer 0.538 / 0.466 / 0.487 ms at 2 / 3 / 4 blocks of 256 per SM
+// (109 / 72 / 64 registers), inner 0.741 / 0.788 / 0.932 ms (128 / 80 / 64 registers, the last two spill)
+#ifndef FM_MINB_IN
+#define FM_MINB_IN 2
 #endif
-#ifndef FM_MINB
-#define FM_MINB 6
+#ifndef FM_MINB_OUT
+#define FM_MINB_OUT 3
 #endif
+// |cflx| >= 1 (polar rows): own 5-point stencil around the upwind cell + whole-cell segment sum (ffsl_mod.F90:831-848)
+template <int LIM> __device__ __noinline__ double ffsl_flux_x_gather(const double* __restrict__ mxr, int ii, int n, double cx, double uu) {
+  int ci = (int)cx;
+  const double cf = cx - ci; const bool pos = cx > 0;
+  const int iu = wrapi(pos ? ii - ci : ii - ci + 1, n);
+  const double x0 = __ldg(mxr + wrapi(iu - 2, n)), x1 = __ldg(mxr + wrapi(iu - 1, n)), x2 = __ldg(mxr + iu);
+  const double x3 = __ldg(mxr + wrapi(iu + 1, n)), x4 = __ldg(mxr + wrapi(iu + 2, n));
+  double sm = 0;
+  if (pos) { for (int l = ii + 1 - ci; l <= ii; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+  else { for (int l = ii + 1; l <= ii - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
+  if (LIM >= 4) return vl_flux<LIM>(x1, x2, x3, sm, cf, cx, uu);
+  const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+  double ml, dm, m6;
+  ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
+  return qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
+}
+// flux through the east edge of tile-local cell lc (global column ii) from the staged row xs / slopes ss
+template <int LIM> __device__ __forceinline__ double ffsl_flux_x_smem(const double* __restrict__ xs, const double* __restrict__ ss,
+                                                                      const double* __restrict__ mxr, int lc, int ii, int n, double cx, double uu) {
+  if (cx == 0) return 0.0;
+  const int ci = (int)cx;
+  if (ci != 0 && ci < n && ci > -n) return ffsl_flux_x_gather<LIM>(mxr, ii, n, cx, uu);
+  // (|cflx| >= nlon: the guard word is already up (k_cfl); treated as a fractional CFL to stay in the row)
+  const double cf = cx;
+  const bool pos = cx > 0;
+  const int o = lc + (pos ? 0 : 1);                       // tile-local upwind cell
+  const double f = xs[o + 3], dfc = ss[o + 2];
+  if (LIM >= 4) { const double t = pos ? cf * (f + dfc * 0.5 * (1 - cf)) : cf * (f - dfc * 0.5 * (1 + cf)); return qdiv(uu * t, cx); }
+  const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
+  double ml, dm, m6;
+  ppm_from_slopes(xs[o + 2], f, xs[o + 4], ss[o + 1], dfc, ss[o + 3], ml, dm, m6);
+  return qdiv((pos ? uu : -uu) * ppm_integral(0.0, ml, dm, m6, s1, s2), cx);
+}
 template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_march_body(const Geo& g, const DMesh& M, const FfslArgs& a, int rj) {
-  __shared__ double xr[2][FM_W + 6];     // x-swept field of the current row, cells x0-3 .. x0+FM_W+2
-  __shared__ double sxr[2][FM_W + 4];    // its limited slopes, cells x0-2 .. x0+FM_W+1
-  __shared__ double fxr[2][FM_W + 1];    // INNER: x fluxes of the edges x0-1 .. x0+FM_W-1
-  const int n = g.nlon, tx = threadIdx.x, k = blockIdx.z, x0 = blockIdx.x * FM_W, i = x0 + tx;
+  __shared__ double xr[2][FM_WMAX + 6];     // x-swept field of the current row, cells x0-3 .. x0+W+2
+  __shared__ double sxr[2][FM_WMAX + 4];    // its limited slopes, cells x0-2 .. x0+W+1
+  __shared__ double fxr[INNER ? 2 : 1][INNER ? FM_WMAX + 1 : 1];    // INNER: x fluxes of the edges x0-1 .. x0+W-1
+  __shared__ double rcf[INNER ? FM_RJMAX : 1][4];                   // INNER: row coefficients of the strip
+  const int n = g.nlon, W = blockDim.x, tx = threadIdx.x, x0 = blockIdx.x * W, i = x0 + tx;
+  const int rs = g.jb + blockIdx.y * rj;
+  if (rs > g.je) return;
+  const int re = rs + rj - 1 > g.je ? g.je : rs + rj - 1;
+  const int r0 = INNER ? rs - 1 : rs;       // INNER: qy of the strip's first row needs the y flux below it
   const bool act = i < n;
   // idle lanes of the last block: the first three stand in for the wrapped cells n, n+1, n+2 of the x sweep (their
   // row values feed the slopes of the row's last cells), the rest read a valid column; none of them stores anything
   const int ic = act ? i : (i <= n + 2 ? i - n : n - 1);
-  const int rs = g.jb + blockIdx.y * rj;
-  if (rs > g.je) return;
-  const int re = rs + rj - 1 > g.je ? g.je : rs + rj - 1;
-  const int r0 = INNER ? rs - 1 : rs;    // INNER: qy of the strip's first row needs the y flux below it
-  // y windows: rows jy0-2 .. jy1+3 are the only ones the y sweep may read (band mode: materialised halo rows)
+  // block-uniform row ranges: x flux (and qx), y flux, qy; y windows may only read rows ylo .. yhi
+  const int xlo = max(max(a.jx0, rs), 2), xhi = min(min(a.jx1, re), g.nlat - 1);
+  const int flo = max(a.jy0, 1), fhi = min(a.jy1, g.nhalf);
   const int ylo = a.jy0 - 2, yhi = a.jy1 + 3;
-  const bool direct = r0 - 2 >= 1 && re + 3 <= g.nlat;       // no pole mirror inside this strip's windows
-  auto ldy = [&](int r) -> double {
+  const bool direct = r0 - 2 >= 1 && re + 3 <= g.nlat && r0 - 2 >= ylo && re + 3 <= yhi;   // plain strided y windows
+  const bool same = a.mx == a.my && rs >= ylo && re <= yhi;       // inner call: the row value is already in the y window
+  const double* __restrict__ pmy = a.my; const double* __restrict__ pmx = a.mx;
+  const double* __restrict__ pcx = a.cflx; const double* __restrict__ pcy = a.cfly;
+  const double* __restrict__ pu = a.u; const double* __restrict__ pv = a.v;
+  auto ldy = [&](int r) -> double {         // generic y-window load (strips touching a pole or the band's y range)
     if (r < ylo || r > yhi) return 0.0;
-    return direct ? __ldg(a.my + gidx(g, ic, r, k)) : ldF(a.my, g, ic, r, k);
+    return ldF(pmy, g, ic, r, blockIdx.z);
   };
-  // apron cell handled by this thread (threads 0..5): x0-3..x0-1 and x0+FM_W..x0+FM_W+2
-  const int alc = tx < 3 ? tx - 3 : FM_W + tx - 3;
+  int c = gidx(g, ic, r0, blockIdx.z);      // element index of (ic, r, k); advances by n per row
+  // apron cell of this thread (threads 0..5): x0-3 .. x0-1 and x0+W .. x0+W+2
+  const int alc = tx < 3 ? tx - 3 : W + tx - 3;
   const bool hasap = tx < 6 && x0 + alc <= n + 2;
-  const int aic = wrapi(x0 + alc, n);
-  auto rowx = [&](int r) { return r > 1 && r < g.nlat && r >= a.jx0 && r <= a.jx1 && r >= rs; };   // block-uniform
-  auto rowy = [&](int r) { return r >= 1 && r <= g.nhalf && r >= a.jy0 && r <= a.jy1; };
+  const int dca = wrapi(x0 + alc, n) - ic;  // column offset of the apron cell from this thread's own column
+  const int dcw = wrapi(x0 - 1, n) - ic;    // ... of the west edge x0-1 (thread 0, INNER)
   // ---- start-up: the y window of row r0 ----------------------------------------------------------------
-  double fm1 = ldy(r0 - 1), f0 = ldy(r0), fp1 = ldy(r0 + 1), fp2 = ldy(r0 + 2), fp3 = ldy(r0 + 3);
-  double sm1, s0, sp1;
-  { const double fm2 = ldy(r0 - 2);
-    sm1 = cell_slope<LIM>(fm2, fm1, f0); s0 = cell_slope<LIM>(fm1, f0, fp1); sp1 = cell_slope<LIM>(f0, fp1, fp2); }
-  // operands of the current row (pipelined: the next row's are loaded one iteration ahead)
-  double cx = 0, uu = 0, cy = 0, vv = 0, xv = 0, xa = 0, dvx = 0, dvy = 0, cxw = 0, uuw = 0;
-  auto load_row = [&](int r, double& cx_, double& uu_, double& cy_, double& vv_, double& xv_, double& xa_, double& dvx_, double& dvy_,
-                      double& cxw_, double& uuw_) {
-    if (r > re) return;
-    const int c = gidx(g, ic, r, k);
-    if (rowx(r)) {
-      cx_ = __ldg(a.cflx + c); uu_ = __ldg(a.u + c);
-      if (a.mx != a.my || r < ylo || r > yhi) xv_ = __ldg(a.mx + c);
-      if (hasap) xa_ = __ldg(a.mx + gidx(g, aic, r, k));
-      if (INNER) { dvx_ = __ldg(a.divx + c); if (tx == 0) { const int cw = gidx(g, wrapi(x0 - 1, n), r, k); cxw_ = __ldg(a.cflx + cw); uuw_ = __ldg(a.u + cw); } }
+  double fm1, f0, fp1, fp2, fp3, sm1, s0, sp1;
+  {
+    double fm2;
+    if (direct) { const double* __restrict__ p = pmy + c; fm2 = __ldg(p - 2 * n); fm1 = __ldg(p - n); f0 = __ldg(p); fp1 = __ldg(p + n); fp2 = __ldg(p + 2 * n); fp3 = __ldg(p + 3 * n); }
+    else { fm2 = ldy(r0 - 2); fm1 = ldy(r0 - 1); f0 = ldy(r0); fp1 = ldy(r0 + 1); fp2 = ldy(r0 + 2); fp3 = ldy(r0 + 3); }
+    sm1 = cell_slope<LIM>(fm2, fm1, f0); s0 = cell_slope<LIM>(fm1, f0, fp1); sp1 = cell_slope<LIM>(f0, fp1, fp2);
+  }
+  // every operand of a row is loaded one iteration ahead (the loop body never waits on HBM)
+  double xv = same ? 0.0 : __ldg(pmx + c), xa = hasap ? __ldg(pmx + c + dca) : 0.0;
+  double cy = __ldg(pcy + c), vv = __ldg(pv + c), cx = __ldg(pcx + c), uu = __ldg(pu + c);
+  double dvx = 0, dvy = 0, cxw = 0, uuw = 0;
+  if (INNER) {
+    dvx = __ldg(a.divx + c); dvy = __ldg(a.divy + c);
+    if (tx == 0) { cxw = __ldg(pcx + c + dcw); uuw = __ldg(pu + c + dcw); }
+    // this strip's row coefficients (le_lon, 1/area_cell, le_lat of rows r and r-1) once, in shared memory
+    for (int t = tx; t <= re - rs; t += W) {
+      const RowCoef* __restrict__ R = M.rows + (rs + t + 1);
+      rcf[t][0] = R->le_lon; rcf[t][1] = R->r_area_cell; rcf[t][2] = R->le_lat; rcf[t][3] = R[-1].le_lat;
     }
-    if (rowy(r)) { cy_ = __ldg(a.cfly + c); vv_ = __ldg(a.v + c); }
-    if (INNER && r >= a.jq0 && r <= a.jq1) dvy_ = __ldg(a.divy + c);
-  };
-  load_row(r0, cx, uu, cy, vv, xv, xa, dvx, dvy, cxw, uuw);
-  double fy_prev = 0;                    // INNER: y flux of half row r-1
-  for (int r = r0; r <= re; ++r) {
+    __syncthreads();
+  }
+  double fy_prev = 0;                        // INNER: y flux of half row r-1
+  for (int r = r0; r <= re; ++r, c += n) {
     const int b = r & 1;
-    // ---- issue the next row's loads -------------------------------------------------------------------
-    double ncx = 0, nuu = 0, ncy = 0, nvv = 0, nxv = 0, nxa = 0, ndvx = 0, ndvy = 0, ncxw = 0, nuuw = 0;
-    load_row(r + 1, ncx, nuu, ncy, nvv, nxv, nxa, ndvx, ndvy, ncxw, nuuw);
-    const double fp4 = r + 1 <= re ? ldy(r + 4) : 0.0;
-    const bool dox = rowx(r), doy = rowy(r);
-    const int c = gidx(g, ic, r, k);
+    const int cn = r < re ? c + n : c;      // next row, clamped to the strip: always a valid address
+    // ---- loads for the NEXT row, and the y window's new row -----------------------------------------------
+    const double ncy = __ldg(pcy + cn), nvv = __ldg(pv + cn), ncx = __ldg(pcx + cn), nuu = __ldg(pu + cn);
+    double ndvx = 0, ndvy = 0, ncxw = 0, nuuw = 0;
+    if (INNER) { ndvx = __ldg(a.divx + cn); ndvy = __ldg(a.divy + cn); if (tx == 0) { ncxw = __ldg(pcx + cn + dcw); nuuw = __ldg(pu + cn + dcw); } }
+    const double nxv = same ? 0.0 : __ldg(pmx + cn), nxa = hasap ? __ldg(pmx + cn + dca) : 0.0;
+    double fp4;
+    if (direct) fp4 = __ldg(pmy + (r < re ? c + 4 * n : c + 3 * n));          // the last iteration re-reads row re+3 (unused)
+    else fp4 = ldy(r + 4);
+    const bool dox = r >= xlo && r <= xhi, doy = r >= flo && r <= fhi;          // block-uniform
+    // ---- x sweep, part 1: stage the row ------------------------------------------------------------------
+    const double qv = same ? f0 : xv;
+    if (dox) { xr[b][tx + 3] = qv; if (hasap) xr[b][alc + 3] = xa; }
     // ---- y sweep: registers only --------------------------------------------------------------------------
     const double sp2 = cell_slope<LIM>(fp1, fp2, fp3);
     double fy = 0;
@@ -301,54 +354,24 @@ template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_march_body(c
       if (!INNER) { if (act) a.oy[c] = fy; }
       else if (act && (r == 1 || r == g.nhalf)) a.qmfy[c] = fy;     // pole-adjacent half rows: zonal means of the pole rows
     }
-    // ---- x sweep: the row shared through shared memory --------------------------------------------------
+    // ---- x sweep, part 2 -----------------------------------------------------------------------------------
     if (dox) {
-      const double qv = (a.mx != a.my || r < ylo || r > yhi) ? xv : f0;   // mx == my: the row value is already in the y window
-      xr[b][tx + 3] = qv;
-      if (hasap) xr[b][alc + 3] = xa;
       __syncthreads();
       sxr[b][tx + 2] = cell_slope<LIM>(xr[b][tx + 2], qv, xr[b][tx + 4]);
-      if (tx < 4) { const int lc = tx < 2 ? tx - 2 : FM_W + tx - 2; sxr[b][lc + 2] = cell_slope<LIM>(xr[b][lc + 2], xr[b][lc + 3], xr[b][lc + 4]); }
+      if (tx < 4) { const int lc = tx < 2 ? tx - 2 : W + tx - 2; sxr[b][lc + 2] = cell_slope<LIM>(xr[b][lc + 2], xr[b][lc + 3], xr[b][lc + 4]); }
       __syncthreads();
-      const double* __restrict__ mxr = a.mx + gidx(g, 0, r, k);
-      auto flux_x = [&](int lc, int ii, double cx_, double uu_) -> double {
-        if (cx_ == 0) return 0.0;
-        int ci = (int)cx_;
-        if (ci >= n || ci <= -n) ci = 0;
-        const double cf = cx_ - ci; const bool pos = cx_ > 0;
-        if (ci == 0) {
-          const int o = lc + (pos ? 0 : 1);              // tile-local upwind cell
-          const double f = xr[b][o + 3], dfc = sxr[b][o + 2];
-          if (LIM >= 4) { const double t = pos ? cf * (f + dfc * 0.5 * (1 - cf)) : cf * (f - dfc * 0.5 * (1 + cf)); return qdiv(uu_ * t, cx_); }
-          const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
-          double ml, dm, m6;
-          ppm_from_slopes(xr[b][o + 2], f, xr[b][o + 4], sxr[b][o + 1], dfc, sxr[b][o + 3], ml, dm, m6);
-          return qdiv((pos ? uu_ : -uu_) * ppm_integral(0.0, ml, dm, m6, s1, s2), cx_);
-        }
-        // |cflx| >= 1: own 5-point stencil around the upwind cell + whole-cell segment sum (ffsl_mod.F90:831-848)
-        const int iu = wrapi(pos ? ii - ci : ii - ci + 1, n);
-        const double x0_ = __ldg(mxr + wrapi(iu - 2, n)), x1 = __ldg(mxr + wrapi(iu - 1, n)), x2 = __ldg(mxr + iu);
-        const double x3 = __ldg(mxr + wrapi(iu + 1, n)), x4 = __ldg(mxr + wrapi(iu + 2, n));
-        double sm = 0;
-        if (pos) { for (int l = ii + 1 - ci; l <= ii; ++l) sm += __ldg(mxr + wrapi(l, n)); }
-        else { for (int l = ii + 1; l <= ii - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
-        if (LIM >= 4) return vl_flux<LIM>(x1, x2, x3, sm, cf, cx_, uu_);
-        const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
-        double ml, dm, m6;
-        ppm<LIM>(x0_, x1, x2, x3, x4, ml, dm, m6);
-        return qdiv((pos ? uu_ : -uu_) * ppm_integral(sm, ml, dm, m6, s1, s2), cx_);
-      };
-      const double fx = flux_x(tx, ic, cx, uu);
+      const double* __restrict__ mxr = pmx + (c - ic);
+      const double fx = ffsl_flux_x_smem<LIM>(xr[b], sxr[b], mxr, tx, ic, n, cx, uu);
       if (!INNER) { if (act) a.ox[c] = fx; }
       else {
         fxr[b][tx + 1] = fx;
-        if (tx == 0) fxr[b][0] = flux_x(-1, wrapi(x0 - 1, n), cxw, uuw);
+        if (tx == 0) fxr[b][0] = ffsl_flux_x_smem<LIM>(xr[b], sxr[b], mxr, -1, ic + dcw, n, cxw, uuw);
         __syncthreads();
         if (act) {
-          const RowCoef* __restrict__ R = M.rows + (r + 1);
-          const double rac = R->r_area_cell;
-          a.ox[c] = qv - 0.5 * ((fx - fxr[b][tx]) * R->le_lon * rac - dvx * qv) * a.dt;
-          if (r >= a.jq0 && r <= a.jq1) a.oy[c] = qv - 0.5 * ((fy * R->le_lat - fy_prev * R[-1].le_lat) * rac - dvy * qv) * a.dt;
+          const double* __restrict__ rc = rcf[r - rs];
+          const double rac = rc[1];
+          a.ox[c] = qv - 0.5 * ((fx - fxr[b][tx]) * rc[0] * rac - dvx * qv) * a.dt;
+          if (r >= a.jq0 && r <= a.jq1) a.oy[c] = qv - 0.5 * ((fy * rc[2] - fy_prev * rc[3]) * rac - dvy * qv) * a.dt;
         }
       }
     }
@@ -356,19 +379,26 @@ template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_march_body(c
     fy_prev = fy;
     fm1 = f0; f0 = fp1; fp1 = fp2; fp2 = fp3; fp3 = fp4;
     sm1 = s0; s0 = sp1; sp1 = sp2;
-    cx = ncx; uu = nuu; cy = ncy; vv = nvv; xv = nxv; xa = nxa; dvx = ndvx; dvy = ndvy; cxw = ncxw; uuw = nuuw;
+    xv = nxv; xa = nxa; cy = ncy; vv = nvv; cx = ncx; uu = nuu;
+    if (INNER) { dvx = ndvx; dvy = ndvy; cxw = ncxw; uuw = nuuw; }
   }
 }
 // named entry points (the profiler keys on the kernel name): inner = half-step fields, outer = fluxes
-template <int LIM> __global__ void __launch_bounds__(FM_W, FM_MINB) k_ffsl_march_in(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, true>(g, M, a, rj); }
-template <int LIM> __global__ void __launch_bounds__(FM_W, FM_MINB) k_ffsl_march_out(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, false>(g, M, a, rj); }
+template <int LIM> __global__ void __launch_bounds__(FM_WMAX, FM_MINB_IN) k_ffsl_march_in(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, true>(g, M, a, rj); }
+template <int LIM> __global__ void __launch_bounds__(FM_WMAX, FM_MINB_OUT) k_ffsl_march_out(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_march_body<LIM, false>(g, M, a, rj); }
 // strips of about 40 rows: the 5 start-up rows of a strip cost ~12 % more loads of `my`, the grid keeps >= 4 waves
 static inline int ffsl_strip_rows(const Geo& g) {
   const int rows = g.je - g.jb + 1;
   const int strips = (rows + 39) / 40;
   return (rows + strips - 1) / strips;
 }
-static inline dim3 ffsl_march_grid(const Geo& g, int nk, int rj) { return dim3((g.nlon + FM_W - 1) / FM_W, (g.je - g.jb + 1 + rj - 1) / rj, nk); }
+// block width: the multiple of 32 in 96..256 that wastes the fewest lanes on the last block of a row
+static inline int ffsl_block_width(int nlon) {
+  int best = 128, waste = 1 << 30;
+  for (int w = 96; w <= FM_WMAX; w += 32) { const int x = (nlon + w - 1) / w * w - nlon; if (x < waste || (x == waste && w == 128)) { waste = x; best = w; } }
+  return best;
+}
+static inline dim3 ffsl_march_grid(const Geo& g, int nk, int rj, int w) { return dim3((g.nlon + w - 1) / w, (g.je - g.jb + 1 + rj - 1) / rj, nk); }
 
 #ifndef FFSL_MINB
 #define FFSL_MINB 3

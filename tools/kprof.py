@@ -14,7 +14,8 @@ host = Host(wl["nlon"], wl["nlat"], wl["nlev"], wl["dt"], wl["case"])
 gpu = GmcoreGPU(host)
 gpu.set_state(host.initial_condition())
 if host.cfg.ntracers:
-    gpu.set_tracers(np.zeros((host.cfg.ntracers,) + host.shape("cell")))
+    from bench import bench_tracer
+    gpu.set_tracers(bench_tracer(host))
 gpu.prepare_run()
 gpu.run_steps(3)
 gpu.synchronize()
