@@ -184,13 +184,21 @@ struct BatchRef { const double *u, *v, *mfx, *mfy, *cflx, *cfly, *divx, *divy; }
 static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double* flx, double* fly, double dt) {
   const Geo gw = xg(h, 3, 4), gn = xg(h, 1, 1), g0 = h->g;
   static const bool old_path = getenv("GMCORE_OLD_HFLX") && getenv("GMCORE_OLD_HFLX")[0] == '1';   // round-1 kernels (A/B runs)
-  static const bool tile_path = getenv("GMCORE_FFSL_TILE") && getenv("GMCORE_FFSL_TILE")[0] == '1';   // 2-D tile variant (measured slower)
+  // x and y sweeps in one marching kernel or as two kernels.  Measured at 0.25 deg L32 (tools/kprof.py): inner call
+  // fused 0.741 ms, split 0.407 + 0.295 ms; outer call fused 0.466 ms, split 0.249 + 0.250 ms -> default: inner split,
+  // outer fused.  GMCORE_FFSL_FUSED = 1 / 0 forces both calls fused / split (A/B runs).
+  static const char* fenv = getenv("GMCORE_FFSL_FUSED");
+  static const bool fused_in = fenv && fenv[0] == '1', fused_out = !(fenv && fenv[0] == '0');
   if (!old_path) {
-    // inner advective half step: fluxes stay on chip, the block writes qx / qy (and the pole-adjacent y fluxes)
+    // inner advective half step: the fluxes stay on chip, the kernels write qx / qy (and the pole-adjacent y fluxes)
     const Geo g01 = xg(h, 0, 1);
     FfslArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qx, h->qy, B.divx, B.divy, h->qmfy, dt, gw.jb, gw.je, gn.jb, gn.je, g01.jb, g01.je};
-    if (tile_path) LAUNCH_LIM(h, k_ffsl_in, ffsl_grid(gw, gw.nlev), dim3(32, FT_Y), 0, gw, h->M, in);
-    else { const int rj = ffsl_strip_rows(gw), w = ffsl_block_width(gw.nlon); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj, w), w, 0, gw, h->M, in, rj); }
+    const int w = ffsl_block_width(gw.nlon);
+    if (fused_in) { const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj, w), w, 0, gw, h->M, in, rj); }
+    else {
+      LAUNCH_LIM2(h, k_ffsl_x, true, ffsl_x_grid(gw, gw.nlev, w), dim3(w, FX_ROWS), 0, gw, h->M, in);
+      const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_y, true, ffsl_y_grid(gw, gw.nlev, rj), 128, 0, gw, h->M, in, rj);
+    }
     if (g0.has_south || g0.has_north) {
       run_pole_sum(h, h->qmfy, h->pole_work, nullptr, 0);
       FfslQArgs qa{q, h->qmfx, h->qmfy, B.divx, B.divy, h->pole_work, h->qx, h->qy, dt, g01.jb, g01.je};
@@ -201,8 +209,11 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
       }
     }
     FfslArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, nullptr, nullptr, nullptr, 0.0, g0.jb, g01.je, gn.jb, gn.je, 0, 0};
-    if (tile_path) LAUNCH_LIM(h, k_ffsl_out, ffsl_grid(gn, gn.nlev), dim3(32, FT_Y), 0, gn, h->M, out);
-    else { const int rj = ffsl_strip_rows(gn), w = ffsl_block_width(gn.nlon); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj, w), w, 0, gn, h->M, out, rj); }
+    if (fused_out) { const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj, w), w, 0, gn, h->M, out, rj); }
+    else {
+      LAUNCH_LIM2(h, k_ffsl_x, false, ffsl_x_grid(gn, gn.nlev, w), dim3(w, FX_ROWS), 0, gn, h->M, out);
+      const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_y, false, ffsl_y_grid(gn, gn.nlev, rj), 128, 0, gn, h->M, out, rj);
+    }
     return;
   }
   HflxArgs in{B.u, B.v, q, q, B.cflx, B.cfly, h->qmfx, h->qmfy, gw.jb, gw.je, gn.jb, gn.je};

@@ -1,35 +1,28 @@
-// FFSL horizontal sweeps with block-shared limited slopes (round 2).
+// FFSL horizontal sweeps with shared limited slopes (round 2).
 //
 // hflx_ppm_cell (ffsl_mod.F90:778-881) builds the PPM coefficients of EVERY cell once (three mono-limited slopes
 // per cell and direction, :813-826) and then lets each edge pick the coefficients of its upwind cell.  The round-1
-// kernel (k_hflx, kernels_hydro.cuh) re-formed those coefficients per EDGE from a 5-point window, i.e. three limited
-// slopes per edge and direction -- every cell's slope was evaluated three times by three neighbouring threads, and the
-// kernel was bound by FP64 / issue slots (432 instructions per point, FP64 pipe 64 %), not by bytes.  Here a block owns
-// a tile of FT_X x FT_Y cells:
-//   phase 1  one limited slope per cell and direction (x: of mx along the row, y: of my along the column), stored in
-//            shared memory with the apron the tile's edges need (2 cells west / 2 east, 2 rows south / 2 north);
-//   phase 2  each edge selects its upwind cell (west / east, south / north neighbour; |cfl| < 1), reads that cell's
-//            three slopes from shared memory and its three values through L1, and evaluates the PPM edge values and
-//            the flux integral ONCE (ffsl_mod.F90:1147-1173, 831-851).  Lanes with |cflx| >= 1 (polar rows) take the
-//            round-1 gather path (own 5-point stencil + whole-cell segment sum, :831-848);
-//   phase 3  (inner call of ffsl_calc_tracer_hflx_cell only, :354-372) the fluxes stay in shared memory and the block
-//            forms the half-step fields qx, qy directly: the inner fluxes are never written to HBM and the separate
-//            k_ffsl_q pass (7 array passes) is gone.  Only the pole rows -- whose qy needs a zonal mean of the
-//            pole-adjacent y fluxes (:375-406) -- are finished by k_ffsl_q on those two rows.
-// Arithmetic is operation-for-operation the round-1 one (same slope, edge-value and integral expressions), so the
-// results are bit-identical to k_hflx + k_ffsl_q.
-//   algorithmic passes: inner 7 reads (u, v, q, cflx, cfly, divx, divy) + 2 writes (qx, qy) = 9;
-//                       outer 6 reads (mfx, mfy, qy, qx, cflx, cfly) + 2 writes = 8      
+// kernel (k_hflx, kernels_hydro.cuh) re-formed those coefficients per EDGE from a 5-point window -- three limited
+// slopes per edge and direction, every cell's slope evaluated three times by three neighbouring threads -- and was
+// bound by FP64 / issue slots (432 instructions per point, FP64 pipe 64 %), not by bytes.  Here every cell's slope is
+// formed ONCE and shared, and the two directions are separate kernels, because they share nothing but the inner
+// call's tracer field (x: wind u, cflx, divx; y: wind v, cfly, divy; the outer call sweeps qy in x and qx in y):
+//   k_ffsl_y   marches over a strip of rows with the y window of its column in REGISTERS (5 values, 4 slopes, rolled
+//              by one row per iteration: one new load and one new slope per row); no shared memory, no barrier;
+//   k_ffsl_x   one block per row segment: the row is staged in shared memory with 3 apron cells either side, each
+//              thread forms the slope of its own cell, each edge reads the 3 slopes / values of its upwind cell.
+// The inner call of ffsl_calc_tracer_hflx_cell (:354-372) writes the half-step fields qx, qy directly: the inner
+// fluxes never go to HBM and the separate k_ffsl_q pass is gone (only the two pole rows, whose qy needs a zonal mean
+// of the pole-adjacent y fluxes, :375-406, are finished by k_ffsl_q).  Lanes with |cflx| >= 1 (polar rows) take the
+// round-1 gather path (own 5-point stencil + whole-cell segment sum, :831-848).
+// Arithmetic is operation-for-operation the round-1 one (same slope, edge-value and integral expressions): results
+// are bit-identical to k_hflx + k_ffsl_q.
+//   algorithmic passes per call: inner x 4+1 (u, q, cflx, divx -> qx), inner y 4+1 (v, q, cfly, divy -> qy),
+//                                outer x 3+1 (mfx, qy, cflx -> flux), outer y 3+1 (mfy, qx, cfly -> flux)   = 18
+//   (round 1: inner 5+2, k_ffsl_q 5+2, outer 6+2 = 22;  a fused x+y marching kernel, 9 + 8 = 17 passes, is kept below
+//   as k_ffsl_march_* for A/B runs: it needs ~125 registers for both windows and measured slower)
 #pragma once
 #include "kernels_hydro.cuh"
-
-#ifndef FT_X
-#define FT_X 128          // tile width in cells: FT_X / 32 points per thread, a warp's points 32 apart (coalesced)
-#endif
-#ifndef FT_Y
-#define FT_Y 8            // tile rows = warps per block
-#endif
-#define FT_Q (FT_X / 32)
 
 struct FfslArgs {
   const double *u, *v;          // advecting wind (inner) or mass flux (outer)
@@ -58,161 +51,6 @@ __device__ __forceinline__ void ppm_from_slopes(double fm1, double f, double fp1
   df = fr - fl;
 }
 
-// x flux through the east edge of cell (i, j); sx = this row's slopes, indexed by tile-local cell + 2
-template <bool EDGE, int LIM> __device__ __forceinline__ double ffsl_flux_x(const double* __restrict__ mxr, const double* __restrict__ sx,
-                                                                           int i, int lc, int n, double cx, double uu) {
-  if (cx == 0) return 0.0;
-  int ci = (int)cx;
-  if (ci >= n || ci <= -n) ci = 0;      // |cflx| > lon_halo_width: the guard word is already up (k_cfl); stay in the row
-  const double cf = cx - ci;
-  const bool pos = cx > 0;
-  if (ci == 0) {
-    const int o = pos ? 0 : 1;                           // upwind cell = i + o
-    const double f = __ldg(mxr + wrapE<EDGE>(i + o, n));
-    const double dfc = sx[lc + o + 2];
-    if (LIM >= 4) {
-      const double t = pos ? cf * (f + dfc * 0.5 * (1 - cf)) : cf * (f - dfc * 0.5 * (1 + cf));
-      return qdiv(uu * t, cx);
-    }
-    const double fm1 = __ldg(mxr + wrapE<EDGE>(i + o - 1, n)), fp1 = __ldg(mxr + wrapE<EDGE>(i + o + 1, n));
-    const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
-    double ml, dm, m6;
-    ppm_from_slopes(fm1, f, fp1, sx[lc + o + 1], dfc, sx[lc + o + 3], ml, dm, m6);
-    return qdiv((pos ? uu : -uu) * ppm_integral(0.0, ml, dm, m6, s1, s2), cx);
-  }
-  // |cflx| >= 1: gather around the lane's own upwind cell and add the whole-cell segment sum (ffsl_mod.F90:831-848)
-  const int iu = wrapi(pos ? i - ci : i - ci + 1, n);
-  const double x0 = __ldg(mxr + wrapi(iu - 2, n)), x1 = __ldg(mxr + wrapi(iu - 1, n)), x2 = __ldg(mxr + iu);
-  const double x3 = __ldg(mxr + wrapi(iu + 1, n)), x4 = __ldg(mxr + wrapi(iu + 2, n));
-  double sm = 0;
-  if (pos) { for (int l = i + 1 - ci; l <= i; ++l) sm += __ldg(mxr + wrapi(l, n)); }
-  else { for (int l = i + 1; l <= i - ci; ++l) sm += __ldg(mxr + wrapi(l, n)); }
-  if (LIM >= 4) return vl_flux<LIM>(x1, x2, x3, sm, cf, cx, uu);
-  const double s1 = pos ? 1 - cf : 0.0, s2 = pos ? 1.0 : -cf;
-  double ml, dm, m6;
-  ppm<LIM>(x0, x1, x2, x3, x4, ml, dm, m6);
-  return qdiv((pos ? uu : -uu) * ppm_integral(sm, ml, dm, m6, s1, s2), cx);
-}
-// y flux through the north edge of cell (i, j) (half row j); sy = this column's slopes, sy[r * FT_X] = row j0 - 2 + r
-template <int LIM> __device__ __forceinline__ double ffsl_flux_y(const double* __restrict__ my, const Geo& g, const double* __restrict__ sy,
-                                                                 int i, int j, int k, int lr, double cy, double vv, bool direct) {
-  const bool pos = cy > 0;
-  const int o = pos ? 0 : 1;                             // upwind cell = row j + o
-  if (LIM < 4 && cy == 0) return 0.0;
-  const double f = direct ? __ldg(my + gidx(g, i, j + o, k)) : ldF(my, g, i, j + o, k);
-  const double dfc = sy[(lr + o + 2) * FT_X];
-  if (LIM >= 4) return vv * (f + dfc * 0.5 * (copysign(1.0, cy) - cy));      // ffsl_mod.F90:605-611: no zero-CFL branch
-  const double fm1 = direct ? __ldg(my + gidx(g, i, j + o - 1, k)) : ldF(my, g, i, j + o - 1, k);
-  const double fp1 = direct ? __ldg(my + gidx(g, i, j + o + 1, k)) : ldF(my, g, i, j + o + 1, k);
-  const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
-  double ml, dm, m6;
-  ppm_from_slopes(fm1, f, fp1, sy[(lr + o + 1) * FT_X], dfc, sy[(lr + o + 3) * FT_X], ml, dm, m6);
-  return qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
-}
-
-template <bool EDGE, int LIM, bool INNER> __device__ __forceinline__ void ffsl_tile(const Geo& g, const DMesh& M, const FfslArgs& a,
-                                                                                  double* __restrict__ Sx, double* __restrict__ Sy,
-                                                                                  double* __restrict__ Fx, double* __restrict__ Fy) {
-  const int n = g.nlon, tx = threadIdx.x, ty = threadIdx.y, k = blockIdx.z;
-  const int x0 = blockIdx.x * FT_X, j0 = g.jb + blockIdx.y * FT_Y;
-  const int j = j0 + ty;
-  const bool rowok = j <= g.je;
-  const bool dox = rowok && j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;     // warp-uniform
-  const bool doy = rowok && j <= g.nhalf && j >= a.jy0 && j <= a.jy1;
-  // rows j0-3 .. j0+FT_Y+2 are read by the y sweep: away from the poles they sit at fixed strides from one address
-  const bool direct = j0 - 3 >= 1 && j0 + FT_Y + 2 <= g.nlat;                     // block-uniform
-  // ---- phase 1: one limited slope per cell and direction ---------------------------------------------
-  if (dox) {
-    const double* __restrict__ mxr = a.mx + gidx(g, 0, j, k);
-    double* __restrict__ sx = Sx + ty * (FT_X + 4);
-#pragma unroll
-    for (int q = 0; q < FT_Q; ++q) {
-      const int lc = tx + 32 * q, c = x0 + lc;
-      if (c <= n + 1) sx[lc + 2] = cell_slope<LIM>(__ldg(mxr + wrapE<EDGE>(c - 1, n)), __ldg(mxr + wrapE<EDGE>(c, n)), __ldg(mxr + wrapE<EDGE>(c + 1, n)));
-    }
-    if (tx < 4) {                                        // apron cells x0-2, x0-1, x0+FT_X, x0+FT_X+1
-      const int lc = tx < 2 ? tx - 2 : FT_X + tx - 2, c = x0 + lc;
-      if (c <= n + 1) sx[lc + 2] = cell_slope<LIM>(__ldg(mxr + wrapi(c - 1, n)), __ldg(mxr + wrapi(c, n)), __ldg(mxr + wrapi(c + 1, n)));
-    }
-  }
-  {
-    // slopes in y of rows j0-2 .. j0+FT_Y+1; row r is needed when it is within one row below / two rows above a
-    // y-flux row (the upwind cell of half row jy is jy or jy+1 and its PPM needs the slopes of its two neighbours)
-    for (int rr = ty; rr < FT_Y + 4; rr += FT_Y) {
-      const int r = j0 - 2 + rr;
-      if (r < a.jy0 - 1 || r > a.jy1 + 2 || r > g.je + 2) continue;                // warp-uniform
-      double* __restrict__ sy = Sy + rr * FT_X;
-#pragma unroll
-      for (int q = 0; q < FT_Q; ++q) {
-        const int lc = tx + 32 * q, i = x0 + lc;
-        if (i >= n) continue;
-        double fm1, f, fp1;
-        if (direct) { const double* __restrict__ p = a.my + gidx(g, i, r, k); fm1 = __ldg(p - n); f = __ldg(p); fp1 = __ldg(p + n); }
-        else { fm1 = ldF(a.my, g, i, r - 1, k); f = ldF(a.my, g, i, r, k); fp1 = ldF(a.my, g, i, r + 1, k); }
-        sy[lc] = cell_slope<LIM>(fm1, f, fp1);
-      }
-    }
-  }
-  __syncthreads();
-  // ---- phase 2: fluxes ----------------------------------------------------------------------------------
-  const double* __restrict__ mxr = a.mx + gidx(g, 0, rowok ? j : g.je, k);
-  const double* __restrict__ sx = Sx + ty * (FT_X + 4);
-  const int rb = gidx(g, 0, rowok ? j : g.je, k);
-#pragma unroll
-  for (int q = 0; q < FT_Q; ++q) {
-    const int lc = tx + 32 * q, i = x0 + lc;
-    if (i >= n) continue;
-    const int c = rb + i;
-    double fx = 0, fy = 0;
-    if (dox) fx = ffsl_flux_x<EDGE, LIM>(mxr, sx, i, lc, n, __ldg(a.cflx + c), __ldg(a.u + c));
-    if (doy) fy = ffsl_flux_y<LIM>(a.my, g, Sy + lc, i, j, k, ty, __ldg(a.cfly + c), __ldg(a.v + c), direct);
-    if (!INNER) {
-      if (dox) a.ox[c] = fx;
-      if (doy) a.oy[c] = fy;
-    } else {
-      Fx[ty * (FT_X + 1) + lc + 1] = fx;
-      Fy[(ty + 1) * FT_X + lc] = fy;
-      if (doy && (j == 1 || j == g.nhalf)) a.qmfy[c] = fy;      // pole-adjacent half rows: zonal means of the pole rows
-    }
-  }
-  if (!INNER) return;
-  // west apron edge x0-1 of every row, south apron half row j0-1 (one extra flux per row / per column)
-  if (tx == 0 && dox) {
-    const int i = wrapi(x0 - 1, n), c = rb + i;
-    Fx[ty * (FT_X + 1)] = ffsl_flux_x<true, LIM>(mxr, sx, i, -1, n, __ldg(a.cflx + c), __ldg(a.u + c));
-  }
-  if (ty == 0) {
-    const int js = j0 - 1;
-    const bool doys = js >= 1 && js <= g.nhalf && js >= a.jy0 && js <= a.jy1;
-#pragma unroll
-    for (int q = 0; q < FT_Q; ++q) {
-      const int lc = tx + 32 * q, i = x0 + lc;
-      if (i >= n) continue;
-      double fy = 0;
-      if (doys) { const int c = gidx(g, i, js, k); fy = ffsl_flux_y<LIM>(a.my, g, Sy + lc, i, js, k, -1, __ldg(a.cfly + c), __ldg(a.v + c), direct); }
-      Fy[lc] = fy;
-    }
-  }
-  __syncthreads();
-  // ---- phase 3: half-step fields of the inner advective step (ffsl_mod.F90:354-372) ------------------------
-  if (!dox) return;                                       // pole rows are finished by k_ffsl_q after the zonal means
-  const RowCoef* __restrict__ R = M.rows + (j + 1);
-  const double rac = R->r_area_cell, lel = R->le_lon, lea = R->le_lat, leas = R[-1].le_lat;
-  const bool doq = j >= a.jq0 && j <= a.jq1;
-#pragma unroll
-  for (int q = 0; q < FT_Q; ++q) {
-    const int lc = tx + 32 * q, i = x0 + lc;
-    if (i >= n) continue;
-    const int c = rb + i;
-    const double qv = __ldg(a.mx + c);
-    const double fx0 = Fx[ty * (FT_X + 1) + lc + 1], fxm = Fx[ty * (FT_X + 1) + lc];
-    a.ox[c] = qv - 0.5 * ((fx0 - fxm) * lel * rac - __ldg(a.divx + c) * qv) * a.dt;
-    if (doq) {
-      const double fy0 = Fy[(ty + 1) * FT_X + lc], fys = Fy[ty * FT_X + lc];
-      a.oy[c] = qv - 0.5 * ((fy0 * lea - fys * leas) * rac - __ldg(a.divy + c) * qv) * a.dt;
-    }
-  }
-}
 
 // ---- row-marching variant -------------------------------------------------------------------------------
 // A block owns blockDim.x columns of one level and marches over a strip of rows.  The y sweep lives entirely in
@@ -400,17 +238,125 @@ static inline int ffsl_block_width(int nlon) {
 }
 static inline dim3 ffsl_march_grid(const Geo& g, int nk, int rj, int w) { return dim3((g.nlon + w - 1) / w, (g.je - g.jb + 1 + rj - 1) / rj, nk); }
 
-#ifndef FFSL_MINB
-#define FFSL_MINB 3
+// ---- y sweep: register marching, no shared memory ----------------------------------------------------------
+#ifndef FY_MINB
+#define FY_MINB 8          // 64 registers: measured 0.301 / 0.253 ms (inner / outer) against 0.330 / 0.289 at 6 blocks, 80 registers
 #endif
-template <int LIM> __global__ void __launch_bounds__(32 * FT_Y, FFSL_MINB) k_ffsl_out(Geo g, DMesh M, FfslArgs a) {
-  __shared__ double Sx[FT_Y * (FT_X + 4)], Sy[(FT_Y + 4) * FT_X];
-  if (blockIdx.x == 0 || (int)(blockIdx.x + 1) * FT_X + 3 > g.nlon) ffsl_tile<true, LIM, false>(g, M, a, Sx, Sy, nullptr, nullptr);
-  else ffsl_tile<false, LIM, false>(g, M, a, Sx, Sy, nullptr, nullptr);
+template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_y_body(const Geo& g, const DMesh& M, const FfslArgs& a, int rj) {
+  const int n = g.nlon, i = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.z;
+  if (i >= n) return;
+  const int rs = g.jb + blockIdx.y * rj;
+  if (rs > g.je) return;
+  const int re = rs + rj - 1 > g.je ? g.je : rs + rj - 1;
+  const int r0 = INNER ? rs - 1 : rs;       // INNER: qy of the strip's first row needs the y flux below it
+  const int flo = max(a.jy0, 1), fhi = min(a.jy1, g.nhalf);       // half rows of the y flux
+  const int ylo = a.jy0 - 2, yhi = a.jy1 + 3;                     // rows the y windows may read (band mode)
+  const int qlo = max(max(a.jq0, 2), rs), qhi = min(a.jq1, g.nlat - 1);   // INNER: rows of qy (never the pole rows)
+  const bool direct = r0 - 2 >= 1 && re + 3 <= g.nlat && r0 - 2 >= ylo && re + 3 <= yhi;   // plain strided windows
+  const double* __restrict__ pmy = a.my; const double* __restrict__ pcy = a.cfly; const double* __restrict__ pv = a.v;
+  auto ldy = [&](int r) -> double {         // generic window load (strips touching a pole or the band's y range)
+    if (r < ylo || r > yhi) return 0.0;
+    return ldF(pmy, g, i, r, k);
+  };
+  int c = gidx(g, i, r0, k);                // element index of (i, r, k); advances by n per row
+  double fm1, f0, fp1, fp2, fp3, sm1, s0, sp1;
+  {
+    double fm2;
+    if (direct) { const double* __restrict__ p = pmy + c; fm2 = __ldg(p - 2 * n); fm1 = __ldg(p - n); f0 = __ldg(p); fp1 = __ldg(p + n); fp2 = __ldg(p + 2 * n); fp3 = __ldg(p + 3 * n); }
+    else { fm2 = ldy(r0 - 2); fm1 = ldy(r0 - 1); f0 = ldy(r0); fp1 = ldy(r0 + 1); fp2 = ldy(r0 + 2); fp3 = ldy(r0 + 3); }
+    sm1 = cell_slope<LIM>(fm2, fm1, f0); s0 = cell_slope<LIM>(fm1, f0, fp1); sp1 = cell_slope<LIM>(f0, fp1, fp2);
+  }
+  // the operands of a row are loaded one iteration ahead; addresses are clamped to the strip, so no load is predicated
+  double cy = __ldg(pcy + c), vv = __ldg(pv + c), dvy = INNER ? __ldg(a.divy + c) : 0.0;
+  double fy_prev = 0;
+  // INNER: row coefficients le_lat(r), le_lat(r-1), 1 / area_cell(r), also one row ahead
+  const RowCoef* __restrict__ Rw = M.rows + (r0 + 1);
+  double lea = INNER ? Rw->le_lat : 0.0, leas = INNER ? Rw[-1].le_lat : 0.0, rac = INNER ? Rw->r_area_cell : 0.0;
+  for (int r = r0; r <= re; ++r, c += n, ++Rw) {
+    const int cn = r < re ? c + n : c;
+    const double ncy = __ldg(pcy + cn), nvv = __ldg(pv + cn), ndvy = INNER ? __ldg(a.divy + cn) : 0.0;
+    const double nlea = INNER ? Rw[1].le_lat : 0.0, nrac = INNER ? Rw[1].r_area_cell : 0.0;
+    double fp4;
+    if (direct) fp4 = __ldg(pmy + (r < re ? c + 4 * n : c + 3 * n));          // the last iteration re-reads row re+3 (unused)
+    else fp4 = ldy(r + 4);
+    const double sp2 = cell_slope<LIM>(fp1, fp2, fp3);
+    double fy = 0;
+    if (r >= flo && r <= fhi) {
+      const bool pos = cy > 0;
+      const double f = pos ? f0 : fp1, dfc = pos ? s0 : sp1;
+      if (LIM >= 4) fy = vv * (f + dfc * 0.5 * (copysign(1.0, cy) - cy));       // ffsl_mod.F90:605-611
+      else if (cy != 0) {
+        const double fa = pos ? fm1 : f0, fb = pos ? fp1 : fp2, dfl = pos ? sm1 : s0, dfr = pos ? sp1 : sp2;
+        const double s1 = pos ? 1 - cy : 0.0, s2 = pos ? 1.0 : -cy;
+        double ml, dm, m6;
+        ppm_from_slopes(fa, f, fb, dfl, dfc, dfr, ml, dm, m6);
+        fy = qdiv((pos ? vv : -vv) * ppm_integral(0.0, ml, dm, m6, s1, s2), cy);
+      }
+      if (!INNER) a.oy[c] = fy;
+      else if (r == 1 || r == g.nhalf) a.qmfy[c] = fy;              // pole-adjacent half rows: zonal means of the pole rows
+    }
+    if (INNER && r >= qlo && r <= qhi)                              // ffsl_mod.F90:363-367
+      a.oy[c] = f0 - 0.5 * ((fy * lea - fy_prev * leas) * rac - dvy * f0) * a.dt;
+    fy_prev = fy;
+    fm1 = f0; f0 = fp1; fp1 = fp2; fp2 = fp3; fp3 = fp4;
+    sm1 = s0; s0 = sp1; sp1 = sp2;
+    cy = ncy; vv = nvv; dvy = ndvy;
+    if (INNER) { leas = lea; lea = nlea; rac = nrac; }
+  }
 }
-template <int LIM> __global__ void __launch_bounds__(32 * FT_Y, FFSL_MINB) k_ffsl_in(Geo g, DMesh M, FfslArgs a) {
-  __shared__ double Sx[FT_Y * (FT_X + 4)], Sy[(FT_Y + 4) * FT_X], Fx[FT_Y * (FT_X + 1)], Fy[(FT_Y + 1) * FT_X];
-  if (blockIdx.x == 0 || (int)(blockIdx.x + 1) * FT_X + 3 > g.nlon) ffsl_tile<true, LIM, true>(g, M, a, Sx, Sy, Fx, Fy);
-  else ffsl_tile<false, LIM, true>(g, M, a, Sx, Sy, Fx, Fy);
+
+// ---- x sweep: one row segment per (block row), shared slopes --------------------------------------------------
+#ifndef FX_ROWS
+#define FX_ROWS 1          // rows per block (blockDim = (W, FX_ROWS)): independent rows, common barriers (measured: 1 best)
+#endif
+#ifndef FX_MINB
+#define FX_MINB 4
+#endif
+template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_x_body(const Geo& g, const DMesh& M, const FfslArgs& a) {
+  __shared__ double xr[FX_ROWS][FM_WMAX + 6];     // x-swept field of the row, cells x0-3 .. x0+W+2
+  __shared__ double sxr[FX_ROWS][FM_WMAX + 4];    // its limited slopes, cells x0-2 .. x0+W+1
+  __shared__ double fxr[INNER ? FX_ROWS : 1][INNER ? FM_WMAX + 1 : 1];    // INNER: x fluxes of the edges x0-1 .. x0+W-1
+  const int n = g.nlon, W = blockDim.x, tx = threadIdx.x, ty = threadIdx.y, x0 = blockIdx.x * W, i = x0 + tx, k = blockIdx.z;
+  const int j = g.jb + blockIdx.y * FX_ROWS + ty;
+  const bool act = i < n;
+  const int ic = act ? i : (i <= n + 2 ? i - n : n - 1);            // idle lanes: wrapped cells n..n+2, then any valid column
+  const bool dox = j <= g.je && j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1;      // warp-uniform (a warp = part of one row)
+  const int jc = j <= g.je ? j : g.je;                                // rows past the band: clamped loads, no stores
+  const int c = gidx(g, ic, jc, k);
+  const int alc = tx < 3 ? tx - 3 : W + tx - 3;                     // apron cell of threads 0..5
+  const bool hasap = tx < 6 && x0 + alc <= n + 2;
+  // ---- one memory phase ---------------------------------------------------------------------------------------
+  const double qv = __ldg(a.mx + c), cx = __ldg(a.cflx + c), uu = __ldg(a.u + c);
+  const double xa = hasap ? __ldg(a.mx + c + (wrapi(x0 + alc, n) - ic)) : 0.0;
+  double dvx = 0, cxw = 0, uuw = 0;
+  const int dcw = wrapi(x0 - 1, n) - ic;
+  double lel = 0, rac = 0;
+  if (INNER) {
+    dvx = __ldg(a.divx + c); if (tx == 0) { cxw = __ldg(a.cflx + c + dcw); uuw = __ldg(a.u + c + dcw); }
+    const RowCoef* __restrict__ R = M.rows + (jc + 1); lel = R->le_lon; rac = R->r_area_cell;
+  }
+  xr[ty][tx + 3] = qv;
+  if (hasap) xr[ty][alc + 3] = xa;
+  __syncthreads();
+  sxr[ty][tx + 2] = cell_slope<LIM>(xr[ty][tx + 2], qv, xr[ty][tx + 4]);
+  if (tx < 4) { const int lc = tx < 2 ? tx - 2 : W + tx - 2; sxr[ty][lc + 2] = cell_slope<LIM>(xr[ty][lc + 2], xr[ty][lc + 3], xr[ty][lc + 4]); }
+  __syncthreads();
+  const double* __restrict__ mxr = a.mx + (c - ic);
+  double fx = 0;
+  if (dox) fx = ffsl_flux_x_smem<LIM>(xr[ty], sxr[ty], mxr, tx, ic, n, cx, uu);
+  if (!INNER) { if (dox && act) a.ox[c] = fx; return; }
+  fxr[ty][tx + 1] = fx;
+  __syncthreads();
+  if (dox && act) {                                                  // ffsl_mod.F90:358-362
+    // the flux through the edge west of the block is needed by thread 0 alone: it forms it AFTER the barrier, so that
+    // only its own warp, not the whole block, waits for the extra flux evaluation
+    const double fxm = tx == 0 ? ffsl_flux_x_smem<LIM>(xr[ty], sxr[ty], mxr, -1, ic + dcw, n, cxw, uuw) : fxr[ty][tx];
+    a.ox[c] = qv - 0.5 * ((fx - fxm) * lel * rac - dvx * qv) * a.dt;
+  }
 }
-static inline dim3 ffsl_grid(const Geo& g, int nk) { return dim3((g.nlon + FT_X - 1) / FT_X, (g.je - g.jb + 1 + FT_Y - 1) / FT_Y, nk); }
+template <int LIM> __global__ void __launch_bounds__(128, FY_MINB) k_ffsl_y_in(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_y_body<LIM, true>(g, M, a, rj); }
+template <int LIM> __global__ void __launch_bounds__(128, FY_MINB) k_ffsl_y_out(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_y_body<LIM, false>(g, M, a, rj); }
+template <int LIM> __global__ void __launch_bounds__(FM_WMAX * FX_ROWS, FX_MINB) k_ffsl_x_in(Geo g, DMesh M, FfslArgs a) { ffsl_x_body<LIM, true>(g, M, a); }
+template <int LIM> __global__ void __launch_bounds__(FM_WMAX * FX_ROWS, FX_MINB) k_ffsl_x_out(Geo g, DMesh M, FfslArgs a) { ffsl_x_body<LIM, false>(g, M, a); }
+static inline dim3 ffsl_x_grid(const Geo& g, int nk, int w) { return dim3((g.nlon + w - 1) / w, (g.je - g.jb + 1 + FX_ROWS - 1) / FX_ROWS, nk); }
+static inline dim3 ffsl_y_grid(const Geo& g, int nk, int rj) { return dim3((g.nlon + 127) / 128, (g.je - g.jb + 1 + rj - 1) / rj, nk); }
