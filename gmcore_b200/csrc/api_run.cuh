@@ -29,9 +29,16 @@ static void diag_to_abi(const double* s, double* out) {
 // time_integrate (gmcore_mod.F90:577-591) for every band driven by this handle
 static int time_integrate_impl(gmc_handle* h, int old_, int nw, double dt, int time_step) {
   if (time_integrator(h, old_, nw, dt)) return 1;
-  if (!h->cfg.baroclinic) { if (h->cfg.use_smag_damp) run_smag_damp(h, h->st[nw], dt); return 0; }
+  if (!h->cfg.baroclinic) {      // damp_run (damp_mod.F90:49-63): div damping, then Smagorinsky
+    if (h->cfg.use_div_damp) run_div_damp(h, h->st[nw]);
+    if (h->cfg.use_smag_damp) run_smag_damp(h, h->st[nw], dt);
+    return 0;
+  }
   bool adv = false;
-  for_bands(h, [&](gmc_handle* b) { adv = hydro_post_compute(b, nw, dt, time_step); });
+  for_bands(h, [&](gmc_handle* b) { hydro_post_compute_1(b, nw, dt); });
+  if (h->cfg.nranks > 1 && h->cfg.use_smag_damp &&      // strain rates read u, v one row beyond the band
+      halo_exchange(h, [&](gmc_handle* b) { HaloSet s = halo_set(); halo_add(s, b->st[nw].u, b->g.nlev); halo_add(s, b->st[nw].v, b->g.nlev); return s; })) return 1;
+  for_bands(h, [&](gmc_handle* b) { adv = hydro_post_compute_2(b, nw, dt, time_step); });
   if (h->cfg.nranks > 1) {
     // one packed exchange per advected batch (the alert clocks are the same on every band), pt with the first
     bool hs = h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ;
@@ -193,6 +200,14 @@ int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double*
   CUDA_CHECK(cudaMemcpyAsync(S.mfx_lon, S.u_f, n3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   CUDA_CHECK(cudaMemcpyAsync(S.mfy_lat, S.v_f, n3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   return 0;
+}
+// 3-D advection cases (tests/adv/dcmip12_test_mod.F90:75-161): the prescribed vertical mass flux we_lev on the half
+// levels (interior-plus-halo Fortran storage), after gmc_adv_prescribe has set m = m_lev = 1
+int gmc_adv_prescribe_we(gmc_handle* h, int itime, const double* we_lev) {
+  if (!h->cfg.baroclinic || h->batches.empty() || h->cfg.nranks > 1) {
+    snprintf(h->err, sizeof(h->err), "the advection-only driver needs the hydrostatic core with a tracer batch on one band"); return 1; }
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  return xfer(h, h->st[itime].we_lev, const_cast<double*>(we_lev), 2, 0);
 }
 int gmc_adv_step(gmc_handle* h, int itime, int time_step) {
   if (check_ready(h)) return 1;

@@ -40,9 +40,6 @@ int gmc_create(const gmc_config* cfg, gmc_handle** out) {
   if (cfg->nlon % 2 != 0) { snprintf(g_create_err, sizeof(g_create_err), "num_lon must be even"); delete h; return 3; }
   if (cfg->coriolis_scheme != 1 && cfg->coriolis_scheme != 2) { snprintf(g_create_err, sizeof(g_create_err), "coriolis_scheme=%d is not a GMCORE scheme (1 or 2)", cfg->coriolis_scheme); delete h; return 3; }
   if (cfg->use_div_damp && cfg->div_damp_order != 2 && cfg->div_damp_order != 4) { snprintf(g_create_err, sizeof(g_create_err), "Unsupported div_damp_order %d!", cfg->div_damp_order); delete h; return 3; }
-  if (cfg->use_div_damp && cfg->div_damp_order == 4 && cfg->nranks > 1) { snprintf(g_create_err, sizeof(g_create_err), "div_damp_order=4 is built for a single band only"); delete h; return 3; }
-  if (cfg->use_div_damp && !cfg->baroclinic) { snprintf(g_create_err, sizeof(g_create_err), "use_div_damp is not built for the shallow-water core"); delete h; return 3; }
-  if (cfg->use_smag_damp && cfg->nranks > 1) { snprintf(g_create_err, sizeof(g_create_err), "use_smag_damp is built for a single band only (u_lon / v_lat halo rows are not exchanged)"); delete h; return 3; }
   if (cfg->nranks > 1 && !cfg->baroclinic) { snprintf(g_create_err, sizeof(g_create_err), "latitude bands (nranks>1) are built for the hydrostatic core only"); delete h; return 3; }
   if (cfg->nranks > 1 && cfg->lat_iend - cfg->lat_ibeg + 1 < 6) { snprintf(g_create_err, sizeof(g_create_err), "a latitude band needs at least 6 rows"); delete h; return 3; }
   if ((cfg->rank == 0) != (cfg->lat_ibeg == 1) || (cfg->rank == cfg->nranks - 1) != (cfg->lat_iend == cfg->nlat)) {
@@ -174,6 +171,7 @@ int gmc_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
     }
     if (!rc) rc = hydro_set_mesh(h, mv);
   }
+  if (!rc) rc = damp_set_mesh(h, mv);
 #undef UPF
 #undef UPH
   M.hx = c.hx;

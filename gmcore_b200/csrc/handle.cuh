@@ -87,6 +87,7 @@ struct gmc_handle {
   double *cflx = 0, *cfly = 0, *cflz = 0, *divx = 0, *divy = 0;   // adv_batch_mass
   double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
   double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)
+  double *div2 = 0;                   // Laplacian of div (div_damp_order = 4)
   double *lon_damp_wgt = 0;
   double *pole_work = 0;
   double *smag_t = 0, *smag_s = 0, *smag_du = 0, *smag_dv = 0;   // smag_damp work arrays (use_smag_damp)

@@ -55,6 +55,36 @@ static int hydro_alloc(gmc_handle* h) {
 
 // damp_init pieces that are pure functions of the mesh: div_damp coefficients
 // (div_damp_mod.F90:27-87) and the lon_damp latitude profile (lon_damp_mod.F90:43-68).
+// div_damp_init (div_damp_mod.F90:27-87), both cores: the level profile applies to the baroclinic core only (:46-51)
+static int damp_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
+  const gmc_config& c = h->cfg;
+  if (!c.use_div_damp) return 0;
+  const int nlat = c.nlat, nhalf = c.nlat - 1, nlev = c.nlev, hy = c.hy;
+  auto F = [&](const double* v, int j) { return v[j - (1 - hy)]; };
+  std::vector<double> cl((size_t)nlat * nlev, 0.0), ca((size_t)nhalf * nlev, 0.0);
+  for (int k = 1; k <= nlev; ++k) {
+    double fac = 1.0;
+    if (c.div_damp_order == 2 && c.baroclinic) {
+      const double hyam = 0.5 * (mv->hyai[k - 1] + mv->hyai[k]), hybm = 0.5 * (mv->hybi[k - 1] + mv->hybi[k]);
+      const double ph = hyam * (c.hybrid_p0 - c.ptop) + hybm * (c.p0 - c.ptop) + c.ptop;
+      fac = std::fmax(1.0, 8 * (1 + std::tanh(std::log(c.ptop / ph))));
+    }
+    for (int j = 2; j <= nlat - 1; ++j) {
+      const double le = F(mv->le_lon, j), de = F(mv->de_lon, j);
+      cl[(size_t)(k - 1) * nlat + (j - 1)] = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * le * de : c.div_damp_coef4 * (le * le) * (de * de);
+    }
+    for (int j = 1; j <= nhalf; ++j) {
+      const double le = F(mv->le_lat, j), de = F(mv->de_lat, j);
+      ca[(size_t)(k - 1) * nhalf + (j - 1)] = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * le * de : c.div_damp_coef4 * (le * le) * (de * de);
+    }
+  }
+  const double* p = nullptr;
+  int rc = dev_upload(h, &p, cl.data(), cl.size()); h->c_lon = const_cast<double*>(p);
+  if (!rc) { rc = dev_upload(h, &p, ca.data(), ca.size()); h->c_lat = const_cast<double*>(p); }
+  if (!rc && c.div_damp_order == 4 && !h->div2) rc = dev_alloc(h, &h->div2, (size_t)h->g.plane * h->g.nlev);
+  return rc;
+}
+
 static int hydro_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
   const gmc_config& c = h->cfg;
   {  // column kernels stage whole columns in dynamic shared memory: opt in above 48 KB (deep level counts)
@@ -83,28 +113,10 @@ static int hydro_set_mesh(gmc_handle* h, const gmc_mesh_vectors* mv) {
     if (cudaStreamSynchronize(h->stream) != cudaSuccess) { snprintf(h->err, sizeof(h->err), "k_lev_tab failed"); return 1; }
     h->M.nconst = nconst;
   }
-  const int nlat = c.nlat, nhalf = c.nlat - 1, nlev = c.nlev, hy = c.hy;
+  const int nlat = c.nlat, nlev = c.nlev, hy = c.hy;
   auto F = [&](const double* v, int j) { return v[j - (1 - hy)]; };
-  std::vector<double> cl((size_t)nlat * nlev, 0.0), ca((size_t)nhalf * nlev, 0.0);
-  for (int k = 1; k <= nlev; ++k) {
-    double fac = 1.0;
-    if (c.div_damp_order == 2) {
-      const double hyam = 0.5 * (mv->hyai[k - 1] + mv->hyai[k]), hybm = 0.5 * (mv->hybi[k - 1] + mv->hybi[k]);
-      const double ph = hyam * (c.hybrid_p0 - c.ptop) + hybm * (c.p0 - c.ptop) + c.ptop;
-      fac = std::fmax(1.0, 8 * (1 + std::tanh(std::log(c.ptop / ph))));
-    }
-    for (int j = 2; j <= nlat - 1; ++j) {
-      const double le = F(mv->le_lon, j), de = F(mv->de_lon, j);
-      cl[(size_t)(k - 1) * nlat + (j - 1)] = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * le * de : c.div_damp_coef4 * (le * le) * (de * de);
-    }
-    for (int j = 1; j <= nhalf; ++j) {
-      const double le = F(mv->le_lat, j), de = F(mv->de_lat, j);
-      ca[(size_t)(k - 1) * nhalf + (j - 1)] = c.div_damp_order == 2 ? c.div_damp_coef2 * fac * le * de : c.div_damp_coef4 * (le * le) * (de * de);
-    }
-  }
   const double* p = nullptr;
-  int rc = dev_upload(h, &p, cl.data(), cl.size()); h->c_lon = const_cast<double*>(p);
-  if (!rc) { rc = dev_upload(h, &p, ca.data(), ca.size()); h->c_lat = const_cast<double*>(p); }
+  int rc = 0;
   // lon_damp weights; full_lat_deg(j) = full_lat(j) * deg (mesh_mod.F90:212)
   const double pi = std::atan(1.0) * 4.0, deg = 180.0 / pi;
   std::vector<double> w(nlat + 1, 0.0);
@@ -420,38 +432,48 @@ static HaloSet tracer_halo_set(gmc_handle* b, int m, int which) {
   return s;
 }
 
-// smag_damp_run (damp_mod.F90:60-62) on state(new)%u_lon, v_lat
+// smag_damp_run (damp_mod.F90:60-62) on state(new)%u_lon, v_lat.  In band mode the caller has exchanged the halo
+// rows of u, v first (steps: strain on rows jb-1 .. je+1, tendencies and update on the owned rows).
 static void run_smag_damp(gmc_handle* h, DState& S, double dt) {
-  const Geo& g = h->g;
+  const Geo& g = h->g; const Geo g11 = xg(h, 1, 1);
   SmagArgs a{S.u, S.v, h->smag_t, h->smag_s, h->smag_du, h->smag_dv, h->cfg.smag_damp_coef, dt};
-  LAUNCH(h, k_smag_strain, gridg(g, g.nlev), 128, 0, g, h->M, a);
+  LAUNCH(h, k_smag_strain, gridg(g11, g.nlev), 128, 0, g11, h->M, a);
   LAUNCH(h, k_smag_tend, gridg(g, g.nlev), 128, 0, g, h->M, a);
   LAUNCH(h, k_smag_apply, gridg(g, g.nlev), 128, 0, g, a, S.u, S.v);
 }
 
-// time_integrate after the time integrator (gmcore_mod.F90:586-590): forcing, damping, tracers
-static bool hydro_post_compute(gmc_handle* h, int nw, double dt, int time_step) {
+// div_damp_run (div_damp_mod.F90:89-139) on state S, both cores.  div is recomputed from the filtered winds
+// (calc_div); order 4 needs div one row beyond the rows of div2 (bands: u_f, v_f halo rows are there, H = 4).
+static void run_div_damp(gmc_handle* h, DState& S) {
+  const Geo& g = h->g;
+  const bool o4 = h->cfg.div_damp_order == 4;
+  const Geo gd = o4 ? xg(h, 1, 2) : xg(h, 0, 1);
+  DivArgs d{S.u_f, S.v_f, S.div};
+  LAUNCH(h, k_div, gridg(gd, g.nlev), 128, 0, gd, h->M, d);
+  run_pole_sum(h, S.v_f, nullptr, S.div, 1);
+  const double* dsrc = S.div; double sgn = 1.0;
+  if (o4) {     // u -= c d(div2)/dx with div2 = lap(div) (div_damp_mod.F90:120-134); pole rows of div2 stay 0
+    const Geo g01 = xg(h, 0, 1);
+    Div2Args d2{S.div, h->div2};
+    LAUNCH(h, k_div2, gridg(g01, g.nlev), 128, 0, g01, h->M, d2);
+    dsrc = h->div2; sgn = -1.0;
+  }
+  DivDampArgs dd{dsrc, h->c_lon, h->c_lat, S.u, S.v, sgn};
+  LAUNCH(h, k_div_damp, gridg(g, g.nlev), 128, 0, g, h->M, dd);
+}
+
+// time_integrate after the time integrator (gmcore_mod.F90:586-590): forcing and divergence damping (part 1), then --
+// after the u, v halo exchange that Smagorinsky damping needs across bands -- Smagorinsky damping and tracers (part 2)
+static void hydro_post_compute_1(gmc_handle* h, int nw, double dt) {
   const Geo& g = h->g; DState& S = h->st[nw];
   if (h->cfg.test_forcing == GMC_FORCING_HELD_SUAREZ) {
     HsArgs a{S.u, S.v, S.pt, S.t, S.phs_f, dt, make_vc(h)};
     LAUNCH(h, k_held_suarez, gridg(g, g.nlev), 128, 0, g, h->M, a);
   }
-  if (h->cfg.use_div_damp) {
-    const Geo g01 = xg(h, 0, 1);
-    DivArgs d{S.u_f, S.v_f, S.div};
-    LAUNCH(h, k_div, gridg(g01, g.nlev), 128, 0, g01, h->M, d);
-    run_pole_sum(h, S.v_f, nullptr, S.div, 1);
-    const double* dsrc = S.div; double sgn = 1.0;
-    if (h->cfg.div_damp_order == 4) {     // u -= c d(div2)/dx with div2 = lap(div) (div_damp_mod.F90:120-134)
-      Div2Args d2{S.div, h->qx};          // qx is free here; its pole rows hold FFSL data, so clear them first
-      cudaMemsetAsync(h->qx, 0, (size_t)g.plane * g.nlev * sizeof(double), h->stream);
-      LAUNCH(h, k_div2, gridg(g, g.nlev), 128, 0, g, h->M, d2);
-      dsrc = h->qx; sgn = -1.0;
-    }
-    DivDampArgs dd{dsrc, h->c_lon, h->c_lat, S.u, S.v, sgn};
-    LAUNCH(h, k_div_damp, gridg(g, g.nlev), 128, 0, g, h->M, dd);
-  }
-  if (h->cfg.use_smag_damp) run_smag_damp(h, S, dt);
+  if (h->cfg.use_div_damp) run_div_damp(h, S);
+}
+static bool hydro_post_compute_2(gmc_handle* h, int nw, double dt, int time_step) {
+  if (h->cfg.use_smag_damp) run_smag_damp(h, h->st[nw], dt);
   return hydro_adv_run(h, nw, time_step);
 }
 

@@ -18,7 +18,7 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_step",
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_prescribe_we", "gmc_adv_step",
                "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host",
                "gmc_add_tracer_batch", "gmc_set_batch_tracers", "gmc_get_batch_tracers"]
 
@@ -67,6 +67,7 @@ def load_library():
     lib.gmc_pin_host.argtypes = [V, C.c_void_p, C.c_size_t]
     lib.gmc_unpin_host.argtypes = [V, C.c_void_p]
     lib.gmc_adv_prescribe.argtypes = [V, C.c_int, P, P]
+    lib.gmc_adv_prescribe_we.argtypes = [V, C.c_int, P]
     lib.gmc_adv_step.argtypes = [V, C.c_int, C.c_int]
     lib.gmc_stream.restype = C.c_void_p
     lib.gmc_stream.argtypes = [V]
@@ -135,8 +136,11 @@ class GmcoreGPU:
         return q
 
     # advection-only driver (gmcore_adv_driver.F90:84-88): set_uv(new) -> adv_run(new) -> time_advance
-    def adv_prescribe(self, u_f, v_f, itime=None):
-        self._chk(self.lib.gmc_adv_prescribe(self.h, self.new.value if itime is None else itime, abi.dptr(u_f), abi.dptr(v_f)))
+    def adv_prescribe(self, u_f, v_f, itime=None, we_lev=None):
+        it = self.new.value if itime is None else itime
+        self._chk(self.lib.gmc_adv_prescribe(self.h, it, abi.dptr(u_f), abi.dptr(v_f)))
+        if we_lev is not None:
+            self._chk(self.lib.gmc_adv_prescribe_we(self.h, it, abi.dptr(we_lev)))
 
     def adv_step(self):
         self._chk(self.lib.gmc_adv_step(self.h, self.new.value, self.time_step.value))

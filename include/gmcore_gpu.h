@@ -154,6 +154,7 @@ int gmc_nccl_init(gmc_handle* h, const char id[128]);
  * tests/adv/*_test_mod.F90 (state(itime)%m = 1, u_f / v_f given, mfx_lon = u_f, mfy_lat = v_f); gmc_adv_step is
  * adv_run(itime) (adv_mod.F90:152-312).  time_step as in gmc_time_integrate. */
 int gmc_adv_prescribe(gmc_handle* h, int itime, const double* u_f, const double* v_f);
+int gmc_adv_prescribe_we(gmc_handle* h, int itime, const double* we_lev /* (lon, lat, half lev) halo'd: state%we_lev of dcmip12_test_set_uv */);
 int gmc_adv_step(gmc_handle* h, int itime, int time_step);
 
 /* time_init (time_mod.F90:61-98): clear the step / tracer-batch sample counters before a fresh upload. */

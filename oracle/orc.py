@@ -36,6 +36,7 @@ def _load(fast):
     lib.orc_set_batch_tracers.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_get_batch_tracers.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_adv_prescribe.argtypes = [C.c_void_p, C.c_int, P, P]
+    lib.orc_adv_prescribe_we.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_adv_step.argtypes = [C.c_void_p]
     lib.orc_prepare_run.argtypes = [C.c_void_p]
     lib.orc_run_steps.argtypes = [C.c_void_p, C.c_int, P]
@@ -92,8 +93,11 @@ class Oracle:
         return q
 
     # advection-only driver (gmcore_adv_driver.F90:84-88)
-    def adv_prescribe(self, u_f, v_f, itime=None):
-        self.lib.orc_adv_prescribe(self.h, self.new_index if itime is None else itime, _dp(u_f), _dp(v_f))
+    def adv_prescribe(self, u_f, v_f, itime=None, we_lev=None):
+        it = self.new_index if itime is None else itime
+        self.lib.orc_adv_prescribe(self.h, it, _dp(u_f), _dp(v_f))
+        if we_lev is not None:
+            self.lib.orc_adv_prescribe_we(self.h, it, _dp(we_lev))
 
     def adv_step(self):
         self._check(self.lib.orc_adv_step(self.h))

@@ -113,6 +113,12 @@ int orc_adv_prescribe(void* h, int itime, const double* u_f, const double* v_f) 
   if (m->b.cfg.baroclinic) { std::fill(s.we_lev.d.begin(), s.we_lev.d.end(), 0.0); std::fill(s.m_lev.d.begin(), s.m_lev.d.end(), 1.0); }
   return 0;
 }
+// dcmip12_test_set_uv (tests/adv/dcmip12_test_mod.F90:146-158): prescribed we_lev
+int orc_adv_prescribe_we(void* h, int itime, const double* we_lev) {
+  Model* m = (Model*)h; State& s = m->b.state[itime];
+  std::memcpy(s.we_lev.d.data(), we_lev, s.we_lev.d.size() * sizeof(double));
+  return 0;
+}
 int orc_adv_step(void* h) {
   Model* m = (Model*)h;
   m->adv_run(m->new_idx);

@@ -45,6 +45,29 @@ def test_bands_match_single_band(gpu_required, case, nlon, nlat, nlev, dt, nband
     grp.close()
 
 
+@pytest.mark.parametrize("opts", [dict(use_smag_damp=1), dict(div_damp_order=4), dict(use_smag_damp=1, div_damp_order=4)])
+def test_bands_with_smagorinsky_and_order4_damping(gpu_required, opts):
+    """Row a20 across bands: Smagorinsky damping (u, v halo rows exchanged before the strain rates,
+    smag_damp_mod.F90:45-205) and 4th-order divergence damping (div one row beyond div2, operators_mod.F90:414-428)
+    give the single-band answer, which test_hydro_gpu.py holds against the oracle."""
+    from gmcore_b200.model import GmcoreBandGroup
+    host, ic, orc, one = make_pair(96, 49, 8, 600.0, "baroclinic_wave", **opts)
+    q = smooth_tracer(host, host.cfg.ntracers)
+    one.set_tracers(q)
+    grp = GmcoreBandGroup(host, 4)
+    grp.set_state(ic); grp.set_tracers(q)
+    one.prepare_run(); grp.prepare_run()
+    for step in range(3):
+        d1 = one.run_steps(1); dn = grp.run_steps(1)
+        for name, loc in PROGNOSTIC_HYDRO + [("u_f", "lon"), ("v_f", "lat")]:
+            a, b = grp.field(name), one.field(name)
+            a = host.interior(a.reshape(a.shape[-2:]) if loc == "2d" else a, loc)
+            b = host.interior(b.reshape(b.shape[-2:]) if loc == "2d" else b, loc)
+            assert rel_l2(a, b) <= 1e-13, (step, name, rel_l2(a, b))
+        np.testing.assert_allclose(dn[:, [0, 1, 7]], d1[:, [0, 1, 7]], rtol=1e-13)
+    grp.close(); one.close()
+
+
 def _nccl_worker(rank, world, port, overlap, out):
     import os
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
