@@ -46,7 +46,8 @@ CPU_SAMPLE = {"bw_1440x720x32": "bw_360x180x32"}
 # Algorithmic 3-D r8 array passes per launch of each kernel (SURVEY.md §8d / DESIGN.md):
 # reads + writes of full 3-D fields; 2-D fields and coefficient vectors ignored.
 KERNEL_PASSES = {
-    "k_fwd1": 3 + 7, "k_pv_edge": 5 + 2, "k_tend": 5 + 3, "k_uv_update": 5 + 2, "k_filter_rows": None,
+    "k_fwd1": 3 + 7, "k_pv_edge": 5 + 2, "k_tend": 5 + 3, "k_uv_update": 5 + 2,
+    "k_filter_rows": 7.0 / 3,      # mean of the three shallow-water launches: gz -> gz_f, gz, m (1+3); u -> u_f (1+1); v -> v_f (1+1)
     "k_diag_partial": 8,
 }
 # hydrostatic core (k_tend / k_uv_update read more there); k_hflx: 5 reads on the inner call

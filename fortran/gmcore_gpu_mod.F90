@@ -118,6 +118,10 @@ module gmcore_gpu_mod
     integer(c_int) function gmc_get_field(h, itime, name, buf) bind(c, name='gmc_get_field')
       import; type(c_ptr), value :: h, buf; integer(c_int), value :: itime; character(kind=c_char), intent(in) :: name(*)
     end function
+    integer(c_int) function gmc_interp_pressure_level(h, itime, var, po, logp, fill, y2d) bind(c, name='gmc_interp_pressure_level')
+      import; type(c_ptr), value :: h, y2d; integer(c_int), value :: itime, logp; real(c_double), value :: po, fill
+      character(kind=c_char), intent(in) :: var(*)
+    end function
     integer(c_int) function gmc_nccl_unique_id(id) bind(c, name='gmc_nccl_unique_id')
       import; character(kind=c_char), intent(out) :: id(128)
     end function
@@ -348,12 +352,33 @@ contains
       ! h0 diagnostics (history_mod.F90:519-597)
       call check(gmc_get_field(handle, int(itime, c_int), 't' // c_null_char, c_loc(block%state(itime)%t)), 'gmc_get_field t')
       call check(gmc_get_field(handle, int(itime, c_int), 'div' // c_null_char, c_loc(block%state(itime)%div)), 'gmc_get_field div')
+      ! z and ph of the h0 set are not stored on the device: the library re-forms them on demand (gz = g z)
+      call check(gmc_get_field(handle, int(itime, c_int), 'gz' // c_null_char, c_loc(block%state(itime)%gz)), 'gmc_get_field gz')
+      call check(gmc_get_field(handle, int(itime, c_int), 'ph' // c_null_char, c_loc(block%state(itime)%ph)), 'gmc_get_field ph')
+      call check(gmc_get_field(handle, int(itime, c_int), 'gz_lev' // c_null_char, c_loc(block%state(itime)%gz_lev)), 'gmc_get_field gz_lev')
+      ! vor: history writes state%vor, the copy left by the last forward pass (one stage old, SURVEY T7); the device
+      ! keeps pv of that pass instead, from which the host can form vor = pv * m_vtx - half_f if it writes 'vor'
+      call check(gmc_get_field(handle, int(itime, c_int), 'pv' // c_null_char, c_loc(block%state(itime)%pv)), 'gmc_get_field pv')
     else
       call check(gmc_download_state(handle, int(itime, c_int), c_loc(block%state(itime)%u_lon), c_loc(block%state(itime)%v_lat), &
                  c_loc(block%state(itime)%gz), c_null_ptr), 'gmc_download_state')
       call check(gmc_get_field(handle, int(itime, c_int), 'pv' // c_null_char, c_loc(block%state(itime)%pv)), 'gmc_get_field pv')
     end if
   end subroutine gmcore_gpu_download
+
+  ! diag_state_run, pressure_levels branch (utils/diag_state_mod.F90:241-258): one variable ('u', 'v', 'pt', 't', 'z')
+  ! on one pressure surface into the caller's 2-D buffer (diag_state%buf), interpolated on the device
+  subroutine gmcore_gpu_interp_pressure_level(itime, var, po, buf, logp)
+    integer, intent(in) :: itime
+    character(*), intent(in) :: var
+    real(r8), intent(in) :: po
+    real(r8), intent(inout), target :: buf(:,:)
+    logical, intent(in), optional :: logp
+    integer(c_int) lp
+    lp = 0; if (present(logp)) lp = merge(1, 0, logp)
+    call check(gmc_interp_pressure_level(handle, int(itime, c_int), trim(var) // c_null_char, real(po, c_double), lp, &
+               real(buf(lbound(buf,1),lbound(buf,2)), c_double), c_loc(buf)), 'gmc_interp_pressure_level')
+  end subroutine gmcore_gpu_interp_pressure_level
 
   subroutine gmcore_gpu_final()
     if (c_associated(handle)) call gmc_destroy(handle)

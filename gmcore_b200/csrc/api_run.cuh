@@ -53,6 +53,31 @@ static int time_integrate_impl(gmc_handle* h, int old_, int nw, double dt, int t
   for_bands(h, [&](gmc_handle* b) { hydro_adv_finish(b, nw); });
   return 0;
 }
+// Shallow-water time_integrate through a captured graph (no host-side state changes inside a shallow-water step:
+// fixed pointers, fixed dt).  Falls back to plain launches while profiling, for non-standard buffer pairings, or when
+// capture is unavailable.
+static int swm_time_integrate(gmc_handle* h, int old_, int nw, double dt, int time_step) {
+  static const bool off = getenv("GMCORE_NO_GRAPH") && getenv("GMCORE_NO_GRAPH")[0] == '1';
+  const bool pair = (old_ == 1 && nw == 2) || (old_ == 2 && nw == 1);
+  if (off || h->prof.on || !pair || dt != h->cfg.dt_dyn) return time_integrate_impl(h, old_, nw, dt, time_step);
+  const int gi = old_ - 1;
+  if (!h->swm_graph[gi]) {
+    cudaGraph_t graph = nullptr;
+    const long long l0 = h->launches;
+    if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return time_integrate_impl(h, old_, nw, dt, time_step); }
+    const int rc = time_integrate_impl(h, old_, nw, dt, time_step);
+    const cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+    h->swm_graph_launches[gi] = h->launches - l0; h->launches = l0;
+    if (rc || e != cudaSuccess || !graph || cudaGraphInstantiate(&h->swm_graph[gi], graph, 0) != cudaSuccess) {
+      cudaGetLastError(); if (graph) cudaGraphDestroy(graph); h->swm_graph[gi] = nullptr;
+      snprintf(h->err, sizeof(h->err), "shallow-water step: graph capture failed"); return 1;
+    }
+    cudaGraphDestroy(graph);
+  }
+  CUDA_CHECK(cudaGraphLaunch(h->swm_graph[gi], h->stream));
+  h->launches += h->swm_graph_launches[gi];
+  return 0;
+}
 // time_advance bookkeeping of the tracer alerts (time_mod.F90:128-159), every band, every batch
 static void alert_advance(gmc_handle* h, int time_step) {
   for_bands(h, [&](gmc_handle* b) {
@@ -91,7 +116,7 @@ int gmc_prepare_run(gmc_handle* h, int old_) {
 int gmc_time_integrate(gmc_handle* h, int old_, int nw, double dt, int time_step) {
   if (check_ready(h)) return 1;
   alert_advance(h, time_step - 1);     // the host's time_advance ran since the previous call
-  if (time_integrate_impl(h, old_, nw, dt, time_step)) return 1;
+  if (h->cfg.baroclinic ? time_integrate_impl(h, old_, nw, dt, time_step) : swm_time_integrate(h, old_, nw, dt, time_step)) return 1;
   CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -130,11 +155,15 @@ static int reduce_diag(gmc_handle* h, std::vector<double*>& dbufs, int nsets, do
 // grow-only per-band device buffer for the per-step sums of gmc_run_steps (no cudaMalloc inside a timed loop)
 static double* diag_steps_buf(gmc_handle* b, int nsteps) {
   if (b->diag_steps_cap < nsteps) {
-    if (b->diag_steps) cudaFree(b->diag_steps);
-    b->diag_steps = nullptr; b->diag_steps_cap = 0;
     const int cap = nsteps < 64 ? 64 : nsteps;
-    if (cudaMalloc(&b->diag_steps, (size_t)cap * 8 * sizeof(double)) != cudaSuccess) return nullptr;
-    b->diag_steps_cap = cap;
+    double* nb = nullptr;
+    if (cudaMalloc(&nb, (size_t)cap * 8 * sizeof(double)) != cudaSuccess) return nullptr;
+    if (b->diag_steps) {      // keep the sets already queued by gmc_diagnose_enqueue
+      cudaMemcpyAsync(nb, b->diag_steps, (size_t)b->diag_steps_cap * 8 * sizeof(double), cudaMemcpyDeviceToDevice, b->stream);
+      cudaStreamSynchronize(b->stream);
+      cudaFree(b->diag_steps);
+    }
+    b->diag_steps = nb; b->diag_steps_cap = cap;
   }
   return b->diag_steps;
 }
@@ -146,9 +175,40 @@ int gmc_diagnose(gmc_handle* h, int itime, double out[8]) {
   return reduce_diag(h, dbufs, 1, out);
 }
 
+// Deferred diagnostics: the reference computes `diagnose` every step but only looks at the sums when the 'print'
+// alert rings (gmcore_mod.F90:140-142, log_print_diag).  gmc_diagnose_enqueue launches the sums of state(itime) into
+// the next slot of a device ring without touching the host; gmc_diagnose_collect reduces all queued sets over the
+// bands (one ncclAllReduce), copies them back in one transfer and checks the guard word.  Same numbers as
+// gmc_diagnose per step, without a host round trip and an all-reduce latency inside every time step.
+int gmc_diagnose_enqueue(gmc_handle* h, int itime) {
+  if (check_ready(h)) return 1;
+  int rc = 0;
+  const int slot = h->diag_queued;
+  for_bands(h, [&](gmc_handle* b) {
+    double* d = diag_steps_buf(b, slot + 1 > 64 ? 2 * (slot + 1) : 64);      // grow-only; existing sets are kept
+    if (!d) { rc = 1; return; }
+    launch_diag(b, itime, d + (size_t)slot * 8);
+  });
+  if (rc) { snprintf(h->err, sizeof(h->err), "cudaMalloc of the diagnostics ring failed"); return 1; }
+  h->diag_queued = slot + 1;
+  return 0;
+}
+int gmc_diagnose_collect(gmc_handle* h, double* out /* [max_sets][8] */, int max_sets, int* nsets) {
+  if (check_ready(h)) return 1;
+  const int n = h->diag_queued;
+  if (nsets) *nsets = n;
+  if (n == 0) return 0;
+  if (n > max_sets) { snprintf(h->err, sizeof(h->err), "gmc_diagnose_collect: %d sets queued, room for %d", n, max_sets); return 1; }
+  std::vector<double*> dbufs;
+  for_bands(h, [&](gmc_handle* b) { dbufs.push_back(b->diag_steps); });
+  h->diag_queued = 0;
+  return reduce_diag(h, dbufs, n, out);
+}
+
 int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int nsteps, double* diag) {
   if (check_ready(h)) return 1;
   if (nsteps <= 0) return 0;
+  if (h->diag_queued) { snprintf(h->err, sizeof(h->err), "gmc_run_steps: %d deferred diagnostics are queued, call gmc_diagnose_collect first", h->diag_queued); return 1; }
   std::vector<double*> dbufs;
   int rc = 0;
   // with diag == NULL one set is still taken after the last step: it carries the guard word back
@@ -159,7 +219,8 @@ int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int
     dbufs.push_back(d);
   });
   for (int s = 0; s < nsteps && !rc; ++s) {
-    rc = time_integrate_impl(h, *old_idx, *new_idx, h->cfg.dt_dyn, *time_step);
+    rc = h->cfg.baroclinic ? time_integrate_impl(h, *old_idx, *new_idx, h->cfg.dt_dyn, *time_step)
+                           : swm_time_integrate(h, *old_idx, *new_idx, h->cfg.dt_dyn, *time_step);
     alert_advance(h, *time_step);   // time_advance (time_mod.F90:128-159)
     int t = *old_idx; *old_idx = *new_idx; *new_idx = t;
     *time_step += 1;
@@ -218,6 +279,46 @@ int gmc_adv_step(gmc_handle* h, int itime, int time_step) {
   hydro_adv_finish(h, itime);
   CUDA_CHECK(cudaGetLastError());
   return hydro_check_flags(h);
+}
+// ---- pressure-level diagnostics (utils/diag_state_mod.F90:241-258 -> dynamics/interp_mod.F90:727-897) -------
+// One variable on one pressure surface, as the reference's interp_{cell,lon_edge,lat_edge,lev_edge}_to_pressure_level:
+// search the column from the surface up for the layer that brackets po, interpolate linearly in p (or log p).
+// u / v are first averaged to the cell centre (:795-796, :843-844).  Columns that do not reach po keep `fill`.
+struct PlevArgs { const double *x, *phs_f; double* y; double po, p0x, fill, rg; int var, logp; VC vc; };
+__global__ void __launch_bounds__(128) k_plev(Geo g, DMesh M, PlevArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
+  auto pfull = [&](int k1) { return 0.5 * (ph_lev_at(M, a.vc, k1, phs) + ph_lev_at(M, a.vc, k1 + 1, phs)); };
+  const bool half = a.var == 4;             // z lives on the half levels (gz_lev), bracketed by ph_lev
+  double y = a.fill;
+  for (int k = half ? g.nlev + 1 : g.nlev; k >= 2; --k) {
+    const double pm = half ? ph_lev_at(M, a.vc, k - 1, phs) : pfull(k - 1), pk = half ? ph_lev_at(M, a.vc, k, phs) : pfull(k);
+    if (pm <= a.po && a.po <= pk) {
+      const double dp1 = a.logp ? a.p0x - log(pm) : a.p0x - pm, dp2 = a.logp ? log(pk) - a.p0x : pk - a.p0x;
+      double x1, x2;
+      if (a.var == 0) {          // u_lon -> cell centre
+        x1 = 0.5 * (ldW(a.x, g, i - 1, j, k - 2) + ldW(a.x, g, i, j, k - 2)); x2 = 0.5 * (ldW(a.x, g, i - 1, j, k - 1) + ldW(a.x, g, i, j, k - 1));
+      } else if (a.var == 1) {   // v_lat -> cell centre (pole rows read the mirrored half row, fill_halo semantics)
+        x1 = 0.5 * (ldH(a.x, g, i, j - 1, k - 2) + ldH(a.x, g, i, j, k - 2)); x2 = 0.5 * (ldH(a.x, g, i, j - 1, k - 1) + ldH(a.x, g, i, j, k - 1));
+      } else { x1 = __ldg(a.x + gidx(g, i, j, k - 2)); x2 = __ldg(a.x + gidx(g, i, j, k - 1)); if (half) { x1 = x1 * a.rg; x2 = x2 * a.rg; } }
+      y = (dp2 * x1 + dp1 * x2) / (dp1 + dp2);
+      break;
+    }
+  }
+  a.y[gidx(g, i, j, 0)] = y;
+}
+int gmc_interp_pressure_level(gmc_handle* h, int itime, const char* var, double po, int logp, double fill, double* y2d) {
+  if (!h->cfg.baroclinic) { snprintf(h->err, sizeof(h->err), "pressure-level diagnostics need the hydrostatic core"); return 1; }
+  if (itime < 1 || itime > 3) { snprintf(h->err, sizeof(h->err), "bad time index %d", itime); return 1; }
+  DState& S = h->st[itime];
+  const std::string v(var);
+  PlevArgs a{nullptr, S.phs_f, h->dphs, po, logp ? std::log(po) : po, fill, 1.0 / h->cfg.g, 0, logp, make_vc(h)};
+  if (v == "u") { a.x = S.u; a.var = 0; } else if (v == "v") { a.x = S.v; a.var = 1; } else if (v == "pt") { a.x = S.pt; a.var = 2; }
+  else if (v == "t") { a.x = S.t; a.var = 3; } else if (v == "z") { a.x = S.gz_lev; a.var = 4; }
+  else { snprintf(h->err, sizeof(h->err), "unknown pressure-level variable %s (u, v, pt, t, z)", var); return 1; }
+  LAUNCH(h, k_plev, gridg(h->g, 1), 128, 0, h->g, h->M, a);
+  return xfer(h, h->dphs, y2d, 3, 1);
 }
 int gmc_set_tracers(gmc_handle* h, const double* q) { return gmc_set_batch_tracers(h, 0, q); }
 int gmc_get_tracers(gmc_handle* h, double* q) { return gmc_get_batch_tracers(h, 0, q); }

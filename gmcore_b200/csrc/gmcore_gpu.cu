@@ -96,6 +96,7 @@ void gmc_destroy(gmc_handle* h) {
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
   if (h->diag_steps) cudaFree(h->diag_steps);
+  for (int q = 0; q < 2; ++q) if (h->swm_graph[q]) cudaGraphExecDestroy(h->swm_graph[q]);
   if (h->nccl_comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->nccl_comm);
   if (h->group) {   // the group vector is shared: the last member to go frees it
     auto* grp = h->group;
@@ -270,6 +271,13 @@ int gmc_get_field(gmc_handle* h, int itime, const char* name, double* buf) {
   else if (n == "du") { p = h->du; kind = 0; }
   else if (n == "dv") { p = h->dv; kind = 1; }
   else if (n == "gzs") { p = h->gzs; kind = 3; }
+  else if (h->cfg.baroclinic && (n == "ph" || n == "gz")) {
+    // h0 variables that are never stored on the device (history_mod.F90:519-597): full-level pressure
+    // (calc_ph, operators_mod.F90:157-164) and geopotential (calc_gz_lev tail, :459-466) are re-formed on demand
+    FullLevArgs fa{h->st[itime].phs_f, h->st[itime].gz_lev, h->du, n == "ph" ? 0 : 1, make_vc(h)};
+    LAUNCH(h, k_full_lev, gridg(h->g, h->g.nlev), 128, 0, h->g, h->M, fa);
+    p = h->du; kind = 0;
+  }
   if (!p) { snprintf(h->err, sizeof(h->err), "unknown field %s", name); return 1; }
   return xfer(h, p, buf, kind, 1);
 }

@@ -88,6 +88,10 @@ struct gmc_handle {
   double *qx = 0, *qy = 0, *ptf_lon = 0, *ptf_lat = 0, *qmfx = 0, *qmfy = 0, *dpt = 0;
   double *c_lon = 0, *c_lat = 0;      // div_damp coefficients (j,k)
   double *div2 = 0;                   // Laplacian of div (div_damp_order = 4)
+  int diag_queued = 0;                // sets waiting in the diagnostics ring (gmc_diagnose_enqueue)
+  // shallow-water time step as a CUDA graph, one per (old, new) pairing: the ~20 kernels of a 0.5 degree step last
+  // 3-15 us each, shorter than a launch, so the step is replayed with one cudaGraphLaunch (GMCORE_NO_GRAPH=1: off)
+  cudaGraphExec_t swm_graph[2] = {nullptr, nullptr}; long long swm_graph_launches[2] = {0, 0};
   double *lon_damp_wgt = 0;
   double *pole_work = 0;
   double *smag_t = 0, *smag_s = 0, *smag_du = 0, *smag_dv = 0;   // smag_damp work arrays (use_smag_damp)

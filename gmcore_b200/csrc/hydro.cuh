@@ -139,6 +139,15 @@ static bool hydro_work_field(gmc_handle* h, const std::string& n, double** p, in
   return false;
 }
 
+// ph = (ph_lev(k) + ph_lev(k+1)) / 2 or gz = (gz_lev(k) + gz_lev(k+1)) / 2 for gmc_get_field
+struct FullLevArgs { const double *phs_f, *gz_lev; double* out; int what; VC vc; };
+__global__ void __launch_bounds__(128) k_full_lev(Geo g, DMesh M, FullLevArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = g.jb + blockIdx.y, k = blockIdx.z;
+  if (i >= g.nlon) return;
+  const int c = gidx(g, i, j, k);
+  if (a.what == 0) { const double phs = __ldg(a.phs_f + gidx(g, i, j, 0)); a.out[c] = 0.5 * (ph_lev_at(M, a.vc, k + 1, phs) + ph_lev_at(M, a.vc, k + 2, phs)); }
+  else a.out[c] = 0.5 * (__ldg(a.gz_lev + c) + __ldg(a.gz_lev + c + (int)g.plane));
+}
 __global__ void k_axpy2d(Geo g, const double* x, const double* d, double* y, double dt) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = g.jb + blockIdx.y;
   if (i >= g.nlon) return;

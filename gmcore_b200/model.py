@@ -18,7 +18,7 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_prescribe_we", "gmc_adv_step",
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_prescribe_we", "gmc_adv_step", "gmc_interp_pressure_level", "gmc_diagnose_enqueue", "gmc_diagnose_collect",
                "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host",
                "gmc_add_tracer_batch", "gmc_set_batch_tracers", "gmc_get_batch_tracers"]
 
@@ -68,6 +68,9 @@ def load_library():
     lib.gmc_unpin_host.argtypes = [V, C.c_void_p]
     lib.gmc_adv_prescribe.argtypes = [V, C.c_int, P, P]
     lib.gmc_adv_prescribe_we.argtypes = [V, C.c_int, P]
+    lib.gmc_diagnose_enqueue.argtypes = [V, C.c_int]
+    lib.gmc_diagnose_collect.argtypes = [V, P, C.c_int, C.POINTER(C.c_int)]
+    lib.gmc_interp_pressure_level.argtypes = [V, C.c_int, C.c_char_p, C.c_double, C.c_int, C.c_double, P]
     lib.gmc_adv_step.argtypes = [V, C.c_int, C.c_int]
     lib.gmc_stream.restype = C.c_void_p
     lib.gmc_stream.argtypes = [V]
@@ -83,7 +86,7 @@ FIELD_LOC = {
     "ph_lev": "cell+lev", "ph_exn_lev": "cell+lev", "gz_lev": "cell+lev", "we_lev": "cell+lev", "m_lev": "cell+lev",
     "du": "lon", "dv": "lat", "gzs": "2d", "cflx": "lon", "cfly": "lat", "cflz": "cell+lev", "divx": "cell",
     "divy": "cell", "qx": "cell", "qy": "cell", "ptf_lon": "lon", "ptf_lat": "lat", "dpt": "cell",
-    "wedudlev": "lon", "wedvdlev": "lat", "dphs": "2d",
+    "wedudlev": "lon", "wedvdlev": "lat", "dphs": "2d", "ph": "cell",
 }
 
 
@@ -172,6 +175,22 @@ class GmcoreGPU:
         out = np.zeros(8)
         self._chk(self.lib.gmc_diagnose(self.h, self.old.value if itime is None else itime, abi.dptr(out)))
         return out
+
+    def diagnose_enqueue(self, itime=None):
+        """diagnose of state(itime) into the device ring: no host round trip (gmc_diagnose_collect fetches them)."""
+        self._chk(self.lib.gmc_diagnose_enqueue(self.h, self.old.value if itime is None else itime))
+
+    def diagnose_collect(self, max_sets=4096):
+        out = np.zeros((max_sets, 8)); n = C.c_int(0)
+        self._chk(self.lib.gmc_diagnose_collect(self.h, abi.dptr(out), max_sets, C.byref(n)))
+        return out[:n.value].copy()
+
+    def interp_pressure_level(self, var, po, logp=False, fill=np.nan, itime=None):
+        """diag_state's pressure-level interpolation of one variable ("u", "v", "pt", "t", "z") -> halo'd 2-D array."""
+        y = np.zeros(self.host.shape("2d"))
+        self._chk(self.lib.gmc_interp_pressure_level(self.h, self.old.value if itime is None else itime, var.encode(),
+                                                     float(po), int(logp), float(fill), abi.dptr(y)))
+        return y
 
     def synchronize(self):
         self._chk(self.lib.gmc_synchronize(self.h))

@@ -133,12 +133,26 @@ int gmc_run_steps(gmc_handle* h, int* old_idx, int* new_idx, int* time_step, int
 
 /* diagnose (gmcore_mod.F90:213-341): out = tm, te, tav, tpe, te_ke, te_ie, te_pe, tpt */
 int gmc_diagnose(gmc_handle* h, int itime, double out[8]);
+/* The same sums without a host round trip per step: gmc_diagnose_enqueue computes the sums of state(itime) into a
+ * device ring (asynchronous, no all-reduce yet); gmc_diagnose_collect reduces every queued set over the bands,
+ * returns them oldest first in out[nsets][8] and reports a raised guard like gmc_diagnose.  For hosts that look at
+ * the sums only when the 'print' alert rings (gmcore_mod.F90:140-142). */
+int gmc_diagnose_enqueue(gmc_handle* h, int itime);
+int gmc_diagnose_collect(gmc_handle* h, double* out, int max_sets, int* nsets);
 
 /* Read back one named derived field of state(itime) for parity tests/history
  * (history_mod.F90 h0 variable set and the per-state work arrays).  buf uses the
  * halo'd host layout of that field's grid location.  Returns non-zero for an
  * unknown name. */
 int gmc_get_field(gmc_handle* h, int itime, const char* name, double* buf);
+
+/* Pressure-level diagnostics of the h1 / diag_state output (utils/diag_state_mod.F90:241-258): one variable of
+ * state(itime) -- "u", "v" (averaged to the cell centre), "pt", "t", "z" (gz_lev / g) -- interpolated to the pressure
+ * surface po, linearly in p or in log p, exactly as interp_*_to_pressure_level (dynamics/interp_mod.F90:727-897).
+ * y2d is a (lon, lat) array in the halo'd host layout; columns that do not reach po get `fill`.  z is bracketed
+ * with ph_lev (the reference passes the full-level pressure into the half-level dummy there -- an index slip that
+ * is not reproduced). */
+int gmc_interp_pressure_level(gmc_handle* h, int itime, const char* var, double po, int logp, double fill, double* y2d);
 
 /* Latitude bands (the 1-D latitude decomposition of process_mod.F90:93-139; halo exchange =
  * fill_halo S/N of parallel_mod.F90:501-527).  Each band is one handle created with its own

@@ -38,6 +38,7 @@ def _load(fast):
     lib.orc_adv_prescribe.argtypes = [C.c_void_p, C.c_int, P, P]
     lib.orc_adv_prescribe_we.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_adv_step.argtypes = [C.c_void_p]
+    lib.orc_interp_pressure_level.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_double, C.c_int, C.c_double, P]
     lib.orc_prepare_run.argtypes = [C.c_void_p]
     lib.orc_run_steps.argtypes = [C.c_void_p, C.c_int, P]
     lib.orc_diagnose.argtypes = [C.c_void_p, C.c_int, P]
@@ -101,6 +102,11 @@ class Oracle:
 
     def adv_step(self):
         self._check(self.lib.orc_adv_step(self.h))
+
+    def interp_pressure_level(self, var, po, logp=False, fill=np.nan, itime=None):
+        y = np.zeros(self.host.shape("2d"))
+        self.lib.orc_interp_pressure_level(self.h, self.old_index if itime is None else itime, var.encode(), float(po), int(logp), float(fill), _dp(y))
+        return y
 
     def prepare_run(self):
         self._check(self.lib.orc_prepare_run(self.h))

@@ -119,6 +119,34 @@ int orc_adv_prescribe_we(void* h, int itime, const double* we_lev) {
   std::memcpy(s.we_lev.d.data(), we_lev, s.we_lev.d.size() * sizeof(double));
   return 0;
 }
+// interp_{cell,lon_edge,lat_edge,lev_edge}_to_pressure_level (interp_mod.F90:727-897) as diag_state_run calls them
+// (utils/diag_state_mod.F90:241-258); z is bracketed with ph_lev (see include/gmcore_gpu.h)
+int orc_interp_pressure_level(void* h, int itime, const char* var, double po, int logp, double fill, double* y2d) {
+  Model* m = (Model*)h; State& s = m->b.state[itime]; const Mesh& mesh = m->b.mesh;
+  const std::string v(var);
+  A3 y; mesh.alloc2(y, true);
+  const double p0 = logp ? std::log(po) : po;
+  const bool half = v == "z";
+  const A3& p = half ? s.ph_lev : s.ph;
+  for (int j = 1; j <= mesh.nlat; ++j) for (int i = 1; i <= mesh.nlon; ++i) {
+    y(i, j) = fill;
+    for (int k = half ? mesh.nlev + 1 : mesh.nlev; k >= 2; --k)
+      if (p(i, j, k - 1) <= po && po <= p(i, j, k)) {
+        const double dp1 = logp ? p0 - std::log(p(i, j, k - 1)) : p0 - p(i, j, k - 1);
+        const double dp2 = logp ? std::log(p(i, j, k)) - p0 : p(i, j, k) - p0;
+        double x1, x2;
+        if (v == "u") { x1 = 0.5 * (s.u_lon(i - 1, j, k - 1) + s.u_lon(i, j, k - 1)); x2 = 0.5 * (s.u_lon(i - 1, j, k) + s.u_lon(i, j, k)); }
+        else if (v == "v") { x1 = 0.5 * (s.v_lat(i, j - 1, k - 1) + s.v_lat(i, j, k - 1)); x2 = 0.5 * (s.v_lat(i, j - 1, k) + s.v_lat(i, j, k)); }
+        else if (v == "pt") { x1 = s.pt(i, j, k - 1); x2 = s.pt(i, j, k); }
+        else if (v == "t") { x1 = s.t(i, j, k - 1); x2 = s.t(i, j, k); }
+        else { x1 = s.gz_lev(i, j, k - 1) * (1.0 / m->b.cfg.g); x2 = s.gz_lev(i, j, k) * (1.0 / m->b.cfg.g); }
+        y(i, j) = (dp2 * x1 + dp1 * x2) / (dp1 + dp2);
+        break;
+      }
+  }
+  std::memcpy(y2d, y.d.data(), y.d.size() * sizeof(double));
+  return 0;
+}
 int orc_adv_step(void* h) {
   Model* m = (Model*)h;
   m->adv_run(m->new_idx);
