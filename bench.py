@@ -63,8 +63,8 @@ L2_BYTES = 126e6
 
 def ncu_traffic(kernel, workload):
     """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture of this workload
-    (profiles/r01_ncu_traffic.json, written by tools/ncu_raw_summary.py --json), or None."""
-    p = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    (profiles/r02_ncu_traffic.json, written by tools/ncu_raw_summary.py --json), or None."""
+    p = os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")
     try:
         t = json.load(open(p))
         return t["kernels"][kernel]["dram_bytes_per_launch"] if t.get("workload") == workload else None

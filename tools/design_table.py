@@ -1,4 +1,4 @@
-"""DESIGN.md §3.1 table from a tools/kprof.py listing + profiles/r01_ncu_traffic.json.
+"""DESIGN.md §3.1 table from a tools/kprof.py listing + profiles/r02_ncu_traffic.json.
 usage: python tools/design_table.py kprof.txt [peak_gbs]"""
 import json, os, re, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -8,7 +8,7 @@ txt = open(sys.argv[1]).read()
 name = re.search(r"^(\S+) lib=", txt, re.M).group(1)
 wl = WORKLOADS[name]; n3 = wl["nlon"] * wl["nlat"] * wl["nlev"]
 peak = float(sys.argv[2]) if len(sys.argv) > 2 else measured_peak_gbs()[0]
-t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))["kernels"]
+t = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))["kernels"]
 print(f"| kernel | launches/step | ms/launch (CUDA events) | alg. passes | alg. GB/s | % of measured HBM peak ({peak:.0f} GB/s) | ncu DRAM GB/launch |")
 print("|---|---|---|---|---|---|---|")
 tot_ms = 0.0
