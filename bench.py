@@ -360,7 +360,15 @@ def _main(out):
         q0p = pinned_like(gpu2.slice_tracers(q0) if banded else q0)[0]
     # page-locked destination of the final download: the host model's own state arrays, allocated once
     outp = {k: (pinned_like(np.zeros_like(v))[0] if v is not None else None) for k, v in src.items()}
-    h2d = sum(v.nbytes for v in icp.values() if v is not None)
+    # bytes that cross PCIe: the library copies the interior of each halo'd host array (one strided copy per field)
+
+    def wire_bytes(a):
+        if a is None:
+            return 0
+        rows = a.shape[-2] - 2 * host.hy                      # owned rows of this array (full- or half-lat)
+        levs = 1 if a.ndim == 2 else (a.shape[0] - 4 if a.shape[0] == wl["nlev"] + 4 else a.shape[0])
+        return 8 * wl["nlon"] * rows * levs
+    h2d = sum(wire_bytes(v) for v in icp.values())
     # untimed warm-up of this handle (first-use costs: NCCL connection set-up, pinned-page registration)
     (gpu2.set_state_sliced if banded else gpu2.set_state)(icp)
     if q0 is not None:
@@ -371,7 +379,7 @@ def _main(out):
     t0 = time.perf_counter()
     (gpu2.set_state_sliced if banded else gpu2.set_state)(icp)
     if q0 is not None:
-        (gpu2.set_tracers_sliced if banded else gpu2.set_tracers)(q0p); h2d += q0p.nbytes
+        (gpu2.set_tracers_sliced if banded else gpu2.set_tracers)(q0p); h2d += sum(wire_bytes(x) for x in q0p)
     gpu2.prepare_run()
     for _ in range(K):
         gpu2.time_integrate()
@@ -379,7 +387,7 @@ def _main(out):
     st = gpu2.download_state(out=outp)
     gpu2.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0, world)
-    d2h = sum(v.nbytes for v in st.values() if v is not None)
+    d2h = sum(wire_bytes(v) for v in st.values())
     e2e = {"value": (1 if banded else world) * K * wl["dt"] / e2e_s, "unit": "simulated days/day",
            "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K + 64, "bytes_are": "per rank",
            "region": "upload_state(pinned)+prepare_run+K*(time_integrate+diagnose D2H)+download_state"}

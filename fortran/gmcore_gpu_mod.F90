@@ -252,9 +252,17 @@ contains
     end if
     call check(gmc_set_mesh(handle, mv), 'gmc_set_mesh')
 
-    ! the three filters built by block%init_stage_1 (block_mod.F90:62-64).  NOTE: the library expects
-    ! GLOBAL row vectors; a banded host must gather ngrid/wgt rows first (filters are per-latitude data).
-    call set_filter(0, block%big_filter); call set_filter(1, block%small_filter1); call set_filter(2, block%small_filter2)
+    ! The library takes GLOBAL per-latitude filter rows (a band recomputes derived fields on rows of its neighbours),
+    ! while block%big_filter etc. (block_mod.F90:62-64) hold the block's own rows.  The filters are pure functions of
+    ! the mesh and dt_dyn (filter_types_mod.F90:49-147), so every rank builds them once more on global_mesh -- which
+    ! exists on every rank (mesh_mod.F90:130) and already carries the final lon_halo_width.
+    block
+      type(filter_type) gf
+      call gf%init(global_mesh, 'big_filter'   ); call set_filter(0, gf)
+      call gf%init(global_mesh, 'small_filter1'); call set_filter(1, gf)
+      call gf%init(global_mesh, 'small_filter2'); call set_filter(2, gf)
+      call gf%clear()
+    end block
     call check(gmc_set_static(handle, c_loc(block%static%gzs)), 'gmc_set_static')
 
     if (proc%np > 1) then

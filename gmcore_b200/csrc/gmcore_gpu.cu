@@ -204,7 +204,33 @@ int gmc_set_filters(gmc_handle* h, int which, const int* ngrid_lon, const double
 }
 
 // kind: 0 full-lat full-lev, 1 half-lat full-lev, 2 full-lat half-lev, 3 2-D full-lat
+// Host (halo'd Fortran storage of one field) <-> device (dense rows, no longitude halo): ONE strided 3-D copy of the
+// interior, straight between the caller's array and the field -- no staging image, no pack kernel, and the halo
+// columns / rows / ghost levels (a quarter of the bytes at 0.25 deg: 246 of 1686 columns, 4 of 36 levels) never cross
+// PCIe.  Host halo cells are left untouched on download (the reference refills them with fill_halo before use).
+// kind: 0 full-lat 3-D, 1 half-lat 3-D, 2 full-lat on half levels, 3 2-D.   GMCORE_XFER_STAGED=1: round-1 path.
+static int xfer_staged(gmc_handle* h, double* dev, double* host, int kind, int dir);
 static int xfer(gmc_handle* h, double* dev, double* host, int kind, int dir) {
+  static const bool staged = getenv("GMCORE_XFER_STAGED") && getenv("GMCORE_XFER_STAGED")[0] == '1';
+  if (staged) return xfer_staged(h, dev, host, kind, dir);
+  const gmc_config& c = h->cfg; const Geo& g = h->g;
+  const int nrows = kind == 1 ? g.hje - g.hjb + 1 : g.je - g.jb + 1;
+  const int nx = c.nlon + 2 * c.hx, ny = nrows + 2 * c.hy;
+  const int klev0 = (kind == 0 || kind == 1) ? 2 : 0, nk = kind == 3 ? 1 : (kind == 2 ? c.nlev + 1 : c.nlev);
+  if (nrows <= 0) return 0;
+  cudaMemcpy3DParms p = {};
+  const cudaPitchedPtr hp = make_cudaPitchedPtr(host, (size_t)nx * sizeof(double), (size_t)nx, (size_t)ny);
+  const cudaPitchedPtr dp = make_cudaPitchedPtr(dev, (size_t)g.nlon * sizeof(double), (size_t)g.nlon, (size_t)g.NY);
+  const cudaPos hpos = make_cudaPos((size_t)c.hx * sizeof(double), (size_t)c.hy, (size_t)klev0);
+  const cudaPos dpos = make_cudaPos(0, (size_t)(g.jb - g.jlo), 0);
+  p.extent = make_cudaExtent((size_t)g.nlon * sizeof(double), (size_t)nrows, (size_t)nk);
+  if (dir == 0) { p.srcPtr = hp; p.srcPos = hpos; p.dstPtr = dp; p.dstPos = dpos; p.kind = cudaMemcpyHostToDevice; }
+  else { p.srcPtr = dp; p.srcPos = dpos; p.dstPtr = hp; p.dstPos = hpos; p.kind = cudaMemcpyDeviceToHost; }
+  CUDA_CHECK(cudaMemcpy3DAsync(&p, h->stream));
+  if (dir != 0) CUDA_CHECK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+static int xfer_staged(gmc_handle* h, double* dev, double* host, int kind, int dir) {
   const gmc_config& c = h->cfg; const Geo& g = h->g;
   PackArgs a;
   a.dev = dev; a.img = h->stage_img; a.hx = c.hx; a.hy = c.hy; a.nx = c.nlon + 2 * c.hx;

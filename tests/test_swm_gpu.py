@@ -81,17 +81,20 @@ def test_upload_download_roundtrip(gpu_required):
     assert np.array_equal(host.interior(st["u_lon"], "lon"), host.interior(ic["u_lon"], "lon"))
     assert np.array_equal(host.interior(st["v_lat"], "lat"), host.interior(ic["v_lat"], "lat"))
     assert np.array_equal(host.interior(st["pt_or_gz"], "cell"), host.interior(ic["pt_or_gz"], "cell"))
-    # in-place download into caller-owned arrays (the host model's state arrays): same image, stale contents overwritten
+    # in-place download into caller-owned arrays (the host model's state arrays): the interior is overwritten, the
+    # halo cells are left alone (one strided copy of the interior; the reference refills halos with fill_halo)
+    loc = {"u_lon": "lon", "v_lat": "lat", "pt_or_gz": "cell", "phs": "2d"}
     out = {k: np.full_like(v, 7.0) for k, v in st.items() if v is not None}
     st2 = gpu.download_state(1, out=out)
     for k in out:
-        assert st2[k] is out[k] and np.array_equal(out[k], st[k]), k
+        assert st2[k] is out[k] and np.array_equal(host.interior(out[k], loc[k]), host.interior(st[k], loc[k])), k
+        assert out[k][0, 0, 0] == 7.0 and out[k][-1, -1, -1] == 7.0, k
     # the same through page-locked arrays (gmc_pin_host / gmc_unpin_host)
     for k in out:
         out[k][...] = -3.0; gpu.pin_host(out[k])
     gpu.download_state(1, out=out)
     for k in out:
-        gpu.unpin_host(out[k]); assert np.array_equal(out[k], st[k]), k
+        gpu.unpin_host(out[k]); assert np.array_equal(host.interior(out[k], loc[k]), host.interior(st[k], loc[k])), k
     with pytest.raises(RuntimeError):
         gpu.unpin_host(out["u_lon"])          # not registered any more: the CUDA error text comes back through the ABI
     with pytest.raises(ValueError):
