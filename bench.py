@@ -54,7 +54,7 @@ KERNEL_PASSES = {
 # (mx == my) and 6 on the outer call + 2 writes -> mean 7.5
 KERNEL_PASSES_HYDRO = {
     "k_hflx": 7.5, "k_ffsl_march_in": 7 + 2, "k_ffsl_march_out": 6 + 2, "k_ffsl_x_in": 4 + 1, "k_ffsl_y_in": 4 + 1,
-    "k_ffsl_x_out": 3 + 1, "k_ffsl_y_out": 3 + 1, "k_fwd1": 3 + 7, "k_tend": 9 + 2, "k_cfl": 2 + 4, "k_pt_col": 7 + 1, "k_we_col": 3 + 2,
+    "k_ffsl_x_out": 3 + 1, "k_ffsl_y_out": 3 + 1, "k_ffsl_xw_in": 4 + 1, "k_ffsl_xw_out": 3 + 1, "k_fwd1": 3 + 7, "k_tend": 9 + 2, "k_cfl": 2 + 4, "k_pt_col": 7 + 1, "k_we_col": 3 + 2,
     "k_uv_update_h": 6 + 2, "k_gz_col": 1 + 2, "k_tracer_v": 4 + 1, "k_ffsl_q": 5 + 2, "k_pv_edge": 5 + 2,
     "k_ph": 0 + 3, "k_accum": 2 + 2, "k_diag_partial": 10, "k_filter_rows": 1 + 1,
 }

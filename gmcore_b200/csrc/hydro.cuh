@@ -210,6 +210,7 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
   // outer fused.  GMCORE_FFSL_FUSED = 1 / 0 forces both calls fused / split (A/B runs).
   static const char* fenv = getenv("GMCORE_FFSL_FUSED");
   static const bool fused_in = fenv && fenv[0] == '1', fused_out = !(fenv && fenv[0] == '0');
+  static const bool xblock = getenv("GMCORE_FFSL_XBLOCK") && getenv("GMCORE_FFSL_XBLOCK")[0] == '1';   // block-staged x sweep (A/B)
   if (!old_path) {
     // inner advective half step: the fluxes stay on chip, the kernels write qx / qy (and the pole-adjacent y fluxes)
     const Geo g01 = xg(h, 0, 1);
@@ -217,7 +218,8 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
     const int w = ffsl_block_width(gw.nlon);
     if (fused_in) { const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_march, true, ffsl_march_grid(gw, gw.nlev, rj, w), w, 0, gw, h->M, in, rj); }
     else {
-      LAUNCH_LIM2(h, k_ffsl_x, true, ffsl_x_grid(gw, gw.nlev, w), dim3(w, FX_ROWS), 0, gw, h->M, in);
+      if (xblock) LAUNCH_LIM2(h, k_ffsl_x, true, ffsl_x_grid(gw, gw.nlev, w), dim3(w, FX_ROWS), 0, gw, h->M, in);
+      else LAUNCH_LIM2(h, k_ffsl_xw, true, ffsl_xw_grid(gw, gw.nlev, true), 32 * XW_WARPS, 0, gw, h->M, in);
       const int rj = ffsl_strip_rows(gw); LAUNCH_LIM2(h, k_ffsl_y, true, ffsl_y_grid(gw, gw.nlev, rj), 128, 0, gw, h->M, in, rj);
     }
     if (g0.has_south || g0.has_north) {
@@ -232,7 +234,8 @@ static void run_ffsl_h(gmc_handle* h, const BatchRef& B, const double* q, double
     FfslArgs out{B.mfx, B.mfy, h->qy, h->qx, B.cflx, B.cfly, flx, fly, nullptr, nullptr, nullptr, 0.0, g0.jb, g01.je, gn.jb, gn.je, 0, 0};
     if (fused_out) { const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_march, false, ffsl_march_grid(gn, gn.nlev, rj, w), w, 0, gn, h->M, out, rj); }
     else {
-      LAUNCH_LIM2(h, k_ffsl_x, false, ffsl_x_grid(gn, gn.nlev, w), dim3(w, FX_ROWS), 0, gn, h->M, out);
+      if (xblock) LAUNCH_LIM2(h, k_ffsl_x, false, ffsl_x_grid(gn, gn.nlev, w), dim3(w, FX_ROWS), 0, gn, h->M, out);
+      else LAUNCH_LIM2(h, k_ffsl_xw, false, ffsl_xw_grid(gn, gn.nlev, false), 32 * XW_WARPS, 0, gn, h->M, out);
       const int rj = ffsl_strip_rows(gn); LAUNCH_LIM2(h, k_ffsl_y, false, ffsl_y_grid(gn, gn.nlev, rj), 128, 0, gn, h->M, out, rj);
     }
     return;

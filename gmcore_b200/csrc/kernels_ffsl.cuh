@@ -354,6 +354,52 @@ template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_x_body(const
     a.ox[c] = qv - 0.5 * ((fx - fxm) * lel * rac - dvx * qv) * a.dt;
   }
 }
+// ---- x sweep, warp-private: no block barrier at all ------------------------------------------------------------
+// Each WARP owns a segment of one row and stages the 37 values / forms the 35 slopes its 32 edges need in its own
+// slice of shared memory (__syncwarp only).  Outer call: 32 fluxes per warp, segments aligned to 32 cells.  Inner
+// call: qx of a cell needs the fluxes through both of its edges, so a warp evaluates 32 consecutive edges and
+// writes the 31 cells between them (the west neighbour's flux comes from a shuffle): segments of 31 cells,
+// one flux in 32 evaluated twice, no barrier and no special thread.
+#ifndef XW_WARPS
+#define XW_WARPS 4
+#endif
+template <int LIM, bool INNER> __device__ __forceinline__ void ffsl_xw_body(const Geo& g, const DMesh& M, const FfslArgs& a) {
+  __shared__ double xs_[XW_WARPS][40];      // values of cells e0-2 .. e0+34, index = local cell + 2
+  __shared__ double ss_[XW_WARPS][36];      // slopes of cells e0-1 .. e0+33, index = local cell + 1
+  const int n = g.nlon, lane = threadIdx.x & 31, w = threadIdx.x >> 5, k = blockIdx.z;
+  const int j = g.jb + blockIdx.y;
+  if (!(j > 1 && j < g.nlat && j >= a.jx0 && j <= a.jx1)) return;             // block-uniform
+  constexpr int STR = INNER ? 31 : 32;      // cells written per warp
+  const int o0 = (blockIdx.x * XW_WARPS + w) * STR;
+  if (o0 >= n) return;                      // warp-uniform
+  const int e0 = INNER ? o0 - 1 : o0;       // lane l evaluates the flux through the east edge of cell e0 + l
+  double* __restrict__ xs = xs_[w]; double* __restrict__ ss = ss_[w];
+  const int rb = gidx(g, 0, j, k);
+  const double* __restrict__ mxr = a.mx + rb;
+  const int ce = e0 + lane, cw = wrapi(ce, n);
+  // ---- one memory phase ---------------------------------------------------------------------------------------
+  const double v = __ldg(mxr + cw), cx = __ldg(a.cflx + rb + cw), uu = __ldg(a.u + rb + cw);
+  const int alc = lane < 2 ? lane - 2 : 30 + lane;                            // apron cells -2, -1, 32, 33, 34 (lanes 0..4)
+  const double xa = lane < 5 ? __ldg(mxr + wrapi(e0 + alc, n)) : 0.0;
+  double dvx = 0, lel = 0, rac = 0;
+  if (INNER) { dvx = __ldg(a.divx + rb + cw); const RowCoef* __restrict__ R = M.rows + (j + 1); lel = R->le_lon; rac = R->r_area_cell; }
+  xs[lane + 2] = v;
+  if (lane < 5) xs[alc + 2] = xa;
+  __syncwarp();
+  ss[lane + 1] = cell_slope<LIM>(xs[lane + 1], v, xs[lane + 3]);
+  if (lane < 3) { const int sl = lane == 0 ? -1 : 31 + lane; ss[sl + 1] = cell_slope<LIM>(xs[sl + 1], xs[sl + 2], xs[sl + 3]); }
+  __syncwarp();
+  const double fx = ffsl_flux_x_smem<LIM>(xs - 1, ss - 1, mxr, lane, cw, n, cx, uu);
+  if (!INNER) { if (ce < n) a.ox[rb + ce] = fx; return; }
+  const double fxm = __shfl_up_sync(0xffffffffu, fx, 1);
+  if (lane >= 1 && ce < n) a.ox[rb + ce] = v - 0.5 * ((fx - fxm) * lel * rac - dvx * v) * a.dt;      // ffsl_mod.F90:358-362
+}
+template <int LIM> __global__ void __launch_bounds__(32 * XW_WARPS) k_ffsl_xw_in(Geo g, DMesh M, FfslArgs a) { ffsl_xw_body<LIM, true>(g, M, a); }
+template <int LIM> __global__ void __launch_bounds__(32 * XW_WARPS) k_ffsl_xw_out(Geo g, DMesh M, FfslArgs a) { ffsl_xw_body<LIM, false>(g, M, a); }
+static inline dim3 ffsl_xw_grid(const Geo& g, int nk, bool inner) {
+  const int str = inner ? 31 : 32, segs = (g.nlon + str - 1) / str;
+  return dim3((segs + XW_WARPS - 1) / XW_WARPS, g.je - g.jb + 1, nk);
+}
 template <int LIM> __global__ void __launch_bounds__(128, FY_MINB) k_ffsl_y_in(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_y_body<LIM, true>(g, M, a, rj); }
 template <int LIM> __global__ void __launch_bounds__(128, FY_MINB) k_ffsl_y_out(Geo g, DMesh M, FfslArgs a, int rj) { ffsl_y_body<LIM, false>(g, M, a, rj); }
 template <int LIM> __global__ void __launch_bounds__(FM_WMAX * FX_ROWS, FX_MINB) k_ffsl_x_in(Geo g, DMesh M, FfslArgs a) { ffsl_x_body<LIM, true>(g, M, a); }
