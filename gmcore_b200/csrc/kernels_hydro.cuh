@@ -192,11 +192,21 @@ __device__ __forceinline__ double m_lev_at(const DMesh& M, const VC& vc, int nle
 // RK4 in eta for one half level (adv_batch_mod.F90:529-627).  wm is this column's eta velocity
 // we_lev / m_lev * half_dlev per half level (index 0 = half level 1), staged in shared memory with
 // stride `st`: one divide per level instead of the reference's seven per RK4 evaluation.
-__device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const double* wm, int st,
+// lev = the block's shared-memory copy of the level tables (cflz_tables): the departure searches read half_lev in a
+// dependent loop, which through global memory was the hottest line of k_we_col (ncu r02: 32 % of its instructions)
+__device__ __forceinline__ void cflz_tables(const DMesh& M, int nlev, double* lev, int tid, int nthreads) {
+  for (int l = tid; l <= nlev + 1; l += nthreads) {        // l = 0 .. nlev+1
+    lev[l] = l >= 1 ? M.half_lev[l - 1] : 0.0;             // lev[l] = half_lev(l), l = 1 .. nlev+1
+    lev[(nlev + 2) + l] = M.full_dlev[l + 1];              // full_dlev(l), l = 0 .. nlev+1 (stored from -1)
+    lev[2 * (nlev + 2) + l] = M.r_full_dlev[l + 1];
+  }
+}
+static inline size_t cflz_tables_bytes(int nlev) { return (size_t)3 * (nlev + 2) * sizeof(double); }
+__device__ __forceinline__ bool cflz_one(const double* __restrict__ lev, int nlev, int k1, const double* wm, int st,
                                          double dt, double* out, int* flags) {
-  const double* hl = M.half_lev - 1;     // hl[l] = half_lev(l)
-  const double* fd = M.full_dlev + 1;    // fd[l] = full_dlev(l), stored from -1
-  const double* rfd = M.r_full_dlev + 1;
+  const double* hl = lev;                      // hl[l] = half_lev(l)
+  const double* fd = lev + (nlev + 2);         // fd[l] = full_dlev(l)
+  const double* rfd = lev + 2 * (nlev + 2);
   auto search = [&](double w, double z) {
     int l;
     if (w > 0) { for (l = k1; l <= nlev; ++l) if (hl[l] <= z && z <= hl[l + 1]) break; if (l == nlev + 1) { atomicOr(flags, 4); l = nlev; } }
@@ -238,8 +248,8 @@ __device__ __forceinline__ bool cflz_one(const DMesh& M, int nlev, int k1, const
 #ifndef WECOL_PFM
 #define WECOL_PFM 1
 #endif
-static inline size_t we_col_smem(int nlev) { return (size_t)((nlev + 1) + 2 * nlev + 1) * WE_TX * sizeof(double); }
-static inline size_t cflz_smem(int nlev) { return (size_t)(nlev + 1) * WE_TX * sizeof(double); }
+static inline size_t we_col_smem(int nlev) { return (size_t)((nlev + 1) + 2 * nlev + 1) * WE_TX * sizeof(double) + cflz_tables_bytes(nlev); }
+static inline size_t cflz_smem(int nlev) { return (size_t)(nlev + 1) * WE_TX * sizeof(double) + cflz_tables_bytes(nlev); }
 __global__ void __launch_bounds__(WE_TX * WE_TY) k_we_col(Geo g, DMesh M, WeArgs a) {
   extern __shared__ double wm_s[];       // wm[nlev+1][TX] | dlon[nlev][TX] | dlat[nlev][TX] | dphs[TX]
   const int tx = threadIdx.x, ty = threadIdx.y, nlev = g.nlev;
@@ -255,6 +265,8 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_we_col(Geo g, DMesh M, WeArgs
   double* dl = wm_s + (nlev + 1) * WE_TX + tx;
   double* da = dl + nlev * WE_TX;
   double* dps = wm_s + ((nlev + 1) + 2 * nlev) * WE_TX;
+  double* lev = dps + WE_TX;
+  cflz_tables(M, nlev, lev, ty * WE_TX + tx, WE_TX * WE_TY);      // visible after the first barrier, used by the RK4 phase
   // calc_grad_mf (operators_mod.F90:1114-1166): the two divergence parts of every level
   if (act) {
 #pragma unroll 4
@@ -302,7 +314,7 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_we_col(Geo g, DMesh M, WeArgs
   if (act) {
     for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
       double cz;
-      if (cflz_one(M, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+      if (cflz_one(lev, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
     }
   }
 }
@@ -317,6 +329,8 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_cflz(Geo g, DMesh M, CflzArgs
   const bool act = i < g.nlon;
   const int st = (int)g.plane, c0 = act ? gidx(g, i, j, 0) : 0;
   double* wm = wm_s + tx;
+  double* lev = wm_s + (nlev + 1) * WE_TX;
+  cflz_tables(M, nlev, lev, ty * WE_TX + tx, WE_TX * WE_TY);
   const double* hd = M.half_dlev - 1;
   if (act)
 #pragma unroll 4
@@ -326,7 +340,7 @@ __global__ void __launch_bounds__(WE_TX * WE_TY) k_cflz(Geo g, DMesh M, CflzArgs
   if (act)
     for (int k1 = 2 + ty; k1 <= nlev; k1 += WE_TY) {
       double cz;
-      if (cflz_one(M, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
+      if (cflz_one(lev, nlev, k1, wm, WE_TX, a.dt, &cz, a.flags)) a.cflz[c0 + (k1 - 1) * st] = cz;
     }
 }
 
