@@ -75,12 +75,46 @@ struct CflArgs {
   double dt, radius; int* flags;
   int jx0, jx1, jy0, jy1;              // rows of the x part (cflx, divx, divy) / the y part (cfly); band mode
 };
-// One memory phase in the common case: a departure point less than one cell away (|CFL| < 1, everywhere
-// except the polar rows in x) interpolates between the edge's own value and one of its two neighbours, so
-// the three-point windows u(i-1..i+1), v(j-1..j+1) and the edge coordinates are loaded up front and the three
-// RK4 stages are register arithmetic; a lane whose point leaves the window gathers as the reference does
-// (adv_batch_mod.F90:256-288,290-335).  x and y chains are interleaved; divides by dx, dy, area_cell are
-// multiplies by host-formed reciprocals.
+// The reference's RK4 loop for one edge with gathers at any distance (adv_batch_mod.F90:256-288 / 290-335): the slow
+// path of k_cfl, taken by the lanes whose departure point leaves the three-point window (polar rows in x).
+__device__ __noinline__ double cfl_chain_x(const double* __restrict__ ur, const double* __restrict__ hl, int i1, int n, int hx,
+                                           double rcl, double rdx, double x0, double u1, double dt, int* flags) {
+  double x = x0 + dt / 2 * u1, us[3];
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const double h = s == 1 ? dt : dt / 2;
+    int lx = __double2int_rd(i1 + (x - x0) * rdx), d = lx - i1;
+    // a departure point outside the longitude halo is the reference's "cflx exceeds mesh%lon_halo_width" abort
+    // (adv_batch_mod.F90:284-287): raise the guard and keep the gather inside the coefficient table
+    if (d < -hx || d > hx - 2) { atomicOr(flags, 1); d = d < 0 ? -hx : hx - 2; lx = i1 + d; }
+    const double ua = __ldg(ur + wrapi(lx - 1, n)), ub = __ldg(ur + wrapi(lx, n)), xl = rcl * hl[lx], xr = rcl * hl[lx + 1];
+    us[s] = ((xr - x) * ua + (x - xl) * ub) * rdx; x = x0 + h * us[s];
+  }
+  return (u1 + 2 * us[0] + 2 * us[1] + us[2]) * (1.0 / 6.0) * dt * rdx;
+}
+// vc = &v(i, j, k); half_lat = mesh vector (entry j at [j + 1])
+__device__ __noinline__ double cfl_chain_y(const double* __restrict__ vc, const double* __restrict__ half_lat, int j, int n, int nhalf,
+                                           double radius, double rdy, double y0, double v1, double dt) {
+  double y = y0 + dt / 2 * v1, vs[3];
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const double h = s == 1 ? dt : dt / 2;
+    const int ly = __double2int_rd(j + (y - y0) * rdy);
+    if (ly < 1 || ly > nhalf - 1) vs[s] = v1;
+    else {
+      const double va = __ldg(vc + (ly - j) * n), vb = __ldg(vc + (ly + 1 - j) * n), yl = radius * half_lat[ly + 1], yr = radius * half_lat[ly + 2];
+      vs[s] = ((yr - y) * va + (y - yl) * vb) * rdy;
+    }
+    y = y0 + h * vs[s];
+  }
+  return (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) * (1.0 / 6.0) * dt * rdy;
+}
+// One memory phase and straight-line code in the common case: a departure point less than one cell away (|CFL| < 1,
+// everywhere except the polar rows in x) interpolates between the edge's own value and one of its two neighbours, so the
+// three-point windows u(i-1..i+1), v(j-1..j+1) and the edge coordinates are loaded up front and the three RK4 stages are
+// branch-free register arithmetic (the window side is a select); a lane whose point leaves the window at any stage redoes
+// its chain with the reference's gathers (cfl_chain_x / _y) -- same expressions, hence the same bits where both apply.
+// x and y chains interleave; divides by dx, dy, area_cell are multiplies by host-formed reciprocals.
 template <bool EDGE> __device__ __forceinline__ void cfl_body(const Geo& g, const DMesh& M, const CflArgs& a, int i, int j, int k) {
   const int n = g.nlon, c = gidx(g, i, j, k), rb = c - i;
   const int i1 = i + 1;                       // Fortran index
@@ -96,50 +130,51 @@ template <bool EDGE> __device__ __forceinline__ void cfl_body(const Geo& g, cons
   if (doy) v_n = __ldg(a.v + c + n);
   const double xm = rcl * hl[i1 - 1], x0 = rcl * hl[i1], xp = rcl * hl[i1 + 1];
   const double ym = a.radius * R[-1].half_lat, y0 = a.radius * R->half_lat, yp = a.radius * R[1].half_lat;
+  const double fi1 = (double)i1, fj = (double)j;
   double x = x0 + a.dt / 2 * u1, y = y0 + a.dt / 2 * v1;
   double us[3], vs[3];
+  bool slowx = false, slowy = false;
 #pragma unroll
   for (int s = 0; s < 3; ++s) {
     const double h = s == 1 ? a.dt : a.dt / 2;
-    if (dox) {
-      int lx = __double2int_rd(i1 + (x - x0) * rdx), d = lx - i1;
-      // a departure point outside the longitude halo is the reference's "cflx exceeds mesh%lon_halo_width" abort
-      // (adv_batch_mod.F90:284-287): raise the guard and keep the gather inside the coefficient table
-      if (d < -M.hx || d > M.hx - 2) { atomicOr(a.flags, 1); d = d < 0 ? -M.hx : M.hx - 2; lx = i1 + d; }
-      double ua, ub, xl, xr;
-      if (d == 0) { ua = u1; ub = u_p; xl = x0; xr = xp; }
-      else if (d == -1) { ua = u_m; ub = u1; xl = xm; xr = x0; }
-      else { ua = __ldg(ur + wrapi(lx - 1, n)); ub = __ldg(ur + wrapi(lx, n)); xl = rcl * hl[lx]; xr = rcl * hl[lx + 1]; }
+    {
+      const int d = __double2int_rd(fi1 + (x - x0) * rdx) - i1;
+      const bool e = d == 0;
+      slowx |= (unsigned)(d + 1) > 1u;
+      const double ua = e ? u1 : u_m, ub = e ? u_p : u1, xl = e ? x0 : xm, xr = e ? xp : x0;
       us[s] = ((xr - x) * ua + (x - xl) * ub) * rdx; x = x0 + h * us[s];
     }
-    if (doy) {
-      const int ly = __double2int_rd(j + (y - y0) * rdy), d = ly - j;
-      const bool inr = !(ly < 1 || ly > g.nhalf - 1);
-      double va, vb, yl, yr;
-      if (d == 0) { va = v1; vb = v_n; yl = y0; yr = yp; }
-      else if (d == -1) { va = v_s; vb = v1; yl = ym; yr = y0; }
-      else if (inr) { va = ldW(a.v, g, i, ly, k); vb = ldW(a.v, g, i, ly + 1, k); yl = a.radius * MJ(M.half_lat, ly); yr = a.radius * MJ(M.half_lat, ly + 1); }
-      else { va = vb = yl = yr = 0; }
-      vs[s] = inr ? ((yr - y) * va + (y - yl) * vb) * rdy : v1;
+    {
+      const int ly = __double2int_rd(fj + (y - y0) * rdy), d = ly - j;
+      const bool inr = !(ly < 1 || ly > g.nhalf - 1), e = d == 0;
+      slowy |= inr && (unsigned)(d + 1) > 1u;
+      const double va = e ? v1 : v_s, vb = e ? v_n : v1, yl = e ? y0 : ym, yr = e ? yp : y0;
+      const double r = ((yr - y) * va + (y - yl) * vb) * rdy;
+      vs[s] = inr ? r : v1;                   // adv_batch_mod.F90:301-303: outside the half rows -> v1
       y = y0 + h * vs[s];
     }
   }
   if (dox) {
     const double rac = R->r_area_cell;
-    const double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) * (1.0 / 6.0) * a.dt * rdx;
+    double cf = (u1 + 2 * us[0] + 2 * us[1] + us[2]) * (1.0 / 6.0) * a.dt * rdx;
+    if (slowx) cf = cfl_chain_x(ur, hl, i1, n, M.hx, rcl, rdx, x0, u1, a.dt, a.flags);
     a.cflx[c] = cf;
     if (fabs(cf) > M.hx) atomicOr(a.flags, 1);
     a.divx[c] = (u1 - u_m) * R->le_lon * rac;
     a.divy[c] = (v1 * R->le_lat - v_s * R[-1].le_lat) * rac;
   }
   if (doy) {
-    const double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) * (1.0 / 6.0) * a.dt * rdy;
+    double cf = (v1 + 2 * vs[0] + 2 * vs[1] + vs[2]) * (1.0 / 6.0) * a.dt * rdy;
+    if (slowy) cf = cfl_chain_y(a.v + c, M.half_lat, j, n, g.nhalf, a.radius, rdy, y0, v1, a.dt);
     a.cfly[c] = cf;
     if (fabs(cf) > 1) atomicOr(a.flags, 2);
   }
 }
 // 10 blocks per SM (48 registers, a 136-byte spill on the gather path) measured 2.5 % faster than 64 registers / 8 blocks
-__global__ void __launch_bounds__(128, 10) k_cfl(Geo g, DMesh M, CflArgs a) {
+#ifndef CFL_MINB
+#define CFL_MINB 10
+#endif
+__global__ void __launch_bounds__(128, CFL_MINB) k_cfl(Geo g, DMesh M, CflArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
   if (i >= g.nlon || j > g.je) return;
