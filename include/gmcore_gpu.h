@@ -139,6 +139,18 @@ int gmc_diagnose(gmc_handle* h, int itime, double out[8]);
  * the sums only when the 'print' alert rings (gmcore_mod.F90:140-142). */
 int gmc_diagnose_enqueue(gmc_handle* h, int itime);
 int gmc_diagnose_collect(gmc_handle* h, double* out, int max_sets, int* nsets);
+/* gmc_diagnose without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same sums as gmc_diagnose of a single-band handle, same out[8] order and guard behaviour; the block sums and
+ * the eight results live in ONE file-scope `static __device__` array of GMC_STATIC_SCRATCH_DOUBLES doubles (4 MiB)
+ * that every GPU loading the library holds until exit, instead of the handle's cudaMalloc'd buffers.  The call
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine, no host heap).  It needs
+ * 32 + 7 * lat_rows * nlev doubles and returns non-zero with a text in gmc_last_error for larger grids (up to
+ * 0.25 deg x 64 levels fit) and for band handles (nranks > 1, linked groups, NCCL).  Every call on a GPU shares the
+ * array, which keeps the last call's contents: the used part is cleared first, and calls that overlap on one GPU
+ * (several handles / streams / host threads) race -- serialise them. */
+#define GMC_STATIC_SCRATCH_DOUBLES (512 * 1024)
+int gmc_diagnose_static(gmc_handle* h, int itime, double out[8]);
 
 /* Read back one named derived field of state(itime) for parity tests/history
  * (history_mod.F90 h0 variable set and the per-state work arrays).  buf uses the
