@@ -380,16 +380,22 @@ def _main(out):
     (gpu2.set_state_sliced if banded else gpu2.set_state)(icp)
     if q0 is not None:
         (gpu2.set_tracers_sliced if banded else gpu2.set_tracers)(q0p); h2d += sum(wire_bytes(x) for x in q0p)
+    t1 = time.perf_counter()
     gpu2.prepare_run()
     for _ in range(K):
         gpu2.time_integrate()
         gpu2.diagnose()
+    t2 = time.perf_counter()
     st = gpu2.download_state(out=outp)
     gpu2.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    t3 = time.perf_counter()
+    e2e_s = max_over_ranks(t3 - t0, world)
+    # host timestamps of rank 0 at the phase boundaries (no synchronisation added: the uploads, every diagnose and the
+    # download are synchronous calls already)
+    phases = {"upload": (t1 - t0) * 1e3, "prepare_run+steps": (t2 - t1) * 1e3, "download": (t3 - t2) * 1e3}
     d2h = sum(wire_bytes(v) for v in st.values())
     e2e = {"value": (1 if banded else world) * K * wl["dt"] / e2e_s, "unit": "simulated days/day",
-           "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K + 64, "bytes_are": "per rank",
+           "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K + 64, "bytes_are": "per rank", "phases_ms_rank0": phases,
            "region": "upload_state(pinned)+prepare_run+K*(time_integrate+diagnose D2H)+download_state"}
     gpu2.close()
 
