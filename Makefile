@@ -20,7 +20,7 @@ all: host gpu oracle
 
 host: $(LIBDIR)/libgmcore_host.so
 gpu: $(LIBDIR)/libgmcore_b200.so
-oracle: oracle/_build/liboracle.so oracle/_build/liboracle_fast.so
+oracle: oracle/_build/liboracle.so oracle/_build/liboracle_fast.so oracle/_build/libfastmath_host.so
 
 $(LIBDIR)/libgmcore_host.so: $(HOSTSRC) $(HOSTHDR)
 	@mkdir -p $(LIBDIR)
@@ -37,6 +37,11 @@ oracle/_build/liboracle.so: $(ORCSRC) $(ORCHDR)
 oracle/_build/liboracle_fast.so: $(ORCSRC) $(ORCHDR)
 	@mkdir -p oracle/_build
 	$(CXX) -std=c++17 -O3 -march=x86-64-v3 -fPIC -fno-fast-math -fopenmp -DORC_OPENMP -DORC_OPENMP_LOOPS -shared -o $@ $(ORCSRC)
+
+# host build of the device's pow_pos / log_pos (tests only: accuracy against libquadmath, bit identity with the device)
+oracle/_build/libfastmath_host.so: tests/fastmath_host.cpp gmcore_b200/csrc/fastmath.cuh
+	@mkdir -p oracle/_build
+	$(CXX) -std=gnu++17 -O2 -fPIC -fno-fast-math -ffp-contract=off -mfma -x c++ -shared -o $@ tests/fastmath_host.cpp -lquadmath
 
 clean:
 	rm -rf $(LIBDIR) oracle/_build

@@ -493,3 +493,24 @@ extern "C" int gmc_diagnose_static(gmc_handle* h, int itime, double out[8]) {
   }
   return 0;
 }
+
+// ---- gmc_fastmath_eval: the device results of pow_pos / log_pos for the bit-identity test ---------------------------
+// out[i] = pow_pos(x[i], y) (what = 0) or log_pos(x[i]) (what = 1), evaluated on the current device.  Host arrays in and
+// out; a verification hook (tests/test_fastmath_gpu.py compares with the host build of the same source), not part of
+// the time-stepping path.
+__global__ void k_fastmath_eval(int what, const double* x, double y, double* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = what == 0 ? pow_pos(x[i], y) : log_pos(x[i]);
+}
+extern "C" int gmc_fastmath_eval(int what, const double* x, double y, double* out, int n) {
+  if (n <= 0 || !x || !out || what < 0 || what > 1) return 1;
+  double *dx = nullptr, *dout = nullptr;
+  int rc = 1;
+  if (cudaMalloc(&dx, (size_t)n * 8) == cudaSuccess && cudaMalloc(&dout, (size_t)n * 8) == cudaSuccess &&
+      cudaMemcpy(dx, x, (size_t)n * 8, cudaMemcpyHostToDevice) == cudaSuccess) {
+    k_fastmath_eval<<<(n + 255) / 256, 256>>>(what, dx, y, dout, n);
+    if (cudaMemcpy(out, dout, (size_t)n * 8, cudaMemcpyDeviceToHost) == cudaSuccess && cudaGetLastError() == cudaSuccess) rc = 0;
+  }
+  cudaFree(dx); cudaFree(dout);
+  return rc;
+}

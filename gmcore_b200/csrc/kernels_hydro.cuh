@@ -9,9 +9,22 @@
 #pragma once
 #include "handle.cuh"
 #include "kernels_dyn.cuh"
+#include "fastmath.cuh"
 
 // Vertical-coordinate constants (hybrid_coord_mod.F90:146-171), by value.
 struct VC { double ptop, p0h, p0, kappa, Rd; };
+// Exner function and layer thickness (k_ph, k_gz_col, k_lev_tab): positive-argument pow / log of fastmath.cuh
+// (GMC_FASTMATH=0: the CUDA library routines, for A/B runs)
+#ifndef GMC_FASTMATH
+#define GMC_FASTMATH 1
+#endif
+#if GMC_FASTMATH
+#define GM_POW(x, y) pow_pos(x, y)
+#define GM_LOG(x) log_pos(x)
+#else
+#define GM_POW(x, y) pow(x, y)
+#define GM_LOG(x) log(x)
+#endif
 
 __device__ __forceinline__ double ph_lev_at(const DMesh& M, const VC& vc, int k1 /*1-based half level*/, double phs) {
   return M.hyai[k1 - 1] * (vc.p0h - vc.ptop) + M.hybi[k1 - 1] * (phs - vc.ptop) + vc.ptop;
@@ -589,7 +602,7 @@ __global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
   const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
   const long long c = gidx(g, i, j, k);
   const double pl = ph_lev_at(M, a.vc, k + 1, phs);
-  a.ph_exn_lev[c] = k + 1 <= M.nconst ? __ldg(M.lev_tab + k) : pow(pl, a.vc.kappa);
+  a.ph_exn_lev[c] = k + 1 <= M.nconst ? __ldg(M.lev_tab + k) : GM_POW(pl, a.vc.kappa);
   a.m_lev[c] = m_lev_at(M, a.vc, g.nlev, k + 1, phs);
   if (k < g.nlev) {
     const double m = ph_lev_at(M, a.vc, k + 2, phs) - pl;
@@ -604,12 +617,12 @@ __global__ void k_lev_tab(DMesh M, VC vc, int nlev, double* tab) {
   if (k > nlev) return;
   const double rp0 = 1.0 / vc.p0;
   const double pl0 = ph_lev_at(M, vc, k + 1, vc.p0);
-  tab[k] = pow(pl0, vc.kappa);
+  tab[k] = GM_POW(pl0, vc.kappa);
   if (k < nlev) {
     const double pl1 = ph_lev_at(M, vc, k + 2, vc.p0);
     const double ph = 0.5 * (pl0 + pl1);
-    tab[nlev + 1 + k] = pow(ph * rp0, vc.kappa);
-    tab[2 * (nlev + 1) + k] = log(qdiv(pl1, pl0));
+    tab[nlev + 1 + k] = GM_POW(ph * rp0, vc.kappa);
+    tab[2 * (nlev + 1) + k] = GM_LOG(qdiv(pl1, pl0));
   }
 }
 
@@ -633,9 +646,9 @@ __global__ void __launch_bounds__(128) k_gz_col(Geo g, DMesh M, GzArgs a) {
     const double pl0 = ph_lev_at(M, a.vc, k + 1, phs);
     const double ph = 0.5 * (pl0 + pl1);
     const bool cst = k + 2 <= M.nconst;       // both interfaces of this layer are pure-pressure levels
-    const double t = __ldg(a.pt + c0 + k * st) * (cst ? __ldg(M.lev_tab + (g.nlev + 1) + k) : pow(ph * rp0, a.vc.kappa));
+    const double t = __ldg(a.pt + c0 + k * st) * (cst ? __ldg(M.lev_tab + (g.nlev + 1) + k) : GM_POW(ph * rp0, a.vc.kappa));
     a.t[c0 + k * st] = t;
-    dgz = dgz + a.vc.Rd * t * (cst ? __ldg(M.lev_tab + 2 * (g.nlev + 1) + k) : log(qdiv(pl1, pl0)));
+    dgz = dgz + a.vc.Rd * t * (cst ? __ldg(M.lev_tab + 2 * (g.nlev + 1) + k) : GM_LOG(qdiv(pl1, pl0)));
     a.gz_lev[c0 + k * st] = gzs + dgz;
     pl1 = pl0;
   }
@@ -906,6 +919,6 @@ __global__ void __launch_bounds__(128) k_held_suarez(Geo g, DMesh M, HsArgs a) {
   const double phs = __ldg(a.phs_f + gidx(g, i, j, 0));
   const double ph = 0.5 * (ph_lev_at(M, a.vc, k + 1, phs) + ph_lev_at(M, a.vc, k + 2, phs));
   const double p_p0 = ph / a.vc.p0;
-  const double teq = fmax(200.0, (315.0 - 60.0 * (sn * sn) - 10.0 * log(p_p0) * (cl * cl)) * pow(p_p0, a.vc.kappa));
+  const double teq = fmax(200.0, (315.0 - 60.0 * (sn * sn) - 10.0 * GM_LOG(p_p0) * (cl * cl)) * GM_POW(p_p0, a.vc.kappa));
   a.pt[c] = a.pt[c] - a.dt * kt * a.pt[c] * (1.0 - teq / __ldg(a.t + c));
 }

@@ -18,7 +18,7 @@ _LIB = None
 ABI_SYMBOLS = ["gmc_create", "gmc_destroy", "gmc_set_mesh", "gmc_set_filters", "gmc_set_static",
                "gmc_upload_state", "gmc_download_state", "gmc_set_tracers", "gmc_get_tracers",
                "gmc_prepare_run", "gmc_time_integrate", "gmc_run_steps", "gmc_diagnose", "gmc_get_field",
-               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_prescribe_we", "gmc_adv_step", "gmc_interp_pressure_level", "gmc_diagnose_enqueue", "gmc_diagnose_collect", "gmc_diagnose_static",
+               "gmc_synchronize", "gmc_launch_count", "gmc_last_error", "gmc_reset_clock", "gmc_adv_prescribe", "gmc_adv_prescribe_we", "gmc_adv_step", "gmc_interp_pressure_level", "gmc_diagnose_enqueue", "gmc_diagnose_collect", "gmc_diagnose_static", "gmc_fastmath_eval",
                "gmc_group_link", "gmc_nccl_unique_id", "gmc_nccl_init", "gmc_pin_host", "gmc_unpin_host",
                "gmc_add_tracer_batch", "gmc_set_batch_tracers", "gmc_get_batch_tracers"]
 
@@ -70,6 +70,7 @@ def load_library():
     lib.gmc_adv_prescribe_we.argtypes = [V, C.c_int, P]
     lib.gmc_diagnose_enqueue.argtypes = [V, C.c_int]
     lib.gmc_diagnose_static.argtypes = [V, C.c_int, P]
+    lib.gmc_fastmath_eval.argtypes = [C.c_int, P, C.c_double, P, C.c_int]
     lib.gmc_diagnose_collect.argtypes = [V, P, C.c_int, C.POINTER(C.c_int)]
     lib.gmc_interp_pressure_level.argtypes = [V, C.c_int, C.c_char_p, C.c_double, C.c_int, C.c_double, P]
     lib.gmc_adv_step.argtypes = [V, C.c_int, C.c_int]

@@ -195,6 +195,12 @@ int gmc_pin_host(gmc_handle* h, void* ptr, size_t bytes);
 int gmc_unpin_host(gmc_handle* h, void* ptr);
 /* Device milliseconds spent in, and kernels launched by, calls on this handle
  * since the last reset (CUDA events on the handle's stream). */
+/* Verification hook for the positive-argument pow / log the Exner function and the hydrostatic integral use on the
+ * device (gmcore_b200/csrc/fastmath.cuh, replacing the ** and log of calc_ph / calc_t / calc_gz_lev,
+ * operators_mod.F90:136-190,433-469): out[i] = pow_pos(x[i], y) (what = 0) or log_pos(x[i]) (what = 1), evaluated on
+ * the current device from host arrays.  The same source compiles for the host, where it is held to < 1 ulp against
+ * libquadmath; the GPU test checks that the device returns the host's bits. */
+int gmc_fastmath_eval(int what, const double* x, double y, double* out, int n);
 int gmc_launch_count(gmc_handle* h, long long* launches);
 int gmc_last_error(gmc_handle* h, char* buf, int len);
 

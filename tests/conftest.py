@@ -13,7 +13,8 @@ sys.path.insert(0, ROOT)
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
     # host + oracle libraries are CPU code; build them if the in-tree copies are missing
-    need = [os.path.join(ROOT, "gmcore_b200/lib/libgmcore_host.so"), os.path.join(ROOT, "oracle/_build/liboracle.so")]
+    need = [os.path.join(ROOT, "gmcore_b200/lib/libgmcore_host.so"), os.path.join(ROOT, "oracle/_build/liboracle.so"),
+            os.path.join(ROOT, "oracle/_build/libfastmath_host.so")]
     if not all(os.path.exists(p) for p in need):
         subprocess.check_call(["make", "-C", ROOT, "host", "oracle"], stdout=subprocess.DEVNULL)
 
