@@ -185,7 +185,7 @@ static inline dim3 gridg(const Geo& g, int nk, int bx = 128) { return dim3((g.nl
 // (operators_prepare backward_pass, operators_mod.F90:123-130)
 static void run_ph(gmc_handle* h, DState& S, const Geo& g) {
   PhArgs p{S.phs_f, S.ph_exn_lev, S.m, S.m_lev, make_vc(h), h->dflags};
-  LAUNCH(h, k_ph, gridg(g, g.nlev + 1), 128, 0, g, h->M, p);
+  LAUNCH(h, k_ph, gridg(g, PH_COL ? 1 : g.nlev + 1), 128, 0, g, h->M, p);
 }
 static void run_gz(gmc_handle* h, DState& S, const Geo& g) {
   GzArgs a{S.pt, S.phs_f, h->gzs, S.t, S.gz_lev, make_vc(h)};

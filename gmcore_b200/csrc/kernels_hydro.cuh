@@ -595,6 +595,37 @@ template <int LIM> __global__ void __launch_bounds__(128) k_pt_col(Geo g, DMesh 
 // ---- calc_ph + calc_m (operators_mod.F90:136-168,471-543) from the filtered phs ------
 // ph_lev / ph are never stored: they are affine in phs_f and re-formed where needed.
 struct PhArgs { const double* phs_f; double *ph_exn_lev, *m, *m_lev; VC vc; int* flags; };
+// PH_COL 1 (default): one thread per column walking down the half levels with the three interface pressures a level
+// needs in registers, so that every ph_lev is formed once per column instead of up to six times per point and the
+// index arithmetic is paid once (the per-point version below spent 110 of its ~235 instructions outside pow).
+// Same expressions per point: bit-identical to the per-point kernel (grid z = nlev + 1), kept for A/B runs.
+#ifndef PH_COL
+#define PH_COL 1
+#endif
+#if PH_COL
+__global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = g.jb + blockIdx.y;
+  if (i >= g.nlon) return;
+  const int st = (int)g.plane, nlev = g.nlev, c0 = gidx(g, i, j, 0);
+  const double phs = __ldg(a.phs_f + c0);
+  double plm = 0.0, pl = ph_lev_at(M, a.vc, 1, phs), plp = ph_lev_at(M, a.vc, 2, phs);      // ph_lev(k), (k+1), (k+2)
+  bool bad = false;
+  for (int k = 0; k <= nlev; ++k) {                    // half level k+1
+    const int c = c0 + k * st;
+    a.ph_exn_lev[c] = k + 1 <= M.nconst ? __ldg(M.lev_tab + k) : GM_POW(pl, a.vc.kappa);
+    double ml;                                         // m_lev_at(k + 1)
+    if (k == 0) ml = 0.5 * (pl + plp) - pl;
+    else if (k == nlev) ml = pl - 0.5 * (plm + pl);
+    else ml = 0.5 * (pl + plp) - 0.5 * (plm + pl);
+    a.m_lev[c] = ml;
+    if (k < nlev) { const double m = plp - pl; a.m[c] = m; bad |= m <= 0; }
+    plm = pl; pl = plp;
+    plp = k + 3 <= nlev + 1 ? ph_lev_at(M, a.vc, k + 3, phs) : 0.0;
+  }
+  if (bad) atomicOr(a.flags, 8);
+}
+#else
 __global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = g.jb + blockIdx.y, k = blockIdx.z;     // k = 0..nlev (half level k+1)
@@ -610,6 +641,7 @@ __global__ void __launch_bounds__(128) k_ph(Geo g, DMesh M, PhArgs a) {
     if (m <= 0) atomicOr(a.flags, 8);
   }
 }
+#endif
 
 // Per-level table of the pure-pressure levels (DMesh.lev_tab); phs is irrelevant there (hybi == 0).
 __global__ void k_lev_tab(DMesh M, VC vc, int nlev, double* tab) {
