@@ -115,6 +115,10 @@ module gmcore_gpu_mod
     integer(c_int) function gmc_diagnose(h, itime, out) bind(c, name='gmc_diagnose')
       import; type(c_ptr), value :: h; integer(c_int), value :: itime; real(c_double), intent(out) :: out(8)
     end function
+    ! same sums as gmc_diagnose, scratch in the library's static device array: allocates nothing (single-band handles)
+    integer(c_int) function gmc_diagnose_static(h, itime, out) bind(c, name='gmc_diagnose_static')
+      import; type(c_ptr), value :: h; integer(c_int), value :: itime; real(c_double), intent(out) :: out(8)
+    end function
     integer(c_int) function gmc_get_field(h, itime, name, buf) bind(c, name='gmc_get_field')
       import; type(c_ptr), value :: h, buf; integer(c_int), value :: itime; character(kind=c_char), intent(in) :: name(*)
     end function
