@@ -79,3 +79,39 @@ def check_jw_steady(coarse, fine):
 
 def test_oracle_holds_the_jw_steady_state():
     check_jw_steady(run_jw_steady(Oracle, *JW_COARSE), run_jw_steady(Oracle, *JW_FINE))
+
+
+def rh_wave_angular_speed(model_cls, nlon, nlat, dt, days=2):
+    """Angular phase speed of zonal wavenumber 4 of gz between 20 and 60 degrees (both hemispheres), from daily phases."""
+    host = Host(nlon, nlat, 1, dt, "rossby_haurwitz_wave")
+    m = model_cls(host); m.set_state(host.initial_condition()); m.prepare_run()
+    lat = host.vec["full_lat"][host.hy:host.hy + host.nlat]
+    rows = np.where((np.abs(lat) > np.radians(20)) & (np.abs(lat) < np.radians(60)))[0]
+
+    def phase():
+        f = np.fft.rfft(host.interior(m.field("gz"), "cell")[0][rows], axis=1)[:, 4]
+        return np.angle((f * np.abs(f)).sum()), float(np.abs(f).mean())
+    prev, a0 = phase(); tot = 0.0
+    for _ in range(days):
+        m.run_steps(int(round(86400 / dt)))
+        p, a = phase()
+        tot += np.angle(np.exp(1j * (prev - p))); prev = p          # cos(4 (lon - nu t)): the phase falls by 4 nu t
+    if hasattr(m, "close"):
+        m.close()
+    return tot / 4 / (days * 86400.0), a / a0, host
+
+
+def test_oracle_moves_the_rossby_haurwitz_wave_east_at_the_known_rate():
+    """Williamson case 6 (tests/swm/rossby_haurwitz_wave_test_mod.F90): wavenumber 4 moves from west to east without
+    change of shape at nu = [R (3 + R) w - 2 Omega] / [(1 + R)(2 + R)] = 12.3 degrees per day in the non-divergent
+    barotropic model (Haurwitz 1940); the divergent shallow-water wave is a few per cent slower.  Direction, rate and
+    mesh independence: a wrong sign or factor in the Coriolis / vorticity-flux terms fails this, whatever the oracle and
+    the kernels agree on."""
+    K, R = 7.848e-6, 4
+    nu90, amp90, host = rh_wave_angular_speed(Oracle, 90, 45, 600.0)
+    nu180, amp180, _ = rh_wave_angular_speed(Oracle, 180, 90, 300.0)
+    nu_th = (R * (3 + R) * K - 2 * host.cfg.omega) / ((1 + R) * (2 + R))
+    for nu in (nu90, nu180):
+        assert 0.88 < nu / nu_th < 0.97, (nu, nu_th)            # measured 0.918 / 0.915
+    assert abs(nu90 - nu180) / nu_th < 0.01                       # converged: not a truncation artefact
+    assert 0.97 < amp90 < 1.06 and 0.97 < amp180 < 1.06           # the wave keeps its amplitude over two days
